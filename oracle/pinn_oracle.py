@@ -1,0 +1,474 @@
+"""Plain-PyTorch CPU restatement of the reference PINN classes (test oracle / CPU baseline).
+
+TEST INFRASTRUCTURE: see oracle/__init__.py.  Every class keeps the reference's method names,
+argument order, return arity, state_dict keys and tensor shapes (including the reference's
+`[N]` x `[N,1]` broadcast in the 2-D files), but is written independently and runs in whatever
+dtype its parameters have, so the same code serves as the fp32 "port" baseline and the fp64
+truth.
+
+Short path names (all under /root/reference/):
+  NBroot = Gross_Pitaevskii_1D_power_Test.ipynb          (cell N:line L)
+  R/     = Gross-Pitaevskii/src/final/refine/
+  S/     = Gross-Pitaevskii/src/
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+from torch.autograd import grad as _grad
+
+
+# --------------------------------------------------------------------------------------
+# activations and the MLP
+# --------------------------------------------------------------------------------------
+class ShiftedTanh(nn.Module):
+    """tanh(x) + 1 + eps  (R/harmonic_pinn_simulation.py:41-49)."""
+
+    def __init__(self, eps=float(np.finfo(float).eps)):
+        super().__init__()
+        self.eps = eps
+
+    def forward(self, z):
+        return torch.tanh(z) + 1.0 + self.eps
+
+
+def sequential_mlp(widths, act_factory):
+    """Linear/act/.../Linear as nn.Sequential; keys network.{0,2,4,...}
+    (NBroot cell 6:30-39, R/harmonic_pinn_simulation.py:84-93, S/gross_pitaevskii_2D.py:59-65)."""
+    mods = []
+    last = len(widths) - 2
+    for i in range(len(widths) - 1):
+        mods.append(nn.Linear(widths[i], widths[i + 1]))
+        if i < last:
+            mods.append(act_factory())
+    return nn.Sequential(*mods)
+
+
+def d_dx(out, x):
+    """`torch.autograd.grad(out, x, ones_like(out), create_graph=True)[0]`, the reference's
+    derivative idiom (NBroot cell 6:90-104)."""
+    return _grad(out, x, grad_outputs=torch.ones_like(out), create_graph=True, retain_graph=True)[0]
+
+
+def xavier_bias001_(module):
+    """S/gross_pitaevskii_2D.py:614-618 / S/gross_pitaevskii_1D_Different_Optimizers.py:443-455."""
+    if isinstance(module, nn.Linear):
+        nn.init.xavier_uniform_(module.weight)
+        module.bias.data.fill_(0.01)
+
+
+# --------------------------------------------------------------------------------------
+# analytic base states
+# --------------------------------------------------------------------------------------
+def hermite_poly_np(n, x):
+    """Physicists' Hermite polynomial H_n by the three-term recurrence (numpy, float64)."""
+    x = np.asarray(x, dtype=np.float64)
+    h0 = np.ones_like(x)
+    if n == 0:
+        return h0
+    h1 = 2.0 * x
+    for k in range(1, n):
+        h0, h1 = h1, 2.0 * x * h1 - 2.0 * k * h0
+    return h1
+
+
+def hermite_norm(n):
+    return (2.0 ** n * math.factorial(n) * math.sqrt(math.pi)) ** (-0.5)
+
+
+def hermite_state_constH(x, n):
+    """NBroot cell 6:41-48 / S/gross_pitaevskii_1D_Different_Optimizers.py:89-111: H_n is
+    evaluated on a *detached* numpy copy of x (so it is a constant for autograd) and cast to
+    float32; only exp(-x^2/2) is differentiated."""
+    h = hermite_poly_np(n, x.detach().cpu().numpy())
+    h_t = torch.tensor(h, dtype=torch.float32).to(x.device)
+    return hermite_norm(n) * torch.exp(-x ** 2 / 2) * h_t
+
+
+def hermite_state_torch(x, n):
+    """R/harmonic_pinn_simulation.py:95-119: recurrence in torch, fully differentiable."""
+    if n == 0:
+        hn = torch.ones_like(x)
+    elif n == 1:
+        hn = 2.0 * x
+    else:
+        a, b = torch.ones_like(x), 2.0 * x
+        for k in range(1, n):
+            hn = 2.0 * x * b - 2.0 * float(k) * a
+            a, b = b, hn
+    return torch.tensor(hermite_norm(n), dtype=x.dtype, device=x.device) * (hn * torch.exp(-0.5 * x ** 2))
+
+
+# --------------------------------------------------------------------------------------
+# F-root: the root notebook class (BASELINE config 1)
+# --------------------------------------------------------------------------------------
+class RootGPE1D(nn.Module):
+    """NBroot cell 6 `GrossPitaevskiiPINN(layers, hbar, m, mode, gamma, power)`."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, power=1.0):
+        super().__init__()
+        self.layers = layers
+        self.network = sequential_mlp(layers, nn.Tanh)
+        self.hbar, self.m, self.mode, self.gamma, self.power = hbar, m, mode, gamma, power
+
+    def weighted_hermite(self, x, n):
+        return hermite_state_constH(x, n)
+
+    def forward(self, inputs):
+        return self.network(inputs)
+
+    def get_complete_solution(self, x, perturbation, mode=0):
+        return self.weighted_hermite(x, mode) + perturbation
+
+    def compute_potential(self, x, potential_type="harmonic", **kw):
+        """NBroot cell 6:63-79."""
+        if potential_type == "harmonic":
+            return 0.5 * kw.get("omega", 1.0) ** 2 * x ** 2
+        if potential_type == "gaussian":
+            return torch.exp(-(x - kw.get("a", 0.0)) ** 2)
+        if potential_type == "periodic":
+            return kw.get("V0", 1.0) * torch.cos(kw.get("k", 2 * np.pi / 5.0) * x) ** 2
+        raise ValueError(f"Unknown potential type: {potential_type}")
+
+    def pde_loss(self, p, inputs, predictions, gamma, potential_type="harmonic", precomputed_potential=None):
+        """NBroot cell 6:81-127: Hu = -u''/2 + V u + gamma u**p, Rayleigh mu, mean r^2."""
+        u = self.get_complete_solution(inputs, predictions, self.mode)
+        u_x = d_dx(u, inputs)
+        u_xx = d_dx(u_x, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        hu = -0.5 * u_xx + V * u + gamma * u ** p
+        mu = torch.mean(u * hu) / torch.mean(u ** 2)
+        r = hu - mu * u
+        return torch.mean(r ** 2), r, mu, u
+
+    def boundary_loss(self, boundary_points, boundary_values):
+        """NBroot cell 6:129-135."""
+        full = self.get_complete_solution(boundary_points, self.forward(boundary_points), self.mode)
+        return torch.mean((full - boundary_values) ** 2)
+
+    def symmetry_loss(self, collocation_points, lb, ub):
+        """NBroot cell 6:137-155: NN output only, mirror about 0, parity from the mode."""
+        a = self.forward(collocation_points)
+        b = self.forward(-collocation_points)
+        return torch.mean((a + b) ** 2) if self.mode % 2 == 1 else torch.mean((a - b) ** 2)
+
+    def normalization_loss(self, u, dx):
+        """NBroot cell 6:157-162."""
+        return (torch.sum(u ** 2) * dx - 1.0) ** 2
+
+
+def root_train_terms(model, X, boundary_points, boundary_values, dx, gamma, power, lb, ub,
+                     potential_type="harmonic"):
+    """Loop body NBroot cell 10:88-97 (without the optimizer): returns
+    (total, pde, bc, norm, sym, mu)."""
+    u_pred = model.forward(X)
+    pde, _, mu, full_u = model.pde_loss(power, X, u_pred, gamma, potential_type)
+    bc = model.boundary_loss(boundary_points, boundary_values)
+    nrm = model.normalization_loss(full_u, dx)
+    sym = model.symmetry_loss(X, lb, ub)
+    return pde + 10.0 * bc + 20.0 * nrm + 5.0 * sym, pde, bc, nrm, sym, mu
+
+
+# --------------------------------------------------------------------------------------
+# F-final: the paper's PL-PINN scripts (own the shipped .pkl fixtures)
+# --------------------------------------------------------------------------------------
+class FinalGPE1D(nn.Module):
+    """R/harmonic_pinn_simulation.py:52-217 `GrossPitaevskiiPINN(layers, hbar, m, mode, gamma,
+    use_perturbation)`; `potential='box'` follows R/box_pinn_simulation.py:52-262 (sin(pi x)
+    boundary factor in forward, analytic base derivatives)."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, use_perturbation=True,
+                 potential="harmonic", L=1.0):
+        super().__init__()
+        self.layers = layers
+        self.network = sequential_mlp(layers, ShiftedTanh)
+        self.hbar, self.m, self.mode, self.gamma = hbar, m, mode, gamma
+        self.use_perturbation = use_perturbation
+        self.potential, self.L = potential, L
+
+    def weighted_hermite(self, x, n):
+        return hermite_state_torch(x, n)
+
+    def box_eigenfunction(self, x, n):
+        """R/box_pinn_simulation.py:99-117."""
+        return torch.sqrt(torch.tensor(2.0 / self.L)) * torch.sin((n + 1) * torch.pi * x / self.L)
+
+    def forward(self, inputs):
+        out = self.network(inputs)
+        if self.potential == "box":                      # R/box_pinn_simulation.py:119-130
+            out = out * torch.sin(torch.pi * inputs)
+        return out
+
+    def get_complete_solution(self, x, perturbation, mode=None):
+        n = self.mode if mode is None else mode
+        base = self.box_eigenfunction(x, n) if self.potential == "box" else self.weighted_hermite(x, n)
+        return base + perturbation
+
+    def compute_potential(self, x, potential_type="harmonic", **kw):
+        if potential_type == "harmonic":                 # R/harmonic_pinn_simulation.py:136-144
+            return x ** 2
+        if potential_type == "box":                      # R/box_pinn_simulation.py:182-190
+            return torch.zeros_like(x)
+        raise ValueError(f"Unknown potential type: {potential_type}")
+
+    def _jets(self, inputs, predictions):
+        if not self.use_perturbation:
+            u = predictions
+            u_x = d_dx(u, inputs)
+            return u, u_x, d_dx(u_x, inputs)
+        if self.potential == "box":                      # R/box_pinn_simulation.py:141-180
+            k = (self.mode + 1) * np.pi / self.L
+            xn = inputs.detach().cpu().numpy().flatten()
+            c = np.sqrt(2.0 / self.L)
+            as_col = lambda a: torch.tensor(a, dtype=torch.float32).reshape(-1, 1).to(inputs.device)
+            b0, b1, b2 = as_col(c * np.sin(k * xn)), as_col(c * k * np.cos(k * xn)), as_col(-c * k ** 2 * np.sin(k * xn))
+            p_x = d_dx(predictions, inputs)
+            p_xx = d_dx(p_x, inputs)
+            return b0 + predictions, b1 + p_x, b2 + p_xx
+        u = self.get_complete_solution(inputs, predictions)
+        u_x = d_dx(u, inputs)
+        return u, u_x, d_dx(u_x, inputs)
+
+    def pde_loss(self, inputs, predictions, gamma, p, potential_type=None, precomputed_potential=None):
+        """R/harmonic_pinn_simulation.py:146-196: Hu = -u'' + V u + gamma u**p."""
+        potential_type = potential_type or self.potential
+        u, _, u_xx = self._jets(inputs, predictions)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        hu = -u_xx + V * u + gamma * u ** p
+        mu = torch.mean(u * hu) / torch.mean(u ** 2)
+        return torch.mean((hu - mu * u) ** 2), mu
+
+    def boundary_loss(self, boundary_points, boundary_values):
+        """R/harmonic_pinn_simulation.py:198-210 (unscaled NN output + base)."""
+        out = self.forward(boundary_points)
+        full = self.get_complete_solution(boundary_points, out) if self.use_perturbation else out
+        return torch.mean((full - boundary_values) ** 2)
+
+    def normalization_loss(self, u, dx):
+        return (torch.sum(u ** 2) * dx - 1.0) ** 2
+
+
+def final_train_terms(model, X, boundary_points, boundary_values, dx, gamma, p, perturb_const, normal_const):
+    """Loop body R/harmonic_pinn_simulation.py:332-355: returns (total, pde, bc, norm, mu)."""
+    u_pred = perturb_const * model.forward(X) / normal_const
+    bc = model.boundary_loss(boundary_points, boundary_values)
+    nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+    pde, mu = model.pde_loss(X, u_pred, gamma, p)
+    return pde + 10.0 * bc + 20.0 * nrm, pde, bc, nrm, mu
+
+
+# --------------------------------------------------------------------------------------
+# F-opt: S/gross_pitaevskii_1D_Different_Optimizers.py (BASELINE config 2 family)
+# --------------------------------------------------------------------------------------
+class OptGPE1D(nn.Module):
+    """S/gross_pitaevskii_1D_Different_Optimizers.py:27-440."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, mode=0, beta_init=1.0, alpha_init=1.0, decay_rate=0.001):
+        super().__init__()
+        self.layers = layers
+        self.network = sequential_mlp(layers, nn.Tanh)
+        self.g, self.hbar, self.m, self.mode = g, hbar, m, mode
+        self.beta, self.alpha, self.decay_rate, self.iteration = beta_init, alpha_init, decay_rate, 0
+
+    def weighted_hermite(self, x, n):
+        return hermite_state_constH(x, n)
+
+    def forward(self, inputs):
+        return self.network(inputs)
+
+    compute_potential = RootGPE1D.compute_potential
+
+    def get_complete_solution(self, x, perturbation, prev_prediction=None):
+        """:175-213 (the norm it computes is unused)."""
+        if prev_prediction is None:
+            return self.weighted_hermite(x, self.mode) + self.alpha * perturbation
+        return self.beta * prev_prediction(x) + self.alpha * perturbation
+
+    def boundary_loss(self, boundary_points, boundary_values, prev_prediction=None):
+        u = self.get_complete_solution(boundary_points, self.forward(boundary_points), prev_prediction)
+        return torch.mean((u - boundary_values) ** 2)
+
+    def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None):
+        """:239-282, mean form."""
+        u = self.get_complete_solution(inputs, predictions, prev_prediction)
+        u_x = d_dx(u, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        return 0.5 * (torch.mean(u_x ** 2) + torch.mean(V * u ** 2) + 0.5 * eta * torch.mean(u ** 4))
+
+    def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None):
+        """:284-346: energy-quotient mu, r = -u'' + V u + eta |u^2| u - mu u."""
+        u = self.get_complete_solution(inputs, predictions, prev_prediction)
+        u_x = d_dx(u, inputs)
+        u_xx = d_dx(u_x, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        mu = torch.mean(u_x ** 2 + V * u ** 2 + eta * u ** 4) / torch.mean(u ** 2)
+        r = -u_xx + V * u + eta * torch.abs(u ** 2) * u - mu * u
+        return torch.mean(r ** 2), r, mu
+
+    def symmetry_loss(self, collocation_points, lb, ub):
+        """:348-375."""
+        a = self.forward(collocation_points)
+        b = self.forward((lb + ub) - collocation_points)
+        return torch.mean((a - b) ** 2)
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights,
+                   potential_type, precomputed_potential=None, prev_prediction=None):
+        """:377-440: returns (total, data, riesz, pde, norm); the weighted 5-term sum is computed
+        and then replaced by data + pde/len + riesz/len (:438).  `weighted` is exposed as a 6th
+        return-less attribute for tests."""
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(collocation_points, potential_type)
+        data = self.boundary_loss(boundary_points, boundary_values, prev_prediction)
+        riesz = self.riesz_loss(self.forward(collocation_points), collocation_points, eta, potential_type, V, prev_prediction)
+        pde, _, _ = self.pde_loss(collocation_points, self.forward(collocation_points), eta, potential_type, V, prev_prediction)
+        norm = (torch.norm(self.forward(collocation_points), p=2) - 1) ** 2
+        sym = self.symmetry_loss(collocation_points, lb, ub)
+        length = ub - lb
+        terms = [data, riesz / length, pde / length, norm, sym]
+        self.last_weighted_sum = sum(w * t for w, t in zip(weights, terms))
+        total = data + pde / length + riesz / length
+        return total, data, riesz, pde, norm
+
+
+# --------------------------------------------------------------------------------------
+# G2D: S/gross_pitaevskii_2D.py (BASELINE configs 4/5 family) -- keeps the [N]x[N,1] broadcast
+# --------------------------------------------------------------------------------------
+class GPE2D(nn.Module):
+    """S/gross_pitaevskii_2D.py:16-274.  `potential` extends compute_potential beyond the
+    reference's Gaussian so the BASELINE harmonic / optical-lattice configs can be stated."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, potential="gaussian"):
+        super().__init__()
+        self.layers = layers
+        self.network = sequential_mlp(layers, nn.Tanh)
+        self.hbar, self.m, self.g, self.potential = hbar, m, g, potential
+
+    def forward(self, x):
+        return self.network(x)
+
+    def boundary_loss(self, x_bc, y_bc):
+        """:83-109: target forced to zero, x10."""
+        return torch.mean(self.forward(x_bc) ** 2) * 10
+
+    def compute_potential(self, inputs, V0=1.0, x0=np.pi / 2, y0=np.pi / 2, sigma=0.5):
+        """:244-274 -> shape [N]."""
+        x, y = inputs[:, 0], inputs[:, 1]
+        if self.potential == "gaussian":
+            return V0 * torch.exp(-((x - x0) ** 2 + (y - y0) ** 2) / (2 * sigma ** 2))
+        if self.potential == "harmonic":
+            return 0.5 * (x ** 2 + y ** 2)
+        if self.potential == "lattice":                  # V0 cos^2(kx) form of NBroot cell 6:73-76 per axis + trap
+            k = 2 * np.pi / 5.0
+            return V0 * torch.cos(k * x) ** 2 + V0 * torch.cos(k * y) ** 2 + 0.5 * (x ** 2 + y ** 2)
+        raise ValueError(self.potential)
+
+    def riesz_loss(self, predictions, inputs):
+        """:112-151, sum form (V unsqueezed -> no broadcast bug here)."""
+        u = predictions
+        g_ = d_dx(u, inputs)
+        V = self.compute_potential(inputs).unsqueeze(1)
+        return 0.5 * (torch.sum(g_ ** 2) + torch.sum(V * u ** 2) + 0.5 * self.g * torch.sum(u ** 4))
+
+    def pde_loss(self, inputs, predictions):
+        """:154-213.  u is [N,1]; u_x, u_xx, V are [N]  => lambda and the residual broadcast to
+        [N,N] exactly as in the reference."""
+        u = predictions
+        u_x = d_dx(u, inputs)[:, 0]
+        u_y = d_dx(u, inputs)[:, 1]
+        u_xx = d_dx(u_x, inputs)[:, 0]
+        u_yy = d_dx(u_y, inputs)[:, 1]
+        lap = u_xx + u_yy
+        V = self.compute_potential(inputs)
+        mu = torch.mean(u_x ** 2 + u_y ** 2 + V * u ** 2 + self.g * u ** 4) / torch.mean(u ** 2)
+        r = -lap + V * u + self.g * torch.abs(u ** 2) * u - (mu * u)
+        L_f = 1 / (torch.mean(u ** 2) + 1e-2)
+        L_lambda = 1 / (mu ** 2 + 1e-6)
+        return torch.mean(r ** 2) + L_f + L_lambda, r, mu
+
+    def loss(self, x, x_bc, u_bc):
+        """:215-242."""
+        data = self.boundary_loss(x_bc, u_bc)
+        riesz = self.riesz_loss(self.forward(x), x)
+        pde, _, _ = self.pde_loss(x, self.forward(x))
+        return data + pde + riesz
+
+
+def gpe2d_pointwise_terms(model, x, x_bc):
+    """The *intended* (pointwise, all [N,1]) mathematics of S/gross_pitaevskii_2D.py:154-242:
+    returns (total, bc, pde_with_regs, riesz, mu)."""
+    u = model.forward(x)
+    gr = d_dx(u, x)
+    u_x, u_y = gr[:, [0]], gr[:, [1]]
+    lap = d_dx(u_x, x)[:, [0]] + d_dx(u_y, x)[:, [1]]
+    V = model.compute_potential(x).unsqueeze(1)
+    mu = torch.mean(u_x ** 2 + u_y ** 2 + V * u ** 2 + model.g * u ** 4) / torch.mean(u ** 2)
+    r = -lap + V * u + model.g * torch.abs(u ** 2) * u - mu * u
+    pde = torch.mean(r ** 2) + 1 / (torch.mean(u ** 2) + 1e-2) + 1 / (mu ** 2 + 1e-6)
+    riesz = 0.5 * (torch.sum(gr ** 2) + torch.sum(V * u ** 2) + 0.5 * model.g * torch.sum(u ** 4))
+    bc = model.boundary_loss(x_bc, None)
+    return bc + pde + riesz, bc, pde, riesz, mu
+
+
+# --------------------------------------------------------------------------------------
+# H-sq: S/helmholtz_2D.py (BASELINE config 3)
+# --------------------------------------------------------------------------------------
+class Helmholtz2D(nn.Module):
+    """S/helmholtz_2D.py:19-132.  `activation='leaky_relu'` is the reference default (:31);
+    'tanh' follows S/helmholtz_2D_circle_3.py:31.  a1,a2 generalise the source to
+    sin(a1 pi x) sin(a2 pi y) (BASELINE config 3); a1=a2=1 is the reference."""
+
+    def __init__(self, layers, activation="leaky_relu", a1=1, a2=1):
+        super().__init__()
+        self.activation = nn.LeakyReLU() if activation == "leaky_relu" else nn.Tanh()
+        self.loss_function = nn.MSELoss()
+        self.linears = nn.ModuleList([nn.Linear(layers[i], layers[i + 1]) for i in range(len(layers) - 1)])
+        self.a1, self.a2 = a1, a2
+        for lin in self.linears:
+            nn.init.xavier_normal_(lin.weight)
+            nn.init.zeros_(lin.bias)
+
+    def forward(self, x):
+        for lin in self.linears[:-1]:
+            x = self.activation(lin(x))
+        return self.linears[-1](x)
+
+    def loss_pde(self, x_f, k):
+        """:58-89 ([N] + [N,1] -> [N,N] residual, MSE over all N^2 entries)."""
+        g = x_f.clone().requires_grad_(True)
+        u = self.forward(g)
+        u_x = d_dx(u, g)[:, 0]
+        u_y = d_dx(u, g)[:, 1]
+        lap = d_dx(u_x, g)[:, 0] + d_dx(u_y, g)[:, 1]
+        q = k ** 2 * torch.sin(self.a1 * np.pi * g[:, [0]]) * torch.sin(self.a2 * np.pi * g[:, [1]])
+        f = lap + k ** 2 * u - q
+        return self.loss_function(f, torch.zeros_like(f))
+
+    def loss_pde_pointwise(self, x_f, k):
+        """Intended mathematics: everything [N,1]."""
+        g = x_f.clone().requires_grad_(True)
+        u = self.forward(g)
+        gr = d_dx(u, g)
+        lap = d_dx(gr[:, [0]], g)[:, [0]] + d_dx(gr[:, [1]], g)[:, [1]]
+        q = k ** 2 * torch.sin(self.a1 * np.pi * g[:, [0]]) * torch.sin(self.a2 * np.pi * g[:, [1]])
+        return torch.mean((lap + k ** 2 * u - q) ** 2)
+
+    def loss_data(self, x_u, u_true):
+        return self.loss_function(self.forward(x_u), u_true)
+
+    def compute_loss(self, x_f, x_u, u_true, k):
+        return self.loss_pde(x_f, k) + self.loss_data(x_u, u_true)
+
+
+# --------------------------------------------------------------------------------------
+# helpers shared by tests / bench
+# --------------------------------------------------------------------------------------
+def linear_layers(module):
+    """The nn.Linear modules of an oracle (or reference) model, input to output."""
+    return [m for m in module.modules() if isinstance(m, nn.Linear)]
+
+
+def param_grads(model, scalar):
+    """d scalar / d theta as a list ordered like `model.parameters()` (zeros for unused)."""
+    ps = list(model.parameters())
+    gs = torch.autograd.grad(scalar, ps, allow_unused=True)
+    return [torch.zeros_like(p) if g is None else g for p, g in zip(ps, gs)]

@@ -1,0 +1,280 @@
+"""Generate the golden vectors in this directory from the REAL reference classes.
+
+Run in the build container only (needs /root/reference):
+    python tests/golden/make_golden.py
+Every case stores its inputs (weights, points, scalars) and the reference's outputs computed
+twice: in the reference's own float32 and with the same class cast to float64 (`model.double()`),
+the latter being the truth the 1e-5 parity bar is measured against.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+from oracle import reference_loader as rl  # noqa: E402
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _state(model):
+    return {k: _np(v).copy() for k, v in model.state_dict().items()}
+
+
+def _grads(model, total):
+    model.zero_grad()
+    total.backward()
+    return [(_np(p.grad) if p.grad is not None else np.zeros(tuple(p.shape), dtype=_np(p).dtype)) for p in model.parameters()]
+
+
+def _pack(prefix, d, out):
+    for k, v in d.items():
+        if isinstance(v, (list, tuple)):
+            for i, vi in enumerate(v):
+                out[f"{prefix}{k}.{i}"] = np.asarray(vi)
+        else:
+            out[f"{prefix}{k}"] = np.asarray(v)
+
+
+def _both_dtypes(build, run):
+    """build() -> model (float32, seeded); run(model, dtype) -> dict of outputs."""
+    out = {}
+    m32 = build()
+    _pack("w.", _state(m32), out)
+    _pack("f32.", run(m32, torch.float32), out)
+    m64 = build().double()
+    _pack("f64.", run(m64, torch.float64), out)
+    return out
+
+
+def seeded(ctor, seed=1234, init=None):
+    def build():
+        torch.manual_seed(seed)
+        m = ctor()
+        if init is not None:
+            m.apply(init)
+        return m
+    return build
+
+
+def xavier(m):
+    if isinstance(m, torch.nn.Linear):
+        torch.nn.init.xavier_uniform_(m.weight)
+        m.bias.data.fill_(0.01)
+
+
+# ------------------------------------------------------------------------------ F-root
+def case_root(mode, p, gamma, layers, n_pts):
+    Cls = rl.load_root_notebook_class()
+    lb, ub = -10.0, 10.0
+    Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
+    dx = float(Xn[1, 0] - Xn[0, 0])
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        bp = torch.tensor([[lb], [ub]], dtype=dt)
+        bv = torch.zeros((2, 1), dtype=dt)
+        u_pred = model.forward(X)
+        pde, res, mu, full_u = model.pde_loss(p, X, u_pred, gamma, "harmonic")
+        bc = model.boundary_loss(bp, bv)
+        nrm = model.normalization_loss(full_u, dx)
+        sym = model.symmetry_loss(X, lb, ub)
+        total = pde + 10.0 * bc + 20.0 * nrm + 5.0 * sym
+        return dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), sym=_np(sym), total=_np(total), mu=_np(mu),
+                    u=_np(full_u)[:, 0], residual=_np(res)[:, 0], grads=_grads(model, total))
+
+    out = _both_dtypes(seeded(lambda: Cls(layers, mode=mode, gamma=gamma, power=p), init=xavier), run)
+    out.update(X=Xn, dx=dx, lb=lb, ub=ub, mode=mode, p=p, gamma=gamma, layers=np.array(layers))
+    return out
+
+
+# ------------------------------------------------------------------------------ F-final (pkl fixtures)
+def case_final_fixture(kind):
+    """Protocol of SURVEY.md 8c-1: shipped weights, X = linspace(lb,ub,4000),
+    u_pred = 0.01*model(X)/const, pde_loss(X,u_pred,0,3) -> mu must equal mu_table."""
+    if kind == "harmonic":
+        mod = rl.load_script("final/refine/harmonic_pinn_simulation.py")
+        data = rl.load_pickle("harmonic_test/harmonic_mode_zero_plot_data.pkl")
+        lb, ub, ptype = -10.0, 10.0, "harmonic"
+    else:
+        mod = rl.load_script("final/refine/box_pinn_simulation.py")
+        data = rl.load_pickle("box_test/box_mode_zero_plot_data.pkl")
+        lb, ub, ptype = 0.0, 1.0, "box"
+    mod.device = torch.device("cpu")
+    Xn = np.linspace(lb, ub, 4000).reshape(-1, 1)
+    dx = float(Xn[1, 0] - Xn[0, 0])
+    out = dict(X=Xn, dx=dx, lb=lb, ub=ub, perturb_const=0.01)
+    for mode in range(6):
+        entry = data["models_state_dicts"][mode][0]
+        const = float(data["constant_history"][mode])
+        out[f"m{mode}.mu_table"] = float(data["mu_table"][mode][0][1])
+        out[f"m{mode}.const"] = const
+        for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+            model = mod.GrossPitaevskiiPINN(entry["layers"], mode=mode, gamma=0.0)
+            model.load_state_dict(entry["state_dict"])
+            model = model.to(dt)
+            X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+            bp = torch.tensor([[lb], [ub]], dtype=dt)
+            bv = torch.zeros((2, 1), dtype=dt)
+            u_pred = 0.01 * model.forward(X) / const
+            bc = model.boundary_loss(bp, bv)
+            nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+            pde, mu = model.pde_loss(X, u_pred, 0.0, 3, ptype)
+            total = pde + 10.0 * bc + 20.0 * nrm
+            _pack(f"m{mode}.{tag}.", dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), total=_np(total), mu=_np(mu),
+                                          grads=_grads(model, total)), out)
+        _pack(f"m{mode}.w.", {k: _np(v) for k, v in entry["state_dict"].items()}, out)
+        out[f"m{mode}.layers"] = np.array(entry["layers"])
+    return out
+
+
+def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic"):
+    script = "final/refine/harmonic_pinn_simulation.py" if kind == "harmonic" else "final/refine/box_pinn_simulation.py"
+    mod = rl.load_script(script)
+    mod.device = torch.device("cpu")
+    lb, ub = (-10.0, 10.0) if kind == "harmonic" else (0.0, 1.0)
+    Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
+    dx = float(Xn[1, 0] - Xn[0, 0])
+    const, pc = 0.37, 0.01
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        bp = torch.tensor([[lb], [ub]], dtype=dt)
+        bv = torch.zeros((2, 1), dtype=dt)
+        u_pred = pc * model.forward(X) / const
+        bc = model.boundary_loss(bp, bv)
+        nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+        pde, mu = model.pde_loss(X, u_pred, gamma, p, kind)
+        total = pde + 10.0 * bc + 20.0 * nrm
+        return dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), total=_np(total), mu=_np(mu), grads=_grads(model, total))
+
+    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, gamma=gamma), init=xavier), run)
+    out.update(X=Xn, dx=dx, lb=lb, ub=ub, mode=mode, p=p, gamma=gamma, const=const, perturb_const=pc,
+               layers=np.array(layers))
+    return out
+
+
+# ------------------------------------------------------------------------------ F-opt
+def case_opt(mode, eta, layers, n_pts):
+    ns = rl.load_class_by_lines("gross_pitaevskii_1D_Different_Optimizers.py", 27, 440)
+    Cls = ns["GrossPitaevskiiPINN"]
+    lb, ub = -10.0, 10.0
+    rng = np.random.default_rng(7)
+    Xn = np.sort(lb + (ub - lb) * rng.random((n_pts, 1)), axis=0)
+    weights = [50.0, 1.0, 2.0, 10.0, 25.0]
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        bp = torch.tensor([[lb], [ub]], dtype=dt)
+        bv = torch.zeros((2, 1), dtype=dt)
+        lbt, ubt = torch.tensor(lb, dtype=dt), torch.tensor(ub, dtype=dt)
+        total, data, riesz, pde, norm = model.total_loss(X, bp, bv, eta, lbt, ubt, weights, "harmonic")
+        sym = model.symmetry_loss(X, lbt, ubt)
+        _, _, mu = model.pde_loss(X, model.forward(X), eta, "harmonic")
+        g_total = _grads(model, total)
+        # the weighted five-term sum (what _Self_Adaptive / _Nonlinearity_Powers actually optimise)
+        total2, data2, riesz2, pde2, norm2 = model.total_loss(X, bp, bv, eta, lbt, ubt, weights, "harmonic")
+        length = ubt - lbt
+        five = (weights[0] * data2 + weights[1] * riesz2 / length + weights[2] * pde2 / length
+                + weights[3] * norm2 + weights[4] * model.symmetry_loss(X, lbt, ubt))
+        g_five = _grads(model, five)
+        return dict(total=_np(total), data=_np(data), riesz=_np(riesz), pde=_np(pde), norm=_np(norm), sym=_np(sym),
+                    mu=_np(mu), five=_np(five), grads=g_total, grads_five=g_five)
+
+    out = _both_dtypes(seeded(lambda: Cls(layers, mode=mode), init=xavier), run)
+    out.update(X=Xn, lb=lb, ub=ub, mode=mode, eta=eta, weights=np.array(weights), layers=np.array(layers))
+    return out
+
+
+# ------------------------------------------------------------------------------ G2D
+def case_g2d(layers, n_pts, n_bc, g):
+    mod = rl.load_script("gross_pitaevskii_2D.py")
+    mod.device = torch.device("cpu")
+    rng = np.random.default_rng(11)
+    Xn = rng.random((n_pts, 2)) * np.pi
+    th = np.linspace(0, 2 * np.pi, n_bc)
+    Xb = np.column_stack((np.pi / 2 + np.pi / 2 * np.cos(th), np.pi / 2 + np.pi / 2 * np.sin(th)))
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        xb = torch.tensor(Xb, dtype=dt)
+        ub = torch.zeros((n_bc, 1), dtype=dt)
+        total = model.loss(X, xb, ub)
+        bc = model.boundary_loss(xb, ub)
+        riesz = model.riesz_loss(model.forward(X), X)
+        pde, res, mu = model.pde_loss(X, model.forward(X))
+        return dict(total=_np(total), bc=_np(bc), riesz=_np(riesz), pde=_np(pde), mu=_np(mu),
+                    res_shape=np.array(res.shape), grads=_grads(model, total))
+
+    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers, g=g), init=xavier), run)
+    out.update(X=Xn, Xb=Xb, g=g, layers=np.array(layers))
+    return out
+
+
+# ------------------------------------------------------------------------------ Helmholtz
+def case_helmholtz(layers, n_pts, n_bc, act):
+    mod = rl.load_script("helmholtz_2D.py")
+    mod.device = torch.device("cpu")
+    rng = np.random.default_rng(13)
+    Xn = rng.random((n_pts, 2)) * np.pi
+    Xb = rng.random((n_bc, 2)) * np.pi
+    Xb[: n_bc // 2, 0] = 0.0
+    Xb[n_bc // 2:, 1] = np.pi
+    ub_n = np.sin(np.pi * Xb[:, [0]]) * np.sin(np.pi * Xb[:, [1]])
+    k = float(np.sqrt(2.0) * np.pi)
+
+    def build():
+        torch.manual_seed(1234)
+        m = mod.HelmholtzPINN(layers)
+        if act == "tanh":
+            m.activation = torch.nn.Tanh()
+        return m
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt)
+        xb = torch.tensor(Xb, dtype=dt)
+        ub = torch.tensor(ub_n, dtype=dt)
+        pde = model.loss_pde(X, k)
+        data = model.loss_data(xb, ub)
+        total = model.compute_loss(X, xb, ub, k)
+        return dict(pde=_np(pde), data=_np(data), total=_np(total), grads=_grads(model, total))
+
+    out = _both_dtypes(build, run)
+    out.update(X=Xn, Xb=Xb, ub=ub_n, k=k, layers=np.array(layers), act=act)
+    return out
+
+
+def main():
+    torch.set_num_threads(8)
+    cases = {
+        "root_m0_p2": lambda: case_root(0, 2, 1.0, [1, 32, 32, 32, 1], 600),
+        "root_m1_p3": lambda: case_root(1, 3, 1.0, [1, 64, 64, 64, 1], 1000),
+        "root_m2_p3": lambda: case_root(2, 3, 1.0, [1, 100, 100, 100, 1], 700),
+        "final_harmonic_fixture": lambda: case_final_fixture("harmonic"),
+        "final_box_fixture": lambda: case_final_fixture("box"),
+        "final_harmonic_g20_p3_m1": lambda: case_final_random(20.0, 3, 1, [1, 64, 64, 64, 1], 900),
+        "final_harmonic_g5_p4_m2": lambda: case_final_random(5.0, 4, 2, [1, 48, 48, 1], 500),
+        "final_box_g10_p3_m0": lambda: case_final_random(10.0, 3, 0, [1, 64, 64, 64, 1], 800, kind="box"),
+        "opt_m0_eta10": lambda: case_opt(0, 10.0, [1, 64, 64, 64, 1], 900),
+        "opt_m1_eta50": lambda: case_opt(1, 50.0, [1, 128, 128, 128, 128, 1], 500),
+        "g2d_g100": lambda: case_g2d([2, 48, 48, 48, 1], 300, 40, 100.0),
+        "g2d_g1_w128": lambda: case_g2d([2, 128, 128, 128, 128, 1], 160, 24, 1.0),
+        "helmholtz_leaky": lambda: case_helmholtz([2, 40, 40, 40, 1], 300, 40, "leaky_relu"),
+        "helmholtz_tanh": lambda: case_helmholtz([2, 100, 100, 100, 1], 200, 40, "tanh"),
+    }
+    only = sys.argv[1:]
+    for name, fn in cases.items():
+        if only and name not in only:
+            continue
+        out = fn()
+        path = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(path, **out)
+        print(f"{name}: {os.path.getsize(path) / 1024:.0f} KiB")
+
+
+if __name__ == "__main__":
+    main()

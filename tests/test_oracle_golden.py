@@ -1,0 +1,153 @@
+"""The oracle restatement (oracle/pinn_oracle.py) against the golden vectors generated from the
+REAL reference classes (tests/golden/make_golden.py) and against the shipped trained weights.
+CPU only.  Tolerances: float64 runs must agree to ~1e-10 (same maths, different op order);
+float32 runs to a few float32 ulps amplified by the loss conditioning."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import pinn_oracle as po
+from helpers import load_weights, golden_grads, flat, rel_err, model_grads
+
+DT = {"f32": torch.float32, "f64": torch.float64}
+TOL = {"f32": 2e-4, "f64": 1e-9}
+
+
+def close(a, b, tol):
+    a, b = float(a), float(b)
+    return abs(a - b) <= tol * max(abs(b), 1e-30)
+
+
+@pytest.mark.parametrize("name", ["root_m0_p2", "root_m1_p3", "root_m2_p3"])
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_root(golden, name, tag):
+    g = golden(name)
+    dt = DT[tag]
+    model = load_weights(po.RootGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
+                                      power=int(g["p"])), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], dtype=dt)
+    total, pde, bc, nrm, sym, mu = po.root_train_terms(model, X, bp, torch.zeros((2, 1), dtype=dt), float(g["dx"]),
+                                                       float(g["gamma"]), int(g["p"]), lb, ub)
+    for key, val in dict(pde=pde, bc=bc, norm=nrm, sym=sym, total=total, mu=mu).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("kind", ["harmonic", "box"])
+def test_final_fixture_mu_table(golden, kind):
+    """Shipped weights -> mu must reproduce the pickled mu_table."""
+    g = golden(f"final_{kind}_fixture")
+    exact = {"harmonic": [1, 3, 5, 7, 9, 11], "box": [(n * np.pi) ** 2 for n in range(1, 7)]}[kind]
+    lb, ub = float(g["lb"]), float(g["ub"])
+    for mode in range(6):
+        for tag in ("f64", "f32"):
+            dt = DT[tag]
+            model = load_weights(po.FinalGPE1D([int(v) for v in g[f"m{mode}.layers"]], mode=mode, gamma=0.0, potential=kind),
+                                 g, prefix=f"m{mode}.w.").to(dt)
+            X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+            bp = torch.tensor([[lb], [ub]], dtype=dt)
+            total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), dtype=dt), float(g["dx"]),
+                                                           0.0, 3, 0.01, float(g[f"m{mode}.const"]))
+            assert close(mu, g[f"m{mode}.{tag}.mu"], 1e-9 if tag == "f64" else 2e-6)
+            # converged losses are ~1e-6 differences of O(1) numbers: fp32 agreement is loose by nature
+            tol = 1e-7 if tag == "f64" else 0.3
+            for key, val in dict(pde=pde, bc=bc, norm=nrm, total=total).items():
+                ref = float(g[f"m{mode}.{tag}.{key}"])
+                assert abs(float(val) - ref) <= tol * abs(ref) + 1e-12, (mode, tag, key)
+            if tag == "f64":
+                assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"m{mode}.f64.grads"))) < 1e-7
+            else:
+                assert abs(float(mu) - float(g[f"m{mode}.mu_table"])) < 2e-5 * abs(exact[mode])
+        assert abs(float(g[f"m{mode}.mu_table"]) - exact[mode]) < 1e-4 * exact[mode]
+
+
+@pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
+                                       ("final_box_g10_p3_m0", "box")])
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_final_random(golden, name, kind, tag):
+    g = golden(name)
+    dt = DT[tag]
+    model = load_weights(po.FinalGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
+                                       potential=kind), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], dtype=dt)
+    total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), dtype=dt), float(g["dx"]),
+                                                   float(g["gamma"]), int(g["p"]), float(g["perturb_const"]), float(g["const"]))
+    for key, val in dict(pde=pde, bc=bc, norm=nrm, total=total, mu=mu).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("name", ["opt_m0_eta10", "opt_m1_eta50"])
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_opt(golden, name, tag):
+    g = golden(name)
+    dt = DT[tag]
+    model = load_weights(po.OptGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"])), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    lb, ub = torch.tensor(float(g["lb"]), dtype=dt), torch.tensor(float(g["ub"]), dtype=dt)
+    bp = torch.stack([lb, ub]).reshape(2, 1)
+    w = [float(v) for v in g["weights"]]
+    total, data, riesz, pde, norm = model.total_loss(X, bp, torch.zeros((2, 1), dtype=dt), float(g["eta"]), lb, ub, w, "harmonic")
+    five = model.last_weighted_sum
+    sym = model.symmetry_loss(X, lb, ub)
+    _, _, mu = model.pde_loss(X, model.forward(X), float(g["eta"]), "harmonic")
+    for key, val in dict(total=total, data=data, riesz=riesz, pde=pde, norm=norm, sym=sym, mu=mu, five=five).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    g5 = model_grads(model, five)
+    assert rel_err(flat(g5), flat(golden_grads(g, f"{tag}.grads_five"))) < TOL[tag]
+    total2 = model.total_loss(X, bp, torch.zeros((2, 1), dtype=dt), float(g["eta"]), lb, ub, w, "harmonic")[0]
+    assert rel_err(flat(model_grads(model, total2)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("name", ["g2d_g100", "g2d_g1_w128"])
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_g2d(golden, name, tag):
+    g = golden(name)
+    dt = DT[tag]
+    model = load_weights(po.GPE2D([int(v) for v in g["layers"]], g=float(g["g"])), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=dt)
+    total = model.loss(X, xb, None)
+    pde, res, mu = model.pde_loss(X, model.forward(X))
+    assert tuple(res.shape) == tuple(int(v) for v in g["f64.res_shape"])  # the [N,N] broadcast
+    for key, val in dict(total=total, pde=pde, mu=mu, bc=model.boundary_loss(xb, None),
+                         riesz=model.riesz_loss(model.forward(X), X)).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("name", ["helmholtz_leaky", "helmholtz_tanh"])
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_helmholtz(golden, name, tag):
+    g = golden(name)
+    dt = DT[tag]
+    act = str(g["act"])
+    model = load_weights(po.Helmholtz2D([int(v) for v in g["layers"]], activation=act), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt)
+    xb, ub = torch.tensor(g["Xb"], dtype=dt), torch.tensor(g["ub"], dtype=dt)
+    k = float(g["k"])
+    total = model.compute_loss(X, xb, ub, k)
+    for key, val in dict(pde=model.loss_pde(X, k), data=model.loss_data(xb, ub), total=total).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+def test_nn_moment_identity(golden):
+    """the [N,N] mean factorises into O(N) moments (what lets the CUDA path
+    reproduce the reference semantics at N = 4M..64M)."""
+    g = golden("helmholtz_tanh")
+    model = load_weights(po.Helmholtz2D([int(v) for v in g["layers"]], activation="tanh"), g).double()
+    X = torch.tensor(g["X"], dtype=torch.float64)
+    k = float(g["k"])
+    ref = float(model.loss_pde(X, k))
+    xg = X.clone().requires_grad_(True)
+    u = model.forward(xg)
+    gr = po.d_dx(u, xg)
+    lap = (po.d_dx(gr[:, [0]], xg)[:, [0]] + po.d_dx(gr[:, [1]], xg)[:, [1]])[:, 0]
+    b = (k ** 2 * u - k ** 2 * torch.sin(np.pi * xg[:, [0]]) * torch.sin(np.pi * xg[:, [1]]))[:, 0]
+    fact = (lap ** 2).mean() + 2 * lap.mean() * b.mean() + (b ** 2).mean()
+    assert abs(float(fact) - ref) < 1e-11 * abs(ref)
