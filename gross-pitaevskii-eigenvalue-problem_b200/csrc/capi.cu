@@ -1,0 +1,339 @@
+// C ABI of libgpe_b200.so (see include/gpe_b200.h).  No torch types; device pointers in,
+// device pointers out, everything enqueued on the caller's stream.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/gpe_b200.h"
+#include "jet_host.h"
+
+namespace gpe {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+namespace {
+
+inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+// ---------------------------------------------------------------- weight packing
+// wt_fwd[l][k=in][n=out] and w_bwd[l][k=out][n=in], zero-padded to WP; small = W0t | b | wout | bout
+__global__ void pack_weights_kernel(PtrArray W, PtrArray B, int D, int L, int Wd, int WP, float* __restrict__ wt_fwd,
+                                    float* __restrict__ w_bwd, float* __restrict__ small, float* __restrict__ small_acc) {
+    const long long n_mat = (long long)(L - 1) * WP * WP;
+    const int n_small = (D + L + 1) * WP + 4;
+    const long long total = n_mat + n_small;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        if (idx < n_mat) {
+            const int l = (int)(idx / ((long long)WP * WP));
+            const int rem = (int)(idx % ((long long)WP * WP));
+            const int k = rem / WP, nn = rem % WP;
+            const bool in = k < Wd && nn < Wd;
+            const float* w = W.p[l + 1];
+            wt_fwd[idx] = in ? w[(size_t)nn * Wd + k] : 0.f;
+            w_bwd[idx] = in ? w[(size_t)k * Wd + nn] : 0.f;
+        } else {
+            const int i = (int)(idx - n_mat);
+            const int row = i / WP, c = i % WP;
+            float v = 0.f;
+            if (row < D) {
+                if (c < Wd) v = W.p[0][(size_t)c * D + row];
+            } else if (row < D + L) {
+                if (c < Wd) v = B.p[row - D][c];
+            } else if (row == D + L) {
+                if (c < Wd) v = W.p[L][c];
+            } else if (c == 0) {
+                v = B.p[L][0];
+            }
+            small[i] = v;
+            if (small_acc) small_acc[i] = 0.f;
+        }
+    }
+}
+
+// sum the per-CTA hidden-layer accumulators and scatter everything into PyTorch-shaped grads
+__global__ void finish_grads_kernel(const float* __restrict__ dWacc, int n_cta, const float* __restrict__ small_acc,
+                                    int D, int L, int Wd, int WP, MutPtrArray dW, MutPtrArray dB) {
+    const long long n_hidden_el = (long long)(L - 1) * Wd * Wd;
+    const long long n_rest = (long long)Wd * D + (long long)L * Wd + Wd + 1;
+    const size_t cta_stride = (size_t)(L - 1) * WP * WP;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n_hidden_el + n_rest;
+         idx += (long long)gridDim.x * blockDim.x) {
+        if (idx < n_hidden_el) {
+            const int l = (int)(idx / ((long long)Wd * Wd));
+            const int rem = (int)(idx % ((long long)Wd * Wd));
+            const int o = rem / Wd, i = rem % Wd;
+            const float* src = dWacc + (size_t)l * WP * WP + (size_t)o * WP + i;
+            double s = 0.0;
+            for (int c = 0; c < n_cta; ++c) s += (double)src[(size_t)c * cta_stride];
+            dW.p[l + 1][(size_t)o * Wd + i] = (float)s;
+        } else {
+            long long j = idx - n_hidden_el;
+            if (j < (long long)Wd * D) {
+                const int c = (int)(j / D), i = (int)(j % D);
+                dW.p[0][j] = small_acc[i * WP + c];
+            } else if ((j -= (long long)Wd * D) < (long long)L * Wd) {
+                const int l = (int)(j / Wd), c = (int)(j % Wd);
+                dB.p[l][c] = small_acc[(D + l) * WP + c];
+            } else if ((j -= (long long)L * Wd) < Wd) {
+                dW.p[L][j] = small_acc[(D + L) * WP + j];
+            } else {
+                dB.p[L][0] = small_acc[(D + L + 1) * WP];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- plan cache
+struct PlanKey {
+    int d, jet, wp, L, dev;
+};
+struct PlanEntry {
+    PlanKey k;
+    JetPlan p;
+};
+std::mutex g_plan_mu;
+PlanEntry g_plans[64];
+int g_n_plans = 0;
+
+int padded_width(int w) { return w <= 64 ? 64 : w <= 128 ? 128 : 0; }
+
+int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
+    if (!desc) { set_error("null descriptor"); return -1; }
+    if (desc->d != 1 && desc->d != 2) { set_error("d must be 1 or 2 (got %d)", desc->d); return -1; }
+    if (desc->n_hidden < 1 || desc->n_hidden > kMaxLayers) { set_error("n_hidden must be in [1,%d]", kMaxLayers); return -1; }
+    if (desc->act < 0 || desc->act > 2) { set_error("unknown activation %d", desc->act); return -1; }
+    if (desc->jet < 0 || desc->jet > 3) { set_error("unknown jet kind %d", desc->jet); return -1; }
+    const int wp = padded_width(desc->width);
+    if (desc->width < 1 || !wp) { set_error("hidden width %d unsupported (1..128)", desc->width); return -1; }
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device (this library has no CPU fallback)"); return -2; }
+    *wp_out = wp;
+    std::lock_guard<std::mutex> lk(g_plan_mu);
+    for (int i = 0; i < g_n_plans; ++i) {
+        const PlanKey& k = g_plans[i].k;
+        if (k.d == desc->d && k.jet == desc->jet && k.wp == wp && k.L == desc->n_hidden && k.dev == dev) {
+            *out = g_plans[i].p;
+            return 0;
+        }
+    }
+    JetPlan p;
+    const int rc = wp == 64 ? plan_wp64(desc->d, desc->jet, desc->n_hidden, &p) : plan_wp128(desc->d, desc->jet, desc->n_hidden, &p);
+    if (rc) return rc;
+    if (g_n_plans < 64) g_plans[g_n_plans++] = PlanEntry{PlanKey{desc->d, desc->jet, wp, desc->n_hidden, dev}, p};
+    *out = p;
+    return 0;
+}
+
+struct WsLayout {
+    size_t wt_fwd, w_bwd, small, small_acc, dWacc, stash, total_fwd, total_bwd;
+    int n_small, grid_fwd, grid_bwd, tiles;
+};
+
+WsLayout layout(const gpe_mlp_desc* desc, const JetPlan& p, int wp, long long n) {
+    WsLayout w;
+    const int L = desc->n_hidden;
+    const size_t mat = (size_t)(L - 1) * wp * wp * sizeof(float);
+    w.n_small = (desc->d + L + 1) * wp + 4;
+    long long tiles = (n + p.pts_per_tile - 1) / p.pts_per_tile;
+    w.tiles = (int)tiles;
+    w.grid_fwd = (int)(tiles < p.max_ctas_fwd ? tiles : p.max_ctas_fwd);
+    w.grid_bwd = (int)(tiles < p.max_ctas_bwd ? tiles : p.max_ctas_bwd);
+    if (w.grid_fwd < 1) w.grid_fwd = 1;
+    if (w.grid_bwd < 1) w.grid_bwd = 1;
+    size_t off = 0;
+    w.wt_fwd = off; off = align_up(off + mat);
+    w.w_bwd = off; off = align_up(off + mat);
+    w.small = off; off = align_up(off + w.n_small * sizeof(float));
+    w.total_fwd = off;
+    w.small_acc = off; off = align_up(off + w.n_small * sizeof(float));
+    w.dWacc = off; off = align_up(off + (size_t)w.grid_bwd * mat);
+    w.stash = off; off = align_up(off + (size_t)w.grid_bwd * p.stash_floats_per_cta * sizeof(float));
+    w.total_bwd = off;
+    return w;
+}
+
+int check_launch(const char* what) {
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); return -4; }
+    return 0;
+}
+
+int pack(const gpe_mlp_desc* desc, int wp, const WsLayout& w, const float* const* W, const float* const* b, char* ws,
+         bool with_acc, cudaStream_t s) {
+    PtrArray Wp{}, Bp{};
+    for (int l = 0; l <= desc->n_hidden; ++l) {
+        if (!W[l] || !b[l]) { set_error("null weight/bias pointer at layer %d", l); return -1; }
+        Wp.p[l] = W[l];
+        Bp.p[l] = b[l];
+    }
+    const long long total = (long long)(desc->n_hidden - 1) * wp * wp + w.n_small;
+    const int blocks = (int)((total + 255) / 256 < 592 ? (total + 255) / 256 : 592);
+    pack_weights_kernel<<<blocks, 256, 0, s>>>(Wp, Bp, desc->d, desc->n_hidden, desc->width, wp,
+                                               reinterpret_cast<float*>(ws + w.wt_fwd), reinterpret_cast<float*>(ws + w.w_bwd),
+                                               reinterpret_cast<float*>(ws + w.small),
+                                               with_acc ? reinterpret_cast<float*>(ws + w.small_acc) : nullptr);
+    return check_launch("pack_weights_kernel");
+}
+
+XForm make_xform(const gpe_xform* xf) {
+    XForm x;
+    for (int i = 0; i < 2; ++i) {
+        x.a[i] = xf ? xf->a[i] : 1.f;
+        x.b[i] = xf ? xf->b[i] : 0.f;
+    }
+    return x;
+}
+
+// ---------------------------------------------------------------- FFMA probe
+__global__ void __launch_bounds__(256) ffma_probe_kernel(int mode, int iters, float a, float b, float* sink) {
+    if (mode == 0) {
+        float acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = (float)(threadIdx.x + i);
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) acc[i] = fmaf(acc[i], a, b);
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s += acc[i];
+        if (s == 123.456f) sink[0] = s;
+    } else {
+        unsigned long long acc[8], av, bv;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(av) : "f"(a));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(bv) : "f"(b));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float lo = (float)(threadIdx.x + i), hi = lo + 0.5f;
+            asm("mov.b64 %0, {%1, %2};" : "=l"(acc[i]) : "f"(lo), "f"(hi));
+        }
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(acc[i]) : "l"(av), "l"(bv));
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float lo, hi;
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc[i]));
+            s += lo + hi;
+        }
+        if (s == 123.456f) sink[0] = s;
+    }
+}
+
+}  // namespace
+}  // namespace gpe
+
+using namespace gpe;
+
+extern "C" {
+
+const char* gpe_version(void) { return "gpe_b200 0.1 (sm_100a)"; }
+const char* gpe_last_error(void) { return g_err; }
+
+int gpe_workspace_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* fwd_bytes, size_t* bwd_bytes) {
+    JetPlan p;
+    int wp;
+    const int rc = get_plan(desc, &p, &wp);
+    if (rc) return rc;
+    if (n < 0) { set_error("negative n"); return -1; }
+    const WsLayout w = layout(desc, p, wp, n);
+    if (fwd_bytes) *fwd_bytes = w.total_fwd;
+    if (bwd_bytes) *bwd_bytes = w.total_bwd;
+    return 0;
+}
+
+int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                    const gpe_xform* xform, float* u, float* g, float* h, void* ws, size_t ws_bytes,
+                    gpe_stream_t stream) {
+    JetPlan p;
+    int wp;
+    int rc = get_plan(desc, &p, &wp);
+    if (rc) return rc;
+    if (n < 0) { set_error("negative n"); return -1; }
+    if (n == 0) return 0;
+    if (!W || !b || !x || !u || !ws) { set_error("null pointer argument"); return -1; }
+    if (desc->jet != GPE_JET_VALUE && (!g || !h)) { set_error("g and h outputs required for derivative jets"); return -1; }
+    if (xform && desc->jet != GPE_JET_VALUE) { set_error("xform is only valid with GPE_JET_VALUE"); return -1; }
+    const WsLayout w = layout(desc, p, wp, n);
+    if (ws_bytes < w.total_fwd) { set_error("workspace too small: %zu < %zu", ws_bytes, w.total_fwd); return -1; }
+    char* base = static_cast<char*>(ws);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if ((rc = pack(desc, wp, w, W, b, base, false, s))) return rc;
+    MlpParams P{desc->n_hidden, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd),
+                reinterpret_cast<float*>(base + w.w_bwd), reinterpret_cast<float*>(base + w.small)};
+    const XForm xf = make_xform(xform);
+    rc = wp == 64 ? launch_fwd_wp64(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s)
+                  : launch_fwd_wp128(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s);
+    if (rc) return rc;
+    return check_launch("jet_fwd_kernel");
+}
+
+int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                    const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar,
+                    float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream) {
+    JetPlan p;
+    int wp;
+    int rc = get_plan(desc, &p, &wp);
+    if (rc) return rc;
+    if (n < 0) { set_error("negative n"); return -1; }
+    if (!W || !b || !dW || !db || !ws || (n > 0 && !x)) { set_error("null pointer argument"); return -1; }
+    if (xform && desc->jet != GPE_JET_VALUE) { set_error("xform is only valid with GPE_JET_VALUE"); return -1; }
+    const WsLayout w = layout(desc, p, wp, n);
+    if (ws_bytes < w.total_bwd) { set_error("workspace too small: %zu < %zu", ws_bytes, w.total_bwd); return -1; }
+    char* base = static_cast<char*>(ws);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if ((rc = pack(desc, wp, w, W, b, base, true, s))) return rc;
+    const int L = desc->n_hidden;
+    const size_t mat = (size_t)(L - 1) * wp * wp * sizeof(float);
+    if (mat) {
+        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (size_t)w.grid_bwd * mat, s);
+        if (e != cudaSuccess) { set_error("memset: %s", cudaGetErrorString(e)); return -4; }
+    }
+    MlpParams P{L, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd), reinterpret_cast<float*>(base + w.w_bwd),
+                reinterpret_cast<float*>(base + w.small)};
+    const XForm xf = make_xform(xform);
+    if (n > 0) {
+        rc = wp == 64 ? launch_bwd_wp64(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, reinterpret_cast<float*>(base + w.stash),
+                                        reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc),
+                                        w.grid_bwd, w.tiles, s)
+                      : launch_bwd_wp128(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, reinterpret_cast<float*>(base + w.stash),
+                                         reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc),
+                                         w.grid_bwd, w.tiles, s);
+        if (rc) return rc;
+        if ((rc = check_launch("jet_bwd_kernel"))) return rc;
+    }
+    MutPtrArray dWp{}, dBp{};
+    for (int l = 0; l <= L; ++l) {
+        if (!dW[l] || !db[l]) { set_error("null gradient pointer at layer %d", l); return -1; }
+        dWp.p[l] = dW[l];
+        dBp.p[l] = db[l];
+    }
+    const long long total = (long long)(L - 1) * desc->width * desc->width + (long long)desc->width * (desc->d + L + 1) + 1;
+    const int blocks = (int)((total + 255) / 256);
+    finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc), n > 0 ? w.grid_bwd : 0,
+                                               reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
+    return check_launch("finish_grads_kernel");
+}
+
+int gpe_ffma_probe(int mode, int iters, float* sink, double* flops, gpe_stream_t stream) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device"); return -2; }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = sms * 8;
+    ffma_probe_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(mode, iters, 1.0000001f, 1e-7f, sink);
+    if (flops) *flops = (double)grid * 256.0 * (double)iters * 16.0 * 2.0;
+    return check_launch("ffma_probe_kernel");
+}
+
+}  // extern "C"

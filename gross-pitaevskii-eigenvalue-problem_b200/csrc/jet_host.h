@@ -1,0 +1,39 @@
+// Host-side declarations shared by the per-width launch units and the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+#include "jet_common.cuh"
+
+namespace gpe {
+
+struct PtrArray {
+    const float* p[kMaxLayers + 1];
+};
+struct MutPtrArray {
+    float* p[kMaxLayers + 1];
+};
+
+struct JetPlan {          // resolved launch geometry for (d, jet, WP, L)
+    int pts_per_tile;
+    int rows_per_tile;
+    size_t smem_fwd, smem_bwd;
+    size_t stash_floats_per_cta;
+    int max_ctas_fwd, max_ctas_bwd;   // persistent grid bound (SMs x occupancy)
+};
+
+// implemented once per padded width (jet_launch.cu compiled with -DGPE_WP=...)
+#define GPE_DECL_WP(WP)                                                                                          \
+    int plan_wp##WP(int d, int jet, int L, JetPlan* plan);                                                       \
+    int launch_fwd_wp##WP(int d, int jet, const MlpParams& P, const float* x, long long n, const XForm& xf,      \
+                          float* u, float* g, float* h, int grid, int num_tiles, cudaStream_t s);                \
+    int launch_bwd_wp##WP(int d, int jet, const MlpParams& P, const float* x, long long n, const XForm& xf,      \
+                          const float* ub, const float* gb, const float* hb, float* stash, float* dWacc,         \
+                          float* small_acc, int grid, int num_tiles, cudaStream_t s);
+GPE_DECL_WP(64)
+GPE_DECL_WP(128)
+#undef GPE_DECL_WP
+
+void set_error(const char* fmt, ...);
+
+}  // namespace gpe

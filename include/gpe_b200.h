@@ -1,0 +1,97 @@
+/* gpe_b200 -- C ABI of the fused B200 (sm_100a) PINN train-step kernels.
+ *
+ * Drop-in boundary for the hot path of LevBahn/Gross-Pitaevskii-Eigenvalue-problem.  The reference
+ * has no FFI of its own: its boundary is the set of nn.Module methods below, and each entry
+ * point here replaces the PyTorch work those methods do (paths relative to /root/reference):
+ *
+ *   gpe_mlp_jet_fwd   <- nn.Sequential forward + the nested torch.autograd.grad derivatives
+ *                        Gross_Pitaevskii_1D_power_Test.ipynb cell 6:50-54, 6:90-104
+ *                        Gross-Pitaevskii/src/final/refine/harmonic_pinn_simulation.py:121-125, 158-172
+ *                        Gross-Pitaevskii/src/gross_pitaevskii_2D.py:67-81, 183-188
+ *                        Gross-Pitaevskii/src/helmholtz_2D.py:40-56, 75-83
+ *   gpe_mlp_jet_bwd   <- loss.backward() through that double-backward graph
+ *                        notebook cell 10:100, harmonic_pinn_simulation.py:358,
+ *                        gross_pitaevskii_2D.py:376,422, helmholtz_2D.py:418
+ *   gpe_loss_moments / gpe_loss_adjoints
+ *                     <- pde_loss / riesz_loss / normalization_loss / symmetry_loss / loss_pde
+ *                        notebook cell 6:81-162, harmonic_pinn_simulation.py:146-217,
+ *                        gross_pitaevskii_1D_Different_Optimizers.py:239-375,
+ *                        gross_pitaevskii_2D.py:112-213, helmholtz_2D.py:58-89
+ *
+ * Conventions: every pointer except the `W`/`b`/`dW`/`db` pointer ARRAYS (host arrays of device
+ * pointers) and the descriptor structs is a DEVICE pointer owned by the caller; fp32, contiguous.
+ * The library allocates nothing, keeps no mutable global state besides cached device
+ * attributes, never synchronises the host, and enqueues all work on `stream`.  Gradients are
+ * WRITTEN, not accumulated.  Return value 0 = success, negative = error (see gpe_last_error()).
+ * There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef GPE_B200_H
+#define GPE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* gpe_stream_t; /* == cudaStream_t */
+
+enum { GPE_ACT_TANH = 0, GPE_ACT_SHIFTED_TANH = 1, GPE_ACT_LEAKY_RELU = 2 };
+/* which derivatives travel with the value */
+enum {
+    GPE_JET_VALUE = 0,     /* u only                                   (boundary / mirror points)   */
+    GPE_JET_DIAG = 1,      /* u, du/dx_i, d2u/dx_i^2                    h is [N,d]                   */
+    GPE_JET_FULL = 2,      /* 2-D only: + d2u/dxdy                      h is [N,3] = (xx, yy, xy)    */
+    GPE_JET_LAPLACIAN = 3  /* u, du/dx_i, Laplacian (one fused stream)  h is [N,1]                   */
+};
+
+/* GPE_PREC_FP32: register-blocked FFMA (fp32 throughout).
+ * GPE_PREC_TF32X3: tcgen05 tensor cores, every fp32 operand split into hi+lo TF32 halves and
+ * three MMAs per product (hi*hi + hi*lo + lo*hi), fp32 accumulation in TMEM.
+ * GPE_PREC_AUTO: TF32X3 where a tensor-core kernel exists for the shape, else FP32. */
+enum { GPE_PREC_FP32 = 0, GPE_PREC_TF32X3 = 1, GPE_PREC_AUTO = 2 };
+
+typedef struct {
+    int d;        /* input dimension: 1 or 2                                     */
+    int n_hidden; /* L: number of hidden layers (>= 1, <= 8)                      */
+    int width;    /* W: hidden width, uniform, <= 128                             */
+    int act;      /* GPE_ACT_*                                                    */
+    int jet;      /* GPE_JET_*                                                    */
+    int precision; /* GPE_PREC_*: arithmetic of the hidden-layer contractions      */
+} gpe_mlp_desc;
+
+/* Optional affine map applied to the inputs before the network: x_eff = a*x + b per coordinate
+ * (mirror points of symmetry_loss: a=-1, b=lb+ub).  NULL = identity.  Only valid with
+ * GPE_JET_VALUE. */
+typedef struct {
+    float a[2], b[2];
+} gpe_xform;
+
+const char* gpe_version(void);
+const char* gpe_last_error(void); /* thread-local */
+
+/* Bytes of device workspace needed by the forward / reverse call for n points. */
+int gpe_workspace_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* fwd_bytes, size_t* bwd_bytes);
+
+/* W[0] [W,d], W[1..L-1] [W,W], W[L] [1,W]  (PyTorch [out,in] row-major); b[l] [W], b[L] [1].
+ * x [n,d].  Outputs: u [n]; g [n,d]; h [n,H] (H by jet kind); g,h may be NULL for JET_VALUE. */
+int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
+                    int64_t n, const gpe_xform* xform, float* u, float* g, float* h, void* ws, size_t ws_bytes,
+                    gpe_stream_t stream);
+
+/* Parameter gradient of  sum_n( u_bar[n] u + <g_bar[n], g> + <h_bar[n], h> ).  Any of
+ * u_bar/g_bar/h_bar may be NULL (= zeros).  dW[l], db[l] have the shapes of W[l], b[l]. */
+int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
+                    int64_t n, const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar,
+                    float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream);
+
+/* ---- FFMA peak probe (roofline denominator; MEASURED_PEAKS.json has no fp32 figure) ----
+ * Runs `iters` dependent-chain-free FFMA (mode 0) or packed FFMA2 (mode 1) per thread on a
+ * full grid; returns the number of fp32 FLOPs executed in *flops.  Time it with CUDA events. */
+int gpe_ffma_probe(int mode, int iters, float* sink, double* flops, gpe_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPE_B200_H */

@@ -7,6 +7,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+PKG = os.path.join(ROOT, "gross-pitaevskii-eigenvalue-problem_b200")
+if PKG not in sys.path:
+    sys.path.insert(0, PKG)
+
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 

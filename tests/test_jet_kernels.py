@@ -1,0 +1,136 @@
+"""GPU parity of the jet kernels (through the C ABI) against the nested-autograd fp64 oracle.
+
+Tolerance: the kernels compute in fp32; the oracle in fp64.  North-star bar: 1e-5 relative
+(L2 over the point set) for values/derivatives and for parameter gradients."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import jet_oracle as jo
+from helpers import rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def make_net(d, W, L, seed, act, gain=1.0):
+    g = torch.Generator().manual_seed(seed)
+    widths = [d] + [W] * L + [1]
+    Ws, bs = [], []
+    for i in range(len(widths) - 1):
+        fan_in, fan_out = widths[i], widths[i + 1]
+        bound = gain * (6.0 / (fan_in + fan_out)) ** 0.5
+        Ws.append((torch.rand((fan_out, fan_in), generator=g) * 2 - 1) * bound)
+        bs.append((torch.rand((fan_out,), generator=g) * 2 - 1) * 0.1)
+    return Ws, bs
+
+
+def points(n, d, seed, lo=-3.0, hi=3.0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.rand((n, d), generator=g) * (hi - lo) + lo
+
+
+def oracle_h(H, d, jet, ops):
+    if jet == ops.JET_DIAG:
+        return torch.stack([H[:, i, i] for i in range(d)], dim=1)
+    if jet == ops.JET_LAPLACIAN:
+        return sum(H[:, i, i] for i in range(d)).unsqueeze(1)
+    if jet == ops.JET_FULL:
+        return torch.stack([H[:, 0, 0], H[:, 1, 1], H[:, 0, 1]], dim=1) if d == 2 else H[:, 0, 0].unsqueeze(1)
+    return H[:, :0, 0]
+
+
+def hbar_full(h_bar, d, jet, ops):
+    """kernel-layout adjoint [N,H] -> oracle [N,d,d] weights on the full Hessian."""
+    n = h_bar.shape[0]
+    out = torch.zeros((n, d, d), dtype=torch.float64)
+    if jet == ops.JET_DIAG:
+        for i in range(d):
+            out[:, i, i] = h_bar[:, i]
+    elif jet == ops.JET_LAPLACIAN:
+        for i in range(d):
+            out[:, i, i] = h_bar[:, 0]
+    elif jet == ops.JET_FULL:
+        if d == 2:
+            out[:, 0, 0], out[:, 1, 1], out[:, 0, 1] = h_bar[:, 0], h_bar[:, 1], h_bar[:, 2]
+        else:
+            out[:, 0, 0] = h_bar[:, 0]
+    return out
+
+
+CASES = [
+    # d, W, L, act, jet, n
+    (1, 64, 3, 0, 1, 1000),
+    (1, 100, 3, 0, 1, 777),
+    (1, 128, 4, 0, 1, 2049),
+    (1, 64, 3, 1, 1, 4000),
+    (1, 128, 4, 0, 0, 513),
+    (2, 100, 3, 0, 3, 1500),
+    (2, 128, 4, 0, 3, 3000),
+    (2, 128, 4, 0, 1, 640),
+    (2, 128, 2, 0, 2, 999),
+    (2, 100, 3, 2, 3, 800),
+    (2, 64, 1, 0, 3, 100),
+    (2, 50, 5, 0, 0, 31),
+    (1, 8, 2, 0, 1, 1),
+]
+
+
+@pytest.mark.parametrize("d,W,L,act,jet,n", CASES)
+def test_jet_fwd(d, W, L, act, jet, n):
+    from gpe_b200 import ops
+    Ws, bs = make_net(d, W, L, seed=7 + W + L, act=act)
+    x = points(n, d, seed=n)
+    u, g, h = ops.mlp_jet_fwd(x.cuda(), [w.cuda() for w in Ws], [b.cuda() for b in bs], act, jet)
+    torch.cuda.synchronize()
+    ur, gr, Hr = jo.jets(x, Ws, bs, act)
+    assert rel_err(u.cpu(), ur) < TOL
+    if jet != ops.JET_VALUE:
+        assert rel_err(g.cpu(), gr) < TOL
+        assert rel_err(h.cpu(), oracle_h(Hr, d, jet, ops)) < TOL
+
+
+@pytest.mark.parametrize("d,W,L,act,jet,n", CASES)
+def test_jet_bwd(d, W, L, act, jet, n):
+    from gpe_b200 import ops
+    Ws, bs = make_net(d, W, L, seed=11 + W + L, act=act)
+    x = points(n, d, seed=n + 1)
+    gen = torch.Generator().manual_seed(99)
+    H = ops.jet_hess(d, jet)
+    u_bar = torch.randn(n, generator=gen)
+    g_bar = torch.randn((n, d), generator=gen) if jet != ops.JET_VALUE else None
+    h_bar = torch.randn((n, H), generator=gen) if H else None
+    dWs, dbs = ops.mlp_jet_bwd(x.cuda(), [w.cuda() for w in Ws], [b.cuda() for b in bs], act, jet, u_bar.cuda(),
+                               None if g_bar is None else g_bar.cuda(), None if h_bar is None else h_bar.cuda())
+    torch.cuda.synchronize()
+    gb = torch.zeros((n, d)) if g_bar is None else g_bar
+    hb = torch.zeros((n, d, d), dtype=torch.float64) if h_bar is None else hbar_full(h_bar, d, jet, ops)
+    rW, rb = jo.jet_functional_param_grads(x, Ws, bs, act, u_bar, gb, hb)
+    got = np.concatenate([t.cpu().numpy().ravel() for t in dWs + dbs])
+    ref = np.concatenate([t.numpy().ravel() for t in rW + rb])
+    assert rel_err(got, ref) < TOL
+    for a, b in zip(dWs + dbs, rW + rb):   # per-tensor too (looser: small tensors, fp32 sums over n)
+        if float(b.norm()) > 1e-6:
+            assert rel_err(a.cpu(), b) < 5 * TOL
+
+
+def test_mirror_xform():
+    from gpe_b200 import ops
+    Ws, bs = make_net(1, 64, 3, seed=3, act=0)
+    x = points(500, 1, seed=5)
+    cW, cb = [w.cuda() for w in Ws], [b.cuda() for b in bs]
+    u, _, _ = ops.mlp_jet_fwd(x.cuda(), cW, cb, 0, ops.JET_VALUE, xform=([-1.0], [0.5]))
+    ur, _, _ = jo.jets(0.5 - x, Ws, bs, 0)
+    assert rel_err(u.cpu(), ur) < TOL
+
+
+def test_empty_and_errors():
+    from gpe_b200 import ops
+    Ws, bs = make_net(1, 64, 3, seed=3, act=0)
+    cW, cb = [w.cuda() for w in Ws], [b.cuda() for b in bs]
+    u, g, h = ops.mlp_jet_fwd(torch.empty((0, 1), device="cuda"), cW, cb, 0, ops.JET_DIAG)
+    assert u.shape == (0,) and g.shape == (0, 1)
+    with pytest.raises(RuntimeError):
+        ops.mlp_jet_fwd(torch.zeros((4, 1)), cW, cb, 0, ops.JET_DIAG)      # CPU tensor: no fallback
+    with pytest.raises(ValueError):
+        ops.mlp_jet_fwd(torch.zeros((4, 2), device="cuda"), cW, cb, 0, ops.JET_DIAG)
