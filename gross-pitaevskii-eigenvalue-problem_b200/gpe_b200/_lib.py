@@ -13,12 +13,27 @@ LIB_PATH = os.path.join(_HERE, "libgpe_b200.so")
 ACT_TANH, ACT_SHIFTED_TANH, ACT_LEAKY_RELU = 0, 1, 2
 JET_VALUE, JET_DIAG, JET_FULL, JET_LAPLACIAN = 0, 1, 2, 3
 MAX_LAYERS = 8
+NFEAT, NMOM, MOM_GRAD2, MOM_NN2, MOM_SYM2 = 7, 32, 28, 29, 30
+F_ONE, F_U, F_LAP, F_V, F_VU, F_NL, F_Q = range(7)
+NL_NONE, NL_POW, NL_ABSPOW = 0, 1, 2
+
+
+def mom(i, j):
+    """Index of sum_n f_i f_j in the moment vector (row-major upper triangle of the 7x7 Gram matrix)."""
+    a, b = (i, j) if i <= j else (j, i)
+    return a * NFEAT - a * (a - 1) // 2 + (b - a)
 
 
 class MlpDesc(ctypes.Structure):
     """gpe_mlp_desc (include/gpe_b200.h)."""
     _fields_ = [("d", ctypes.c_int), ("n_hidden", ctypes.c_int), ("width", ctypes.c_int),
                 ("act", ctypes.c_int), ("jet", ctypes.c_int), ("precision", ctypes.c_int)]
+
+
+class LossDesc(ctypes.Structure):
+    """gpe_loss_desc (include/gpe_b200.h)."""
+    _fields_ = [("d", ctypes.c_int), ("nl_kind", ctypes.c_int), ("nl_power", ctypes.c_float), ("scale", ctypes.c_float),
+                ("bfactor", ctypes.c_int), ("sym_sign", ctypes.c_int), ("h_cols", ctypes.c_int), ("lap_cols", ctypes.c_int)]
 
 
 class XForm(ctypes.Structure):
@@ -46,8 +61,13 @@ lib.gpe_last_error.restype = ctypes.c_char_p
 lib.gpe_workspace_bytes.argtypes = [_desc_p, _i64, ctypes.POINTER(_sz), ctypes.POINTER(_sz)]
 lib.gpe_mlp_jet_fwd.argtypes = [_desc_p, _pp, _pp, _vp, _i64, _xf_p, _vp, _vp, _vp, _vp, _sz, _vp]
 lib.gpe_mlp_jet_bwd.argtypes = [_desc_p, _pp, _pp, _vp, _i64, _xf_p, _vp, _vp, _vp, _pp, _pp, _vp, _sz, _vp]
+_loss_p = ctypes.POINTER(LossDesc)
+lib.gpe_gram_moments.argtypes = [_loss_p, _i64] + [_vp] * 8 + [_vp, _vp]
+lib.gpe_gram_adjoints.argtypes = [_loss_p, _i64] + [_vp] * 8 + [_vp] + [_vp] * 4 + [_vp]
 lib.gpe_ffma_probe.argtypes = [ctypes.c_int, ctypes.c_int, _vp, ctypes.POINTER(ctypes.c_double), _vp]
-for _f in ("gpe_workspace_bytes", "gpe_mlp_jet_fwd", "gpe_mlp_jet_bwd", "gpe_ffma_probe"):
+EXPORTS = ("gpe_version", "gpe_last_error", "gpe_workspace_bytes", "gpe_mlp_jet_fwd", "gpe_mlp_jet_bwd",
+           "gpe_gram_moments", "gpe_gram_adjoints", "gpe_ffma_probe")
+for _f in EXPORTS[2:]:
     getattr(lib, _f).restype = ctypes.c_int
 
 

@@ -12,7 +12,7 @@
  *   gpe_mlp_jet_bwd   <- loss.backward() through that double-backward graph
  *                        notebook cell 10:100, harmonic_pinn_simulation.py:358,
  *                        gross_pitaevskii_2D.py:376,422, helmholtz_2D.py:418
- *   gpe_loss_moments / gpe_loss_adjoints
+ *   gpe_gram_moments / gpe_gram_adjoints
  *                     <- pde_loss / riesz_loss / normalization_loss / symmetry_loss / loss_pde
  *                        notebook cell 6:81-162, harmonic_pinn_simulation.py:146-217,
  *                        gross_pitaevskii_1D_Different_Optimizers.py:239-375,
@@ -85,6 +85,44 @@ int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float
 int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
                     int64_t n, const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar,
                     float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream);
+
+/* ---- fused loss epilogue ------------------------------------------------------------------
+ * Full solution per point (1-D factor forms follow R/box_pinn_simulation.py:119-180):
+ *     u   = base0 + s * F(x) * N
+ *     u_i = base_i + s * (F N_i + F' N)          lap u = base_lap + s * (F lap N + 2 F' N_x + F'' N)
+ * with N, N_i, lap N the network jets from gpe_mlp_jet_fwd (lap N = sum of the first `lap_cols`
+ * columns of h), F = 1 or sin(pi x), `base` = caller-supplied [n, 2+d] array (value, grad, laplacian)
+ * or NULL.  Features f = [1, u, lap u, V, V u, nl(u), q]; moments m[k(i,j)] = sum_n f_i f_j for
+ * i <= j (row-major upper triangle, 28 entries), then m[28] = sum |grad u|^2, m[29] = sum N^2,
+ * m[30] = sum (N - sym_sign * N_mirror)^2, m[31] unused.  All sums in fp64, ADDED into m
+ * (the caller zeroes m; partial sums of several shards may share one buffer). */
+enum { GPE_NFEAT = 7, GPE_NMOM = 32, GPE_MOM_GRAD2 = 28, GPE_MOM_NN2 = 29, GPE_MOM_SYM2 = 30 };
+enum { GPE_F_ONE = 0, GPE_F_U = 1, GPE_F_LAP = 2, GPE_F_V = 3, GPE_F_VU = 4, GPE_F_NL = 5, GPE_F_Q = 6 };
+enum { GPE_NL_NONE = 0, GPE_NL_POW = 1 /* u**p, integer p */, GPE_NL_ABSPOW = 2 /* |u|^(p-1) u */ };
+
+typedef struct {
+    int d;          /* 1 or 2                                                              */
+    int nl_kind;    /* GPE_NL_*                                                            */
+    float nl_power; /* p                                                                   */
+    float scale;    /* s                                                                   */
+    int bfactor;    /* 0: F = 1;  1: F = sin(pi x) (d = 1 only)                            */
+    int sym_sign;   /* 0: no mirror stream; +1: (N - N_mirror)^2; -1: (N + N_mirror)^2     */
+    int h_cols;     /* columns of h (0..3)                                                 */
+    int lap_cols;   /* the first lap_cols columns of h sum to the Laplacian                */
+} gpe_loss_desc;
+
+/* x [n,d] (needed only with bfactor), u [n], g [n,d] or NULL, h [n,h_cols] or NULL, base [n,2+d] or
+ * NULL, V [n] or NULL (=0), q [n] or NULL (=0), nm [n] (network value at the mirror point) or NULL. */
+int gpe_gram_moments(const gpe_loss_desc* desc, int64_t n, const float* x, const float* u, const float* g,
+                     const float* h, const float* base, const float* V, const float* q, const float* nm,
+                     double* m, gpe_stream_t stream);
+
+/* Given c[k] = dL/dm[k] (fp64, device), writes the adjoints of the NETWORK jets:
+ * u_bar [n], g_bar [n,d], h_bar [n,h_cols], nm_bar [n]  (each required iff its forward input was given). */
+int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, const float* u, const float* g,
+                      const float* h, const float* base, const float* V, const float* q, const float* nm,
+                      const double* c, float* u_bar, float* g_bar, float* h_bar, float* nm_bar,
+                      gpe_stream_t stream);
 
 /* ---- FFMA peak probe (roofline denominator; MEASURED_PEAKS.json has no fp32 figure) ----
  * Runs `iters` dependent-chain-free FFMA (mode 0) or packed FFMA2 (mode 1) per thread on a

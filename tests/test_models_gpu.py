@@ -1,0 +1,221 @@
+"""GPU parity of the drop-in modules (gpe_b200.models) against the golden vectors of the REAL reference
+classes (tests/golden/*.npz, float64 runs) and against the oracle run on the same inputs.
+
+The loop bodies are the oracle's own (`root_train_terms`, `final_train_terms`, ...): they only use the
+reference method names, so the same function drives the oracle class on the CPU and the B200 class on
+the GPU.  Tolerances (north-star): loss terms and parameter gradients 1e-5 relative in fp32 -- measured
+here against the float64 goldens, so the bound includes the kernels' own fp32 rounding."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import pinn_oracle as po
+from helpers import load_weights, golden_grads, flat, rel_err, model_grads
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+GTOL = 2e-5
+
+
+def close(a, b, tol=TOL):
+    a, b = float(a), float(b)
+    return abs(a - b) <= tol * max(abs(b), 1e-30)
+
+
+def cuda_model(cls, gold, *args, prefix="w.", **kw):
+    return load_weights(cls(*args, **kw), gold, prefix=prefix).cuda()
+
+
+@pytest.mark.parametrize("name", ["root_m0_p2", "root_m1_p3", "root_m2_p3"])
+def test_root(golden, name):
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.RootGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
+                       power=int(g["p"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    total, pde, bc, nrm, sym, mu = po.root_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                       float(g["gamma"]), int(g["p"]), lb, ub)
+    for key, val in dict(pde=pde, bc=bc, norm=nrm, sym=sym, total=total, mu=mu).items():
+        assert close(val, g[f"f64.{key}"]), (key, float(val), float(g[f"f64.{key}"]))
+    _, res, _, full = model.pde_loss(int(g["p"]), X, model.forward(X), float(g["gamma"]))
+    assert rel_err(full.detach().cpu().numpy().ravel(), g["f64.u"]) < TOL
+    assert rel_err(res.detach().cpu().numpy().ravel(), g["f64.residual"]) < 5 * TOL
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
+
+
+@pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
+                                       ("final_box_g10_p3_m0", "box")])
+def test_final_random(golden, name, kind):
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.FinalGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
+                       potential=kind)
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                   float(g["gamma"]), int(g["p"]), float(g["perturb_const"]), float(g["const"]))
+    for key, val in dict(pde=pde, total=total, mu=mu).items():
+        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+    # (sum u^2 dx - 1)^2 of a nearly normalised state: squares an O(1e-4) fp32 difference
+    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
+    assert abs(float(bc) - float(g["f64.bc"])) <= 2 * TOL * abs(float(g["f64.bc"])) + 1e-12
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
+
+
+@pytest.mark.parametrize("kind", ["harmonic", "box"])
+def test_final_fixture_mu_table(golden, kind):
+    """Shipped trained weights: the fused path must reproduce the pickled mu_table;
+    converged mu within 1e-4 (north-star) -- in fact ~1e-6."""
+    import gpe_b200
+    g = golden(f"final_{kind}_fixture")
+    lb, ub = float(g["lb"]), float(g["ub"])
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    for mode in range(6):
+        model = cuda_model(gpe_b200.FinalGPE1D, g, [int(v) for v in g[f"m{mode}.layers"]], prefix=f"m{mode}.w.", mode=mode,
+                           gamma=0.0, potential=kind)
+        total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                       0.0, 3, 0.01, float(g[f"m{mode}.const"]))
+        assert abs(float(mu) - float(g[f"m{mode}.mu_table"])) < 2e-5 * abs(float(g[f"m{mode}.mu_table"])), mode
+        assert abs(float(mu) - float(g[f"m{mode}.f64.mu"])) < 2e-5 * abs(float(g[f"m{mode}.f64.mu"])), mode
+        # converged losses are ~1e-6 differences of O(1) numbers: fp32 agreement is loose by nature
+        for key, val in dict(pde=pde, total=total).items():
+            ref = float(g[f"m{mode}.f64.{key}"])
+            assert abs(float(val) - ref) <= 0.3 * abs(ref) + 1e-9, (mode, key, float(val), ref)
+
+
+@pytest.mark.parametrize("name", ["opt_m0_eta10", "opt_m1_eta50"])
+def test_opt(golden, name):
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.OptGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = torch.tensor(float(g["lb"])), torch.tensor(float(g["ub"]))
+    bp = torch.stack([lb, ub]).reshape(2, 1).cuda()
+    w = [float(v) for v in g["weights"]]
+    total, data, riesz, pde, norm = model.total_loss(X, bp, torch.zeros((2, 1), device="cuda"), float(g["eta"]), lb, ub, w, "harmonic")
+    five = model.last_weighted_sum
+    sym = model.symmetry_loss(X, lb, ub)
+    _, res, mu = model.pde_loss(X, model.forward(X), float(g["eta"]), "harmonic")
+    assert tuple(res.shape) == (X.shape[0], 1)
+    for key, val in dict(total=total, data=data, riesz=riesz, pde=pde, norm=norm, sym=sym, mu=mu, five=five).items():
+        assert close(val, g[f"f64.{key}"]), (key, float(val), float(g[f"f64.{key}"]))
+    assert rel_err(flat(model_grads(model, five)), flat(golden_grads(g, "f64.grads_five"))) < GTOL
+    total2 = model.total_loss(X, bp, torch.zeros((2, 1), device="cuda"), float(g["eta"]), lb, ub, w, "harmonic")[0]
+    assert rel_err(flat(model_grads(model, total2)), flat(golden_grads(g, "f64.grads"))) < GTOL
+
+
+@pytest.mark.parametrize("name", ["g2d_g100", "g2d_g1_w128"])
+def test_g2d_reference_semantics(golden, name):
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.GPE2D, g, [int(v) for v in g["layers"]], g=float(g["g"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    total = model.loss(X, xb, None)
+    pde, res, mu = model.pde_loss(X, model.forward(X))
+    assert tuple(res.shape) == tuple(int(v) for v in g["f64.res_shape"])       # the [N,N] broadcast
+    for key, val in dict(total=total, pde=pde, mu=mu, bc=model.boundary_loss(xb, None),
+                         riesz=model.riesz_loss(model.forward(X), X)).items():
+        assert close(val, g[f"f64.{key}"]), (key, float(val), float(g[f"f64.{key}"]))
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
+
+
+def test_g2d_pointwise_vs_oracle(golden):
+    import gpe_b200
+    g = golden("g2d_g1_w128")
+    layers = [int(v) for v in g["layers"]]
+    ref = load_weights(po.GPE2D(layers, g=float(g["g"]), potential="harmonic"), g).double()
+    model = cuda_model(gpe_b200.GPE2D, g, layers, g=float(g["g"]), potential="harmonic", semantics="pointwise")
+    Xr = torch.tensor(g["X"], dtype=torch.float64, requires_grad=True)
+    total_r, bc_r, pde_r, riesz_r, mu_r = po.gpe2d_pointwise_terms(ref, Xr, torch.tensor(g["Xb"], dtype=torch.float64))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    total = model.loss(X, xb, None)
+    pde, res, mu = model.pde_loss(X, model.forward(X))
+    assert tuple(res.shape) == (X.shape[0], 1)
+    for a, b in ((total, total_r), (pde, pde_r), (mu, mu_r)):
+        assert close(a, b), (float(a), float(b))
+    assert rel_err(flat(model_grads(model, total)), flat(model_grads(ref, total_r))) < GTOL
+
+
+@pytest.mark.parametrize("name", ["helmholtz_leaky", "helmholtz_tanh"])
+def test_helmholtz(golden, name):
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.Helmholtz2D, g, [int(v) for v in g["layers"]], activation=str(g["act"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda")
+    xb, ub = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda"), torch.tensor(g["ub"], dtype=torch.float32, device="cuda")
+    k = float(g["k"])
+    total = model.compute_loss(X, xb, ub, k)
+    for key, val in dict(pde=model.loss_pde(X, k), data=model.loss_data(xb, ub), total=total).items():
+        assert close(val, g[f"f64.{key}"]), (key, float(val), float(g[f"f64.{key}"]))
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
+    # pointwise semantics against the oracle's intended-maths method
+    ref = load_weights(po.Helmholtz2D([int(v) for v in g["layers"]], activation=str(g["act"])), g).double()
+    model.semantics = "pointwise"
+    assert close(model.loss_pde(X, k), ref.loss_pde_pointwise(torch.tensor(g["X"], dtype=torch.float64), k))
+
+
+# ------------------------------------------------------------------------------------------------
+# compat path: the ORACLE's (= reference's) own loss code, nested autograd.grad included, on top of
+# the jet node -- only forward() is rerouted (gpe_b200.models.patch)
+# ------------------------------------------------------------------------------------------------
+def test_compat_root(golden):
+    from gpe_b200.models import patch
+    g = golden("root_m1_p3")
+    model = patch(load_weights(po.RootGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
+                                            power=int(g["p"])), g).cuda())
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    total, pde, bc, nrm, sym, mu = po.root_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                       float(g["gamma"]), int(g["p"]), lb, ub)
+    for key, val in dict(pde=pde, bc=bc, norm=nrm, sym=sym, total=total, mu=mu).items():
+        assert close(val, g[f"f64.{key}"], 2e-5), (key, float(val), float(g[f"f64.{key}"]))
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+
+
+def test_compat_g2d_and_helmholtz(golden):
+    from gpe_b200.models import patch
+    g = golden("g2d_g100")
+    model = patch(load_weights(po.GPE2D([int(v) for v in g["layers"]], g=float(g["g"])), g).cuda())
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    total = model.loss(X, xb, None)
+    assert close(total, g["f64.total"], 2e-5)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+    g = golden("helmholtz_tanh")
+    model = patch(load_weights(po.Helmholtz2D([int(v) for v in g["layers"]], activation="tanh"), g).cuda())
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda")
+    xb, ub = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda"), torch.tensor(g["ub"], dtype=torch.float32, device="cuda")
+    total = model.compute_loss(X, xb, ub, float(g["k"]))
+    assert close(total, g["f64.total"], 2e-5)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+
+
+def test_reverse_kernel_runs_once_per_step(golden):
+    """The C++ node must not run the parameter-reverse kernel during the nested autograd.grad(u, x)
+    visits (SURVEY 8b-A note ii): count launches through the profiler-free route of a call counter."""
+    import gpe_b200
+    from gpe_b200.models import patch
+    g = golden("root_m0_p2")
+    model = patch(load_weights(po.RootGPE1D([int(v) for v in g["layers"]], mode=0, gamma=1.0, power=2), g).cuda())
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA, torch.profiler.ProfilerActivity.CPU]) as prof:
+        pde, _, _, _ = model.pde_loss(2, X, model.forward(X), 1.0)
+        pde.backward()
+        torch.cuda.synchronize()
+    n_bwd = sum(1 for e in prof.events() if "jet_bwd_kernel" in e.name)
+    n_fwd = sum(1 for e in prof.events() if "jet_fwd_kernel" in e.name)
+    assert n_fwd == 1 and n_bwd == 1, (n_fwd, n_bwd)
+
+
+def test_cpu_tensor_raises():
+    import gpe_b200
+    model = gpe_b200.RootGPE1D([1, 16, 16, 1])
+    with pytest.raises(RuntimeError):
+        model.forward(torch.zeros(4, 1))
