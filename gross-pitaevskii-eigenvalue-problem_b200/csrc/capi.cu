@@ -2,6 +2,7 @@
 // device pointers out, everything enqueued on the caller's stream.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -133,8 +134,19 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
     return 0;
 }
 
+// GPE_TENSOR=0 forces the FFMA kernels (the tcgen05 path is the default where it applies)
+bool tc_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("GPE_TENSOR");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v != 0;
+}
+
 struct WsLayout {
-    size_t wt_fwd, w_bwd, small, small_acc, dWacc, stash, total_fwd, total_bwd;
+    size_t wt_fwd, w_bwd, small, wimg, small_acc, dWacc, stash, total_fwd, total_bwd;
+    bool tc;
     int n_small, grid_fwd, grid_bwd, tiles;
 };
 
@@ -153,6 +165,9 @@ WsLayout layout(const gpe_mlp_desc* desc, const JetPlan& p, int wp, long long n)
     w.wt_fwd = off; off = align_up(off + mat);
     w.w_bwd = off; off = align_up(off + mat);
     w.small = off; off = align_up(off + w.n_small * sizeof(float));
+    w.tc = tc_enabled() && tc_eligible(desc->d, desc->jet, desc->width, L);
+    w.wimg = off;
+    if (w.tc) off = align_up(off + tc_wimg_bytes(L));
     w.total_fwd = off;
     w.small_acc = off; off = align_up(off + w.n_small * sizeof(float));
     w.dWacc = off; off = align_up(off + (size_t)w.grid_bwd * mat);
@@ -273,6 +288,13 @@ int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float
     MlpParams P{desc->n_hidden, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd),
                 reinterpret_cast<float*>(base + w.w_bwd), reinterpret_cast<float*>(base + w.small)};
     const XForm xf = make_xform(xform);
+    if (w.tc) {
+        PtrArray Wp{};
+        for (int l = 0; l <= desc->n_hidden; ++l) Wp.p[l] = W[l];
+        float* wimg = reinterpret_cast<float*>(base + w.wimg);
+        if ((rc = tc_pack_wimg(Wp, desc->n_hidden, desc->width, 0, wimg, s))) return rc;
+        return launch_fwd_tc(desc->d, desc->n_hidden, desc->act, wimg, P.small, x, n, u, g, h, s);
+    }
     rc = wp == 64 ? launch_fwd_wp64(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s)
                   : launch_fwd_wp128(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s);
     if (rc) return rc;

@@ -36,4 +36,11 @@ GPE_DECL_WP(128)
 
 void set_error(const char* fmt, ...);
 
+// tensor-core (tcgen05) path, jet_launch_tc.cu
+bool tc_eligible(int d, int jet, int width, int L);
+size_t tc_wimg_bytes(int L);
+int tc_pack_wimg(const PtrArray& W, int L, int Wd, int transpose, float* wimg, cudaStream_t s);
+int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
+                  float* g, float* h, cudaStream_t s);
+
 }  // namespace gpe

@@ -1,0 +1,278 @@
+// Tensor-core (tcgen05 / TMEM) path of the Taylor-mode MLP -- sm_100a, hidden width padded to 128.
+//
+// Same mathematics as jet_fwd_kernel (jet_kernels.cuh): the nn.Sequential forward plus the nested
+// autograd.grad derivatives of the reference (S/gross_pitaevskii_2D.py:59-81,183-188; NBroot cell 6:30-54,
+// 90-104), but the per-layer contraction  [rows x 128] . W^T  runs on the 5th-gen tensor cores.
+//
+// Precision: every fp32 operand is split  v = hi + lo  (hi = RN to tf32, lo = v - hi) and the product is
+// formed as hi*hi + lo*hi + hi*lo with kind::tf32 MMAs accumulating in fp32 (3xTF32).  Measured on B200
+// (scripts/tc_probe): max error 1.6e-5 on |D| <= 15 over K = 128, i.e. fp32-GEMM class.
+//
+// Work decomposition: a CTA *pair* (cluster of 2, tcgen05 cta_group::2) owns 2 x 32 collocation points.
+//   rows of the M = 2 x 128 tile: TMEM lane 32q + 8s + p  <->  point 8q + p of the CTA, stream s
+//                                 (s = 0 value, 1..D first derivatives, D+1 trace of second derivatives)
+//   A operand (activations)     : TMEM, columns [0,128) hi and [128,256) lo, written by the epilogue warps
+//   B operand (weights)         : shared memory, resident for the whole kernel; each CTA holds the 64 output
+//                                 features of its half, hi and lo images in the SWIZZLE_NONE K-major
+//                                 canonical layout (8 x 16 B core matrices)
+//   D accumulators              : TMEM columns [256,384) and [384,512), alternating per layer
+// Epilogue threads use the 16x256b TMEM fragment (thread t: rows t/4 and t/4+8, two adjacent columns), so
+// with the lane map above one thread holds all streams of one point for two features: the activation jets
+// are thread-local, with no shuffles and no shared-memory staging.
+// The epilogue of layer l hands its output to the MMA of layer l+1 in 32-column chunks (mbarriers
+// a_ready[0..3]), so tensor work trails the activation work by one chunk.
+#pragma once
+#include "jet_common.cuh"
+#include "tc_tmem.cuh"
+
+namespace gpe {
+namespace tcp {
+
+constexpr int kEpiWarps = 8;                       // 2 per TMEM lane quadrant
+constexpr int kTcThreads = (kEpiWarps + 1) * 32;   // + MMA / control warp
+constexpr int kTcPts = 32;                         // points per CTA tile
+constexpr int kTcMaxMat = 3;                       // resident hidden matrices (64 KB each per CTA)
+constexpr uint32_t kColAHi = 0, kColALo = 128, kColD0 = 256;
+constexpr int kImgFloats = 64 * 128;               // one half-matrix image (hi or lo)
+
+struct TcParams {
+    int n_hidden;          // L
+    int act;
+    const float* wimg;     // [L-1][cta 2][hi,lo][kImgFloats]
+    const float* small;    // W0t[D][128], b[L][128], wout[128], bout[4]   (same pack as the FFMA path)
+};
+
+__host__ __device__ constexpr size_t tc_smem_bytes(int D, int L) {
+    return (size_t)(L - 1) * 2 * kImgFloats * 4 + ((size_t)(D + L + 1) * 128 + 4) * 4 + kEpiWarps * 32 * 4 * 4 + 128;
+}
+
+// byte offset of element (r, c) of a [rows x 128] matrix image: 8-row x 16-byte core matrices, cores of one
+// row group contiguous along c (LBO = 128 B), row groups 4096 B apart (SBO)
+__host__ __device__ __forceinline__ uint32_t img_off128(int r, int c) {
+    return (uint32_t)((r >> 3) * 4096 + (c >> 2) * 128 + (r & 7) * 16 + (c & 3) * 4);
+}
+
+__device__ __forceinline__ uint32_t tf32_hi(float v) {
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
+    return h;
+}
+
+// hidden weight images for the tensor path.  transpose = 0: B[n = out][k = in] (forward);
+// transpose = 1: B[n = in][k = out] (reverse sweep).  Zero padded to 128 x 128.
+__global__ void pack_wimg_kernel(PtrArray W, int L, int Wd, int transpose, float* __restrict__ wimg) {
+    const int total = (L - 1) * 128 * 128;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int l = idx / (128 * 128), rem = idx % (128 * 128);
+        const int nn = rem / 128, k = rem % 128;
+        const int o = transpose ? k : nn, i = transpose ? nn : k;
+        const float v = (o < Wd && i < Wd) ? W.p[l + 1][(size_t)o * Wd + i] : 0.f;
+        const float hi = __uint_as_float(tf32_hi(v));
+        float* base = wimg + ((size_t)l * 2 + (nn >> 6)) * 2 * kImgFloats;
+        const uint32_t off = img_off128(nn & 63, k) >> 2;
+        base[off] = hi;
+        base[kImgFloats + off] = v - hi;
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------
+// forward: u, grad u, Laplacian per point (JET_LAPLACIAN semantics; for D = 1 the trace is u_xx)
+// ------------------------------------------------------------------------------------------
+// split the 4 stream slots of one (point, feature) into the hi / lo fragment registers
+template <int R>
+__device__ __forceinline__ void put_slots(const float* a, int i, int e, uint32_t (&LoHi)[16], uint32_t (&HiHi)[16],
+                                          uint32_t (&LoLo)[16], uint32_t (&HiLo)[16]) {
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const float v = s < R ? a[s] : 0.f;
+        const uint32_t h = tf32_hi(v);
+        const uint32_t l = __float_as_uint(v - __uint_as_float(h));
+        const int r = 4 * i + 2 * (s & 1) + e;
+        if (s < 2) LoHi[r] = h, LoLo[r] = l;
+        else HiHi[r] = h, HiLo[r] = l;
+    }
+}
+
+template <int D>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
+jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* __restrict__ out_u, float* __restrict__ out_g,
+                  float* __restrict__ out_h, int num_pairs) {
+    using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
+    using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
+    using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
+    using tc::tmem_ld_16x256b_x4; using tc::tmem_st_16x256b_x4;
+    constexpr int R = D + 2;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int L = P.n_hidden, nmat = L - 1;
+    const int n_small = (D + L + 1) * 128 + 4;
+    float* wimg_s = reinterpret_cast<float*>(smem);
+    float* small = wimg_s + (size_t)nmat * 2 * kImgFloats;
+    float* comb = small + n_small;
+    uint64_t* a_ready = reinterpret_cast<uint64_t*>(comb + kEpiWarps * 32 * 4);
+    uint64_t* d_full = a_ready + 4;
+    uint64_t* w_full = d_full + 2;
+    uint32_t* tbase_s = reinterpret_cast<uint32_t*>(w_full + 1);
+
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const uint32_t cta = cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+    if (tid == 0) {
+        for (int c = 0; c < 4; ++c) mbar_init(&a_ready[c], 8);
+        mbar_init(&d_full[0], 1);
+        mbar_init(&d_full[1], 1);
+        mbar_init(w_full, 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(w_full, (uint32_t)nmat * 2 * kImgFloats * 4);
+        for (int l = 0; l < nmat; ++l)
+            for (int hl = 0; hl < 2; ++hl)
+                tma_bulk_g2s(wimg_s + ((size_t)l * 2 + hl) * kImgFloats, P.wimg + (((size_t)l * 2 + cta) * 2 + hl) * kImgFloats,
+                             kImgFloats * 4, w_full);
+        mbar_wait(w_full, 0);   // both halves must be resident before the leader's first MMA (cluster_sync below)
+    }
+    if (w == kEpiWarps) tmem_alloc<2>(tbase_s, 512);
+    for (int i = tid; i < n_small; i += kTcThreads) small[i] = P.small[i];
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();
+    tc_fence_after();
+    const uint32_t tb = *tbase_s;
+    const float* W0t = small;
+    const float* bias = small + D * 128;
+    const float* wout = small + (D + L) * 128;
+    const float bout = small[(D + L + 1) * 128];
+    const int act = P.act;
+
+    if (w < kEpiWarps) {
+        const int q = w & 3, half = w >> 2, pl = lane >> 2, tq = lane & 3;
+        const uint32_t lane_lo = tb + ((uint32_t)(32 * q) << 16), lane_hi = lane_lo + (16u << 16);
+        uint32_t dcnt[2] = {0u, 0u};
+        for (int it = 0;; ++it) {
+            const long long T = cluster_id + (long long)it * num_clusters;
+            if (T >= num_pairs) break;
+            const long long p = (T * 2 + cta) * kTcPts + 8 * q + pl;
+            const bool valid = p < n;
+            float xin[D];
+#pragma unroll
+            for (int i = 0; i < D; ++i) xin[i] = valid ? x[p * D + i] : 0.f;
+            float o[R];
+#pragma unroll
+            for (int s = 0; s < R; ++s) o[s] = 0.f;
+            for (int l = 0; l < L; ++l) {
+                const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
+                if (l > 0) {
+                    mbar_wait(&d_full[l & 1], dcnt[l & 1] & 1u);
+                    ++dcnt[l & 1];
+                    tc_fence_after();
+                }
+                const float* bl = bias + l * 128;
+#pragma unroll 1
+                for (int cc = 0; cc < 2; ++cc) {
+                    const int c = half + 2 * cc;
+                    uint32_t LoHi[16], HiHi[16], LoLo[16], HiLo[16];
+                    if (l > 0) {
+                        tmem_ld_16x256b_x4(lane_lo + dcol + 32 * c, LoHi);
+                        tmem_ld_16x256b_x4(lane_hi + dcol + 32 * c, HiHi);
+                        tmem_wait_ld();
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int f = 32 * c + 8 * i + 2 * tq + e;
+                            float z[R];
+                            if (l == 0) {
+                                float z0 = bl[f];
+#pragma unroll
+                                for (int k = 0; k < D; ++k) {
+                                    const float wk = W0t[k * 128 + f];
+                                    z0 = fmaf(wk, xin[k], z0);
+                                    z[1 + k] = wk;
+                                }
+                                z[0] = z0;
+                                z[1 + D] = 0.f;
+                            } else {
+#pragma unroll
+                                for (int s = 0; s < R; ++s) {
+                                    const int r = 4 * i + 2 * (s & 1) + e;
+                                    z[s] = __uint_as_float(s < 2 ? LoHi[r] : HiHi[r]);
+                                }
+                                z[0] += bl[f];
+                            }
+                            float st0;
+                            act_jet_fwd<D, JET_LAPLACIAN>(z, act, st0);
+                            if (l < L - 1) {
+                                put_slots<R>(z, i, e, LoHi, HiHi, LoLo, HiLo);
+                            } else {
+                                const float wo = wout[f];
+#pragma unroll
+                                for (int s = 0; s < R; ++s) o[s] = fmaf(wo, z[s], o[s]);
+                            }
+                        }
+                    if (l < L - 1) {
+                        tmem_st_16x256b_x4(lane_lo + kColAHi + 32 * c, LoHi);
+                        tmem_st_16x256b_x4(lane_hi + kColAHi + 32 * c, HiHi);
+                        tmem_st_16x256b_x4(lane_lo + kColALo + 32 * c, LoLo);
+                        tmem_st_16x256b_x4(lane_hi + kColALo + 32 * c, HiLo);
+                        tmem_wait_st();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
+                    }
+                }
+            }
+            // output layer: reduce over the 4 lanes of a point, then over the two warps of the quadrant
+#pragma unroll
+            for (int s = 0; s < R; ++s) {
+                o[s] += __shfl_xor_sync(0xffffffffu, o[s], 1);
+                o[s] += __shfl_xor_sync(0xffffffffu, o[s], 2);
+            }
+            if (tq == 0) {
+#pragma unroll
+                for (int s = 0; s < R; ++s) comb[(w * 8 + pl) * 4 + s] = o[s];
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+            if (half == 0 && tq == 0 && valid) {
+                const float* oc = comb + ((w + 4) * 8 + pl) * 4;
+                out_u[p] = o[0] + oc[0] + bout;
+#pragma unroll
+                for (int i = 0; i < D; ++i) out_g[p * D + i] = o[1 + i] + oc[1 + i];
+                out_h[p] = o[1 + D] + oc[1 + D];
+            }
+        }
+    } else if (cta == 0 && lane == 0) {
+        // ---- MMA issue thread (leader CTA) ----
+        constexpr uint32_t idesc = instr_desc(2, 256, 128, 0, 0);
+        const uint32_t wbase = smem_u32(wimg_s);
+        uint32_t acnt = 0;
+        for (int it = 0;; ++it) {
+            const long long T = cluster_id + (long long)it * num_clusters;
+            if (T >= num_pairs) break;
+            for (int l = 1; l < L; ++l, ++acnt) {
+                const uint32_t dcol = tb + kColD0 + 128u * (uint32_t)(l & 1);
+                const uint32_t bhi0 = wbase + (uint32_t)(l - 1) * 2 * kImgFloats * 4, blo0 = bhi0 + kImgFloats * 4;
+                for (int c = 0; c < 4; ++c) {
+                    mbar_wait_cluster(&a_ready[c], acnt & 1u);
+                    tc_fence_after();
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const int j = 4 * c + kk;
+                        const uint64_t bhi = smem_desc(bhi0 + j * 256, 128, 4096), blo = smem_desc(blo0 + j * 256, 128, 4096);
+                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
+                        mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, 1u);
+                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
+                    }
+                }
+                mma_commit_pair(&d_full[l & 1], 3);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();
+    if (w == kEpiWarps) tmem_dealloc<2>(tb, 512);
+}
+
+}  // namespace tcp
+}  // namespace gpe
