@@ -145,7 +145,7 @@ bool tc_enabled() {
 }
 
 struct WsLayout {
-    size_t wt_fwd, w_bwd, small, wimg, small_acc, dWacc, stash, total_fwd, total_bwd;
+    size_t wt_fwd, w_bwd, small, wimg, small_acc, dWacc, stash, wimg_rev, zb, total_fwd, total_bwd;
     bool tc;
     int n_small, grid_fwd, grid_bwd, tiles;
 };
@@ -170,8 +170,16 @@ WsLayout layout(const gpe_mlp_desc* desc, const JetPlan& p, int wp, long long n)
     if (w.tc) off = align_up(off + tc_wimg_bytes(L));
     w.total_fwd = off;
     w.small_acc = off; off = align_up(off + w.n_small * sizeof(float));
-    w.dWacc = off; off = align_up(off + (size_t)w.grid_bwd * mat);
-    w.stash = off; off = align_up(off + (size_t)w.grid_bwd * p.stash_floats_per_cta * sizeof(float));
+    w.wimg_rev = w.zb = 0;
+    if (w.tc) {   // tensor path: one global accumulator, chunked stash of forward jets and of their adjoints
+        w.dWacc = off; off = align_up(off + mat);
+        w.wimg_rev = off; off = align_up(off + tc_wimg_bytes(L));
+        w.stash = off; off = align_up(off + tc_stash_bytes(L, n));
+        w.zb = off; off = align_up(off + tc_zb_bytes(L, n));
+    } else {
+        w.dWacc = off; off = align_up(off + (size_t)w.grid_bwd * mat);
+        w.stash = off; off = align_up(off + (size_t)w.grid_bwd * p.stash_floats_per_cta * sizeof(float));
+    }
     w.total_bwd = off;
     return w;
 }
@@ -319,13 +327,24 @@ int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float
     const int L = desc->n_hidden;
     const size_t mat = (size_t)(L - 1) * wp * wp * sizeof(float);
     if (mat) {
-        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (size_t)w.grid_bwd * mat, s);
+        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (w.tc ? (size_t)1 : (size_t)w.grid_bwd) * mat, s);
         if (e != cudaSuccess) { set_error("memset: %s", cudaGetErrorString(e)); return -4; }
     }
     MlpParams P{L, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd), reinterpret_cast<float*>(base + w.w_bwd),
                 reinterpret_cast<float*>(base + w.small)};
     const XForm xf = make_xform(xform);
-    if (n > 0) {
+    if (n > 0 && w.tc) {
+        PtrArray Wp{};
+        for (int l = 0; l <= L; ++l) Wp.p[l] = W[l];
+        float* wimg_f = reinterpret_cast<float*>(base + w.wimg);
+        float* wimg_r = reinterpret_cast<float*>(base + w.wimg_rev);
+        if ((rc = tc_pack_wimg(Wp, L, desc->width, 0, wimg_f, s))) return rc;
+        if ((rc = tc_pack_wimg(Wp, L, desc->width, 1, wimg_r, s))) return rc;
+        rc = launch_bwd_tc(desc->d, L, desc->act, wimg_f, wimg_r, P.small, x, n, u_bar, g_bar, h_bar,
+                           reinterpret_cast<float*>(base + w.stash), reinterpret_cast<float*>(base + w.zb),
+                           reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc), s);
+        if (rc) return rc;
+    } else if (n > 0) {
         rc = wp == 64 ? launch_bwd_wp64(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, reinterpret_cast<float*>(base + w.stash),
                                         reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc),
                                         w.grid_bwd, w.tiles, s)
@@ -343,7 +362,7 @@ int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float
     }
     const long long total = (long long)(L - 1) * desc->width * desc->width + (long long)desc->width * (desc->d + L + 1) + 1;
     const int blocks = (int)((total + 255) / 256);
-    finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc), n > 0 ? w.grid_bwd : 0,
+    finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc), n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0,
                                                reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
     return check_launch("finish_grads_kernel");
 }

@@ -18,8 +18,8 @@ int tc_pack_wimg(const PtrArray& W, int L, int Wd, int transpose, float* wimg, c
     return 0;
 }
 
-template <int D>
-static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, cudaStream_t s) {
+template <int D, bool STASH>
+static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
     static int sms = 0;
     if (!sms) {
         int dev = 0;
@@ -27,21 +27,76 @@ static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u,
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
     const size_t smem = tcp::tc_smem_bytes(D, P.n_hidden);
-    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, STASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { set_error("tc fwd smem attr (%zu B): %s", smem, cudaGetErrorString(e)); return -3; }
     const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
     long long clusters = sms / 2;
     if (pairs < clusters) clusters = pairs;
-    tcp::jet_fwd_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, (int)pairs);
+    tcp::jet_fwd_tc_kernel<D, STASH><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (int)pairs);
     e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("jet_fwd_tc_kernel launch: %s (grid %lld, smem %zu)", cudaGetErrorString(e), 2 * clusters, smem); return -4; }
     return 0;
 }
 
+static int tc_sms() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    return sms;
+}
+
+template <int D>
+static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
+                  const float* hb, float* stash, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
+    const int sms = tc_sms(), L = Pf.n_hidden;
+    const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes(D, L);
+    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::jet_rev_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::dw_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dw);
+    if (e != cudaSuccess) { set_error("tc bwd smem attr: %s", cudaGetErrorString(e)); return -3; }
+    for (long long c0 = 0; c0 < n; c0 += chunk) {
+        const long long nc = n - c0 < chunk ? n - c0 : chunk;
+        const long long pairs = (nc + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
+        long long clusters = sms / 2;
+        if (pairs < clusters) clusters = pairs;
+        const float* xc = x + c0 * D;
+        tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, (int)pairs);
+        tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
+            Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, (int)pairs);
+        const long long blocks = (nc + tcp::kDwPts - 1) / tcp::kDwPts;
+        const int grid = (int)(blocks < sms ? blocks : sms);
+        tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(Pf, xc, nc, stash, zb, dWacc, small_acc, (int)blocks);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }
+    }
+    return 0;
+}
+
+// chunk of points processed per (stash forward, reverse sweep, dW contraction) round
+long long tc_bwd_chunk(long long n) {
+    const long long cap = 262144;
+    long long c = (n + 63) / 64 * 64;
+    return c < cap ? (c > 0 ? c : 64) : cap;
+}
+size_t tc_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
+size_t tc_zb_bytes(int L, long long n) { return (size_t)L * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
+
+int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
+                  long long n, const float* ub, const float* gb, const float* hb, float* stash, float* zb, float* dWacc,
+                  float* small_acc, cudaStream_t s) {
+    tcp::TcParams Pf{L, act, wimg_fwd, small}, Pr{L, act, wimg_rev, small};
+    const long long chunk = tc_bwd_chunk(n);
+    return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, zb, dWacc, small_acc, chunk, s)
+                  : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, zb, dWacc, small_acc, chunk, s);
+}
+
 int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
                   float* g, float* h, cudaStream_t s) {
     tcp::TcParams P{L, act, wimg, small};
-    return d == 1 ? fwd_tc<1>(P, x, n, u, g, h, s) : fwd_tc<2>(P, x, n, u, g, h, s);
+    return d == 1 ? fwd_tc<1, false>(P, x, n, u, g, h, nullptr, s) : fwd_tc<2, false>(P, x, n, u, g, h, nullptr, s);
 }
 
 }  // namespace gpe

@@ -94,10 +94,12 @@ __device__ __forceinline__ void put_slots(const float* a, int i, int e, uint32_t
     }
 }
 
-template <int D>
+// STASH: additionally write, for every hidden layer l >= 1, the pre-activation jets {tanh value | a0, z1.., z2}
+// to stash[l-1][point][stream][128] (what the reverse sweep and the dW contraction read back).
+template <int D, bool STASH>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* __restrict__ out_u, float* __restrict__ out_g,
-                  float* __restrict__ out_h, int num_pairs) {
+                  float* __restrict__ out_h, float* __restrict__ stash, int num_pairs) {
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
@@ -177,7 +179,8 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                         tmem_wait_ld();
                     }
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
+                    for (int i = 0; i < 4; ++i) {
+                        float sv[2][R];
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             const int f = 32 * c + 8 * i + 2 * tq + e;
@@ -200,8 +203,9 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                                 }
                                 z[0] += bl[f];
                             }
-                            float st0;
-                            act_jet_fwd<D, JET_LAPLACIAN>(z, act, st0);
+#pragma unroll
+                            for (int s = 1; s < R; ++s) sv[e][s] = z[s];
+                            act_jet_fwd<D, JET_LAPLACIAN>(z, act, sv[e][0]);
                             if (l < L - 1) {
                                 put_slots<R>(z, i, e, LoHi, HiHi, LoLo, HiLo);
                             } else {
@@ -210,6 +214,12 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                                 for (int s = 0; s < R; ++s) o[s] = fmaf(wo, z[s], o[s]);
                             }
                         }
+                        if (STASH && l > 0 && valid) {
+                            float* sp = stash + ((size_t)(l - 1) * n + p) * 512 + 32 * c + 8 * i + 2 * tq;
+#pragma unroll
+                            for (int s = 0; s < R; ++s) *reinterpret_cast<float2*>(sp + s * 128) = make_float2(sv[0][s], sv[1][s]);
+                        }
+                    }
                     if (l < L - 1) {
                         tmem_st_16x256b_x4(lane_lo + kColAHi + 32 * c, LoHi);
                         tmem_st_16x256b_x4(lane_hi + kColAHi + 32 * c, HiHi);
@@ -233,7 +243,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                 for (int s = 0; s < R; ++s) comb[(w * 8 + pl) * 4 + s] = o[s];
             }
             asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
-            if (half == 0 && tq == 0 && valid) {
+            if (half == 0 && tq == 0 && valid && out_u) {
                 const float* oc = comb + ((w + 4) * 8 + pl) * 4;
                 out_u[p] = o[0] + oc[0] + bout;
 #pragma unroll
@@ -272,6 +282,431 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
     __syncthreads();
     cluster_sync();
     if (w == kEpiWarps) tmem_dealloc<2>(tb, 512);
+}
+
+// ------------------------------------------------------------------------------------------
+// reverse sweep: given the adjoints (u_bar, g_bar, h_bar) of the per-point outputs and the stashed forward
+// jets, propagate  abar_{l-1} = zbar_l . W_l  down the layers on the tensor cores (B = images of W_l^T) and
+// write zbar_l (adjoint of the pre-activation jets, all streams) for every layer to zb[l][point][stream][128].
+// The weight gradients dW_l = zbar_l^T a_{l-1} are a contraction over points: dw_tc_kernel.
+// Also accumulates the output-layer gradient (dwout, dbout) into small_acc (layout of `small`).
+// ------------------------------------------------------------------------------------------
+template <int D>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
+jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ u_bar,
+                  const float* __restrict__ g_bar, const float* __restrict__ h_bar, const float* __restrict__ stash,
+                  float* __restrict__ zb, float* __restrict__ small_acc, int num_pairs) {
+    using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
+    using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
+    using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
+    using tc::tmem_ld_16x256b_x4; using tc::tmem_st_16x256b_x4;
+    constexpr int R = D + 2;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int L = P.n_hidden, nmat = L - 1;
+    const int n_small = (D + L + 1) * 128 + 4;
+    float* wimg_s = reinterpret_cast<float*>(smem);
+    float* small = wimg_s + (size_t)nmat * 2 * kImgFloats;
+    float* comb = small + n_small;
+    uint64_t* a_ready = reinterpret_cast<uint64_t*>(comb + kEpiWarps * 32 * 4);
+    uint64_t* d_full = a_ready + 4;
+    uint64_t* w_full = d_full + 2;
+    uint32_t* tbase_s = reinterpret_cast<uint32_t*>(w_full + 1);
+
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const uint32_t cta = cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+    if (tid == 0) {
+        for (int c = 0; c < 4; ++c) mbar_init(&a_ready[c], 8);
+        mbar_init(&d_full[0], 1);
+        mbar_init(&d_full[1], 1);
+        mbar_init(w_full, 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(w_full, (uint32_t)nmat * 2 * kImgFloats * 4);
+        for (int l = 0; l < nmat; ++l)
+            for (int hl = 0; hl < 2; ++hl)
+                tma_bulk_g2s(wimg_s + ((size_t)l * 2 + hl) * kImgFloats, P.wimg + (((size_t)l * 2 + cta) * 2 + hl) * kImgFloats,
+                             kImgFloats * 4, w_full);
+        mbar_wait(w_full, 0);
+    }
+    if (w == kEpiWarps) tmem_alloc<2>(tbase_s, 512);
+    for (int i = tid; i < n_small; i += kTcThreads) small[i] = P.small[i];
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();
+    tc_fence_after();
+    const uint32_t tb = *tbase_s;
+    const float* W0t = small;
+    const float* bias = small + D * 128;
+    const float* wout = small + (D + L) * 128;
+    const int act = P.act;
+
+    if (w < kEpiWarps) {
+        const int q = w & 3, half = w >> 2, pl = lane >> 2, tq = lane & 3;
+        const uint32_t lane_lo = tb + ((uint32_t)(32 * q) << 16), lane_hi = lane_lo + (16u << 16);
+        uint32_t dcnt[2] = {0u, 0u};
+        float dwout_acc[2][8];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 8; ++b) dwout_acc[a][b] = 0.f;
+        float dbout_acc = 0.f;
+        for (int it = 0;; ++it) {
+            const long long T = cluster_id + (long long)it * num_clusters;
+            if (T >= num_pairs) break;
+            const long long p = (T * 2 + cta) * kTcPts + 8 * q + pl;
+            const bool valid = p < n;
+            float xin[D], adj[R];
+#pragma unroll
+            for (int i = 0; i < D; ++i) xin[i] = valid ? x[p * D + i] : 0.f;
+            adj[0] = (valid && u_bar) ? u_bar[p] : 0.f;
+#pragma unroll
+            for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? g_bar[p * D + i] : 0.f;
+            adj[1 + D] = (valid && h_bar) ? h_bar[p] : 0.f;
+            if (half == 0 && tq == 0) dbout_acc += adj[0];
+            for (int l = L - 1; l >= 0; --l) {
+                const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
+                if (l < L - 1) {
+                    mbar_wait(&d_full[l & 1], dcnt[l & 1] & 1u);
+                    ++dcnt[l & 1];
+                    tc_fence_after();
+                }
+                const float* bl = bias + l * 128;
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc) {
+                    const int c = half + 2 * cc;
+                    uint32_t LoHi[16], HiHi[16], LoLo[16], HiLo[16];
+                    if (l < L - 1) {
+                        tmem_ld_16x256b_x4(lane_lo + dcol + 32 * c, LoHi);
+                        tmem_ld_16x256b_x4(lane_hi + dcol + 32 * c, HiHi);
+                        tmem_wait_ld();
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int f0 = 32 * c + 8 * i + 2 * tq;
+                        float stv[R][2];
+                        if (l > 0) {
+                            const float* sp = stash + ((size_t)(l - 1) * n + (valid ? p : 0)) * 512 + f0;
+#pragma unroll
+                            for (int s = 0; s < R; ++s) {
+                                const float2 v = *reinterpret_cast<const float2*>(sp + s * 128);
+                                stv[s][0] = v.x, stv[s][1] = v.y;
+                            }
+                        }
+                        float zbv[R][2];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int f = f0 + e;
+                            float st[R], ab[R];
+                            if (l > 0) {
+#pragma unroll
+                                for (int s = 0; s < R; ++s) st[s] = stv[s][e];
+                            } else {
+                                float zz[R];
+                                float z0 = bl[f];
+#pragma unroll
+                                for (int k = 0; k < D; ++k) {
+                                    const float wk = W0t[k * 128 + f];
+                                    z0 = fmaf(wk, xin[k], z0);
+                                    zz[1 + k] = wk;
+                                }
+                                zz[0] = z0;
+                                zz[1 + D] = 0.f;
+#pragma unroll
+                                for (int s = 1; s < R; ++s) st[s] = zz[s];
+                                act_jet_fwd<D, JET_LAPLACIAN>(zz, act, st[0]);
+                            }
+                            if (l < L - 1) {
+#pragma unroll
+                                for (int s = 0; s < R; ++s) {
+                                    const int r = 4 * i + 2 * (s & 1) + e;
+                                    ab[s] = __uint_as_float(s < 2 ? LoHi[r] : HiHi[r]);
+                                }
+                            } else {
+                                float a[R];
+                                act_jet_from_stash<D, JET_LAPLACIAN>(st, a, act);
+                                const float wo = wout[f];
+                                float dw = dwout_acc[cc][2 * i + e];
+#pragma unroll
+                                for (int s = 0; s < R; ++s) {
+                                    dw = fmaf(adj[s], a[s], dw);
+                                    ab[s] = adj[s] * wo;
+                                }
+                                dwout_acc[cc][2 * i + e] = dw;
+                            }
+                            act_jet_bwd<D, JET_LAPLACIAN>(st, ab, act);
+#pragma unroll
+                            for (int s = 0; s < R; ++s) zbv[s][e] = ab[s];
+                            if (l > 0) put_slots<R>(ab, i, e, LoHi, HiHi, LoLo, HiLo);
+                        }
+                        if (valid) {
+                            float* zp = zb + ((size_t)l * n + p) * 512 + f0;
+#pragma unroll
+                            for (int s = 0; s < R; ++s) *reinterpret_cast<float2*>(zp + s * 128) = make_float2(zbv[s][0], zbv[s][1]);
+                        }
+                    }
+                    if (l > 0) {
+                        tmem_st_16x256b_x4(lane_lo + kColAHi + 32 * c, LoHi);
+                        tmem_st_16x256b_x4(lane_hi + kColAHi + 32 * c, HiHi);
+                        tmem_st_16x256b_x4(lane_lo + kColALo + 32 * c, LoLo);
+                        tmem_st_16x256b_x4(lane_hi + kColALo + 32 * c, HiLo);
+                        tmem_wait_st();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
+                    }
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");   // all D reads of this tile done
+        }
+        // flush the output-layer gradient: sum over the 8 points of the warp, one atomic per feature
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float v = dwout_acc[cc][j];
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                if (pl == 0) atomicAdd(&small_acc[(D + L) * 128 + 32 * (half + 2 * cc) + 8 * (j >> 1) + 2 * tq + (j & 1)], v);
+            }
+        dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 4);
+        dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 8);
+        dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 16);
+        if (lane == 0 && half == 0) atomicAdd(&small_acc[(D + L + 1) * 128], dbout_acc);
+    } else if (cta == 0 && lane == 0) {
+        constexpr uint32_t idesc = instr_desc(2, 256, 128, 0, 0);
+        const uint32_t wbase = smem_u32(wimg_s);
+        uint32_t acnt = 0;
+        for (int it = 0;; ++it) {
+            const long long T = cluster_id + (long long)it * num_clusters;
+            if (T >= num_pairs) break;
+            for (int l = L - 1; l >= 1; --l, ++acnt) {
+                const uint32_t dcol = tb + kColD0 + 128u * (uint32_t)((l - 1) & 1);
+                const uint32_t bhi0 = wbase + (uint32_t)(l - 1) * 2 * kImgFloats * 4, blo0 = bhi0 + kImgFloats * 4;
+                for (int c = 0; c < 4; ++c) {
+                    mbar_wait_cluster(&a_ready[c], acnt & 1u);
+                    tc_fence_after();
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const int j = 4 * c + kk;
+                        const uint64_t bhi = smem_desc(bhi0 + j * 256, 128, 4096), blo = smem_desc(blo0 + j * 256, 128, 4096);
+                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
+                        mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, 1u);
+                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
+                    }
+                }
+                mma_commit_pair(&d_full[(l - 1) & 1], 3);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();
+    if (w == kEpiWarps) tmem_dealloc<2>(tb, 512);
+}
+
+// ------------------------------------------------------------------------------------------
+// weight gradients: for every hidden matrix l = 1..L-1
+//     dW_l[o][i] = sum_rows zbar_l[row][o] * a_{l-1}[row][i],   db_l[o] = sum_{value rows} zbar_l[row][o]
+// and for the input layer  dW_0[o][i] = sum_points zbar_0,val[o] x_i + zbar_0,d_i[o],  db_0[o] = sum zbar_0,val[o]
+// as tensor-core contractions over rows (= points x streams) with K = 32 rows per pipeline stage.
+//   A operand: image of zbar_l^T [M = 128 features x K rows]; B operand: image of a_{l-1}^T [N x K rows] where
+//   N = 128 features + a ones-column for the bias gradient, padded to 144 (for l = 0: N = 16 holding x and ones).
+// Both operands are built in shared memory by 8 conversion warps (one 16-byte core-matrix row = the 4 streams
+// of one point for one feature, so the activation jets a = act(z) are again thread-local); the accumulators
+// stay in TMEM for the whole kernel and are added to global memory once at the end.
+// ------------------------------------------------------------------------------------------
+constexpr int kDwConvWarps = 8;
+constexpr int kDwThreads = (kDwConvWarps + 1) * 32;
+constexpr int kDwPts = 8;                 // points per stage (K = 32 rows)
+constexpr int kDwStages = 3;
+constexpr int kDwN = 144;
+constexpr uint32_t kDwZBytes = 128 * 32 * 4, kDwABytes = kDwN * 32 * 4;
+constexpr uint32_t kDwStageBytes = 2 * kDwZBytes + 2 * kDwABytes;
+__host__ __device__ constexpr size_t dw_smem_bytes(int D, int L) {
+    return (size_t)kDwStages * kDwStageBytes + ((size_t)(D + L + 1) * 128 + 4) * 4 + 128;
+}
+// [rows x 32] image: cores contiguous along k (LBO = 128 B), 8-row groups 1024 B apart (SBO)
+__device__ __forceinline__ uint32_t dw_off(int m, int kgroup) { return (uint32_t)((m >> 3) * 1024 + kgroup * 128 + (m & 7) * 16); }
+
+__device__ __forceinline__ void sts_split4(unsigned char* hi_img, unsigned char* lo_img, uint32_t off, const float (&v)[4]) {
+    uint4 h, l;
+    h.x = tf32_hi(v[0]), h.y = tf32_hi(v[1]), h.z = tf32_hi(v[2]), h.w = tf32_hi(v[3]);
+    l.x = __float_as_uint(v[0] - __uint_as_float(h.x)), l.y = __float_as_uint(v[1] - __uint_as_float(h.y));
+    l.z = __float_as_uint(v[2] - __uint_as_float(h.z)), l.w = __float_as_uint(v[3] - __uint_as_float(h.w));
+    *reinterpret_cast<uint4*>(hi_img + off) = h;
+    *reinterpret_cast<uint4*>(lo_img + off) = l;
+}
+
+template <int D>
+__global__ void __launch_bounds__(kDwThreads, 1)
+dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ stash,
+             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks) {
+    using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
+    using tc::smem_desc; using tc::instr_desc; using tc::mma_ss; using tc::mma_commit; using tc::fence_async_smem;
+    using tc::tmem_ld_32x32b_x8;
+    constexpr int R = D + 2;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int L = P.n_hidden;
+    const int n_small = (D + L + 1) * 128 + 4;
+    float* small = reinterpret_cast<float*>(smem + (size_t)kDwStages * kDwStageBytes);
+    uint64_t* full = reinterpret_cast<uint64_t*>(small + n_small);
+    uint64_t* empty = full + kDwStages;
+    uint64_t* done = empty + kDwStages;
+    uint32_t* tbase_s = reinterpret_cast<uint32_t*>(done + 1);
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int s = 0; s < kDwStages; ++s) {
+            mbar_init(&full[s], kDwConvWarps);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(done, 1);
+        mbar_fence_init();
+    }
+    if (w == kDwConvWarps) tmem_alloc<1>(tbase_s, 512);
+    for (int i = tid; i < n_small; i += kDwThreads) small[i] = P.small[i];
+    // constant rows 128..143 of every B image: row 128 = indicator of the value stream, the rest zero
+    for (int i = tid; i < kDwStages * 2 * 16 * 8; i += kDwThreads) {
+        const int st = i / 256, rem = i % 256, lo = rem / 128, r = (rem % 128) / 8, kg = rem % 8;
+        unsigned char* img = smem + (size_t)st * kDwStageBytes + 2 * kDwZBytes + (lo ? kDwABytes : 0);
+        const float one = (!lo && r == 0) ? 1.f : 0.f;
+        *reinterpret_cast<float4*>(img + dw_off(128 + r, kg)) = make_float4(one, 0.f, 0.f, 0.f);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = *tbase_s;
+    const float* W0t = small;
+    const float* b0 = small + D * 128;
+    const int act = P.act;
+    const int my_blocks = num_blocks > (int)blockIdx.x ? (num_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const long long items = (long long)my_blocks * L;
+
+    if (w < kDwConvWarps) {
+        const int f = tid & 127, ph = tid >> 7;
+        for (long long it = 0; it < items; ++it) {
+            const int stg = (int)(it % kDwStages);
+            const long long blk = blockIdx.x + (it / L) * (long long)gridDim.x;
+            const int l = (int)(it % L);
+            unsigned char* ZH = smem + (size_t)stg * kDwStageBytes;
+            unsigned char* ZL = ZH + kDwZBytes;
+            unsigned char* AH = ZL + kDwZBytes;
+            unsigned char* AL = AH + kDwABytes;
+            // issue all global loads of this item first
+            float zv[4][R], sv[4][R], xv[4][D];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const long long p = blk * kDwPts + ph * 4 + j;
+                const bool valid = p < n;
+                const float* zp = zb + ((size_t)l * n + (valid ? p : 0)) * 512 + f;
+#pragma unroll
+                for (int s = 0; s < R; ++s) zv[j][s] = valid ? zp[s * 128] : 0.f;
+                if (l >= 2) {
+                    const float* sp = stash + ((size_t)(l - 2) * n + (valid ? p : 0)) * 512 + f;
+#pragma unroll
+                    for (int s = 0; s < R; ++s) sv[j][s] = sp[s * 128];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < D; ++k) xv[j][k] = valid ? x[p * D + k] : 0.f;
+                }
+            }
+            if (it >= kDwStages) mbar_wait(&empty[stg], (uint32_t)((it / kDwStages - 1) & 1));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int kg = ph * 4 + j;
+                float v[4];
+#pragma unroll
+                for (int s = 0; s < 4; ++s) v[s] = s < R ? zv[j][s] : 0.f;
+                sts_split4(ZH, ZL, dw_off(f, kg), v);
+                if (l >= 1) {
+                    float a[R];
+                    if (l >= 2) {
+                        act_jet_from_stash<D, JET_LAPLACIAN>(sv[j], a, act);
+                    } else {
+                        float z0 = b0[f];
+#pragma unroll
+                        for (int k = 0; k < D; ++k) {
+                            const float wk = W0t[k * 128 + f];
+                            z0 = fmaf(wk, xv[j][k], z0);
+                            a[1 + k] = wk;
+                        }
+                        a[0] = z0;
+                        a[1 + D] = 0.f;
+                        float st0;
+                        act_jet_fwd<D, JET_LAPLACIAN>(a, act, st0);
+                    }
+#pragma unroll
+                    for (int s = 0; s < 4; ++s) v[s] = s < R ? a[s] : 0.f;
+                    sts_split4(AH, AL, dw_off(f, kg), v);
+                } else if (f < 16) {
+                    // input layer: B row f holds x_f on the value stream and 1 on derivative stream f (f < D); row D = ones
+#pragma unroll
+                    for (int s = 0; s < 4; ++s) v[s] = 0.f;
+                    if (f < D) v[0] = xv[j][f], v[1 + f] = 1.f;
+                    else if (f == D) v[0] = 1.f;
+                    sts_split4(AH, AL, dw_off(f, kg), v);
+                }
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[stg]);
+        }
+        // ---- drain: accumulators -> global (one atomic per element per CTA) ----
+        mbar_wait(done, 0);
+        tc_fence_after();
+        const int q = w & 3, half = w >> 2, m = 32 * q + lane;
+        const uint32_t tl = tb + ((uint32_t)(32 * q) << 16);
+        if (my_blocks > 0) {
+            for (int l = 1; l < L; ++l) {
+                for (int c0 = half * 8; c0 < kDwN - 8; c0 += 16) {
+                    uint32_t r[8];
+                    tmem_ld_32x32b_x8(tl + (uint32_t)(l - 1) * kDwN + c0, r);
+                    tmem_wait_ld();
+                    if (c0 < 128) {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) atomicAdd(&dWacc[((size_t)(l - 1) * 128 + m) * 128 + c0 + c], __uint_as_float(r[c]));
+                    } else {
+                        atomicAdd(&small_acc[(D + l) * 128 + m], __uint_as_float(r[0]));
+                    }
+                }
+            }
+            if (half == 0) {
+                uint32_t r[8];
+                tmem_ld_32x32b_x8(tl + 3u * kDwN, r);
+                tmem_wait_ld();
+#pragma unroll
+                for (int k = 0; k < D; ++k) atomicAdd(&small_acc[k * 128 + m], __uint_as_float(r[k]));
+                atomicAdd(&small_acc[D * 128 + m], __uint_as_float(r[D]));
+            }
+        }
+    } else if (lane == 0) {
+        constexpr uint32_t idescN = instr_desc(2, 128, kDwN, 0, 0), idesc0 = instr_desc(2, 128, 16, 0, 0);
+        for (long long it = 0; it < items; ++it) {
+            const int stg = (int)(it % kDwStages);
+            const int l = (int)(it % L);
+            const bool first = it < L;
+            mbar_wait(&full[stg], (uint32_t)((it / kDwStages) & 1));
+            tc_fence_after();
+            const uint32_t zh = smem_u32(smem + (size_t)stg * kDwStageBytes), zl = zh + kDwZBytes, ah = zl + kDwZBytes, al = ah + kDwABytes;
+            const uint32_t dcol = tb + (l == 0 ? 3u * kDwN : (uint32_t)(l - 1) * kDwN);
+            const uint32_t idesc = l == 0 ? idesc0 : idescN;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint64_t azh = smem_desc(zh + j * 256, 128, 1024), azl = smem_desc(zl + j * 256, 128, 1024);
+                const uint64_t bah = smem_desc(ah + j * 256, 128, 1024), bal = smem_desc(al + j * 256, 128, 1024);
+                mma_ss<0, 1>(dcol, azh, bah, idesc, (first && j == 0) ? 0u : 1u);
+                mma_ss<0, 1>(dcol, azl, bah, idesc, 1u);
+                mma_ss<0, 1>(dcol, azh, bal, idesc, 1u);
+            }
+            mma_commit(&empty[stg]);
+        }
+        mma_commit(done);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (w == kDwConvWarps) tmem_dealloc<1>(tb, 512);
 }
 
 }  // namespace tcp
