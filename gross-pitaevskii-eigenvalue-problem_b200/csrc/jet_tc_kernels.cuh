@@ -28,7 +28,10 @@
 namespace gpe {
 namespace tcp {
 
-constexpr int kEpiWarps = 8;                       // 2 per TMEM lane quadrant
+constexpr int kEpiWarps = 16;                      // 4 per TMEM lane quadrant
+constexpr int kWpq = kEpiWarps / 4;                // warps per quadrant
+constexpr int kCw = 32 / kWpq;                     // columns per warp in every 32-column chunk
+constexpr int kNI = kCw / 8;                       // 16x256b repetitions per warp and chunk
 constexpr int kTcThreads = (kEpiWarps + 1) * 32;   // + MMA / control warp
 constexpr int kTcPts = 32;                         // points per CTA tile
 constexpr int kTcMaxMat = 3;                       // resident hidden matrices (64 KB each per CTA)
@@ -79,10 +82,20 @@ __global__ void pack_wimg_kernel(PtrArray W, int L, int Wd, int transpose, float
 // ------------------------------------------------------------------------------------------
 // forward: u, grad u, Laplacian per point (JET_LAPLACIAN semantics; for D = 1 the trace is u_xx)
 // ------------------------------------------------------------------------------------------
+
+template <int NI> struct FragIO;
+template <> struct FragIO<1> {
+    static __device__ __forceinline__ void ld(uint32_t a, uint32_t (&r)[4]) { tc::tmem_ld_16x256b_x1(a, r); }
+    static __device__ __forceinline__ void st(uint32_t a, const uint32_t (&r)[4]) { tc::tmem_st_16x256b_x1(a, r); }
+};
+template <> struct FragIO<2> {
+    static __device__ __forceinline__ void ld(uint32_t a, uint32_t (&r)[8]) { tc::tmem_ld_16x256b_x2(a, r); }
+    static __device__ __forceinline__ void st(uint32_t a, const uint32_t (&r)[8]) { tc::tmem_st_16x256b_x2(a, r); }
+};
 // split the 4 stream slots of one (point, feature) into the hi / lo fragment registers
 template <int R>
-__device__ __forceinline__ void put_slots(const float* a, int i, int e, uint32_t (&LoHi)[16], uint32_t (&HiHi)[16],
-                                          uint32_t (&LoLo)[16], uint32_t (&HiLo)[16]) {
+__device__ __forceinline__ void put_slots(const float* a, int i, int e, uint32_t (&LoHi)[4 * kNI], uint32_t (&HiHi)[4 * kNI],
+                                          uint32_t (&LoLo)[4 * kNI], uint32_t (&HiLo)[4 * kNI]) {
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
         const float v = s < R ? a[s] : 0.f;
@@ -103,7 +116,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
-    using tc::tmem_ld_16x256b_x4; using tc::tmem_st_16x256b_x4;
+    using IO = FragIO<kNI>;
     constexpr int R = D + 2;
     extern __shared__ __align__(1024) unsigned char smem[];
     const int L = P.n_hidden, nmat = L - 1;
@@ -121,7 +134,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
     const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
 
     if (tid == 0) {
-        for (int c = 0; c < 4; ++c) mbar_init(&a_ready[c], 8);
+        for (int c = 0; c < 4; ++c) mbar_init(&a_ready[c], 2 * kEpiWarps);
         mbar_init(&d_full[0], 1);
         mbar_init(&d_full[1], 1);
         mbar_init(w_full, 1);
@@ -147,7 +160,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
     const int act = P.act;
 
     if (w < kEpiWarps) {
-        const int q = w & 3, half = w >> 2, pl = lane >> 2, tq = lane & 3;
+        const int q = w & 3, sub = w >> 2, pl = lane >> 2, tq = lane & 3;
         const uint32_t lane_lo = tb + ((uint32_t)(32 * q) << 16), lane_hi = lane_lo + (16u << 16);
         uint32_t dcnt[2] = {0u, 0u};
         for (int it = 0;; ++it) {
@@ -170,20 +183,20 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                 }
                 const float* bl = bias + l * 128;
 #pragma unroll 1
-                for (int cc = 0; cc < 2; ++cc) {
-                    const int c = half + 2 * cc;
-                    uint32_t LoHi[16], HiHi[16], LoLo[16], HiLo[16];
+                for (int c = 0; c < 4; ++c) {
+                    const int col0 = 32 * c + kCw * sub;   // every warp owns kCw columns of every 32-column chunk
+                    uint32_t LoHi[4 * kNI], HiHi[4 * kNI], LoLo[4 * kNI], HiLo[4 * kNI];
                     if (l > 0) {
-                        tmem_ld_16x256b_x4(lane_lo + dcol + 32 * c, LoHi);
-                        tmem_ld_16x256b_x4(lane_hi + dcol + 32 * c, HiHi);
+                        IO::ld(lane_lo + dcol + col0, LoHi);
+                        IO::ld(lane_hi + dcol + col0, HiHi);
                         tmem_wait_ld();
                     }
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
+                    for (int i = 0; i < kNI; ++i) {
                         float sv[2][R];
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
-                            const int f = 32 * c + 8 * i + 2 * tq + e;
+                            const int f = col0 + 8 * i + 2 * tq + e;
                             float z[R];
                             if (l == 0) {
                                 float z0 = bl[f];
@@ -215,16 +228,16 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                             }
                         }
                         if (STASH && l > 0 && valid) {
-                            float* sp = stash + ((size_t)(l - 1) * n + p) * 512 + 32 * c + 8 * i + 2 * tq;
+                            float* sp = stash + ((size_t)(l - 1) * n + p) * 512 + col0 + 8 * i + 2 * tq;
 #pragma unroll
                             for (int s = 0; s < R; ++s) *reinterpret_cast<float2*>(sp + s * 128) = make_float2(sv[0][s], sv[1][s]);
                         }
                     }
                     if (l < L - 1) {
-                        tmem_st_16x256b_x4(lane_lo + kColAHi + 32 * c, LoHi);
-                        tmem_st_16x256b_x4(lane_hi + kColAHi + 32 * c, HiHi);
-                        tmem_st_16x256b_x4(lane_lo + kColALo + 32 * c, LoLo);
-                        tmem_st_16x256b_x4(lane_hi + kColALo + 32 * c, HiLo);
+                        IO::st(lane_lo + kColAHi + col0, LoHi);
+                        IO::st(lane_hi + kColAHi + col0, HiHi);
+                        IO::st(lane_lo + kColALo + col0, LoLo);
+                        IO::st(lane_hi + kColALo + col0, HiLo);
                         tmem_wait_st();
                         tc_fence_before();
                         __syncwarp();
@@ -243,12 +256,17 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                 for (int s = 0; s < R; ++s) comb[(w * 8 + pl) * 4 + s] = o[s];
             }
             asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
-            if (half == 0 && tq == 0 && valid && out_u) {
-                const float* oc = comb + ((w + 4) * 8 + pl) * 4;
-                out_u[p] = o[0] + oc[0] + bout;
+            if (sub == 0 && tq == 0 && valid && out_u) {
 #pragma unroll
-                for (int i = 0; i < D; ++i) out_g[p * D + i] = o[1 + i] + oc[1 + i];
-                out_h[p] = o[1 + D] + oc[1 + D];
+                for (int k = 1; k < kWpq; ++k) {
+                    const float* oc = comb + ((w + 4 * k) * 8 + pl) * 4;
+#pragma unroll
+                    for (int s = 0; s < R; ++s) o[s] += oc[s];
+                }
+                out_u[p] = o[0] + bout;
+#pragma unroll
+                for (int i = 0; i < D; ++i) out_g[p * D + i] = o[1 + i];
+                out_h[p] = o[1 + D];
             }
         }
     } else if (cta == 0 && lane == 0) {
@@ -299,7 +317,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
-    using tc::tmem_ld_16x256b_x4; using tc::tmem_st_16x256b_x4;
+    using IO = FragIO<kNI>;
     constexpr int R = D + 2;
     extern __shared__ __align__(1024) unsigned char smem[];
     const int L = P.n_hidden, nmat = L - 1;
@@ -317,7 +335,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
 
     if (tid == 0) {
-        for (int c = 0; c < 4; ++c) mbar_init(&a_ready[c], 8);
+        for (int c = 0; c < 4; ++c) mbar_init(&a_ready[c], 2 * kEpiWarps);
         mbar_init(&d_full[0], 1);
         mbar_init(&d_full[1], 1);
         mbar_init(w_full, 1);
@@ -342,14 +360,14 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     const int act = P.act;
 
     if (w < kEpiWarps) {
-        const int q = w & 3, half = w >> 2, pl = lane >> 2, tq = lane & 3;
+        const int q = w & 3, sub = w >> 2, pl = lane >> 2, tq = lane & 3;
         const uint32_t lane_lo = tb + ((uint32_t)(32 * q) << 16), lane_hi = lane_lo + (16u << 16);
         uint32_t dcnt[2] = {0u, 0u};
-        float dwout_acc[2][8];
+        float dwout_acc[4][2 * kNI];
 #pragma unroll
-        for (int a = 0; a < 2; ++a)
+        for (int a = 0; a < 4; ++a)
 #pragma unroll
-            for (int b = 0; b < 8; ++b) dwout_acc[a][b] = 0.f;
+            for (int b = 0; b < 2 * kNI; ++b) dwout_acc[a][b] = 0.f;
         float dbout_acc = 0.f;
         for (int it = 0;; ++it) {
             const long long T = cluster_id + (long long)it * num_clusters;
@@ -363,7 +381,19 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
 #pragma unroll
             for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? g_bar[p * D + i] : 0.f;
             adj[1 + D] = (valid && h_bar) ? h_bar[p] : 0.f;
-            if (half == 0 && tq == 0) dbout_acc += adj[0];
+            if (sub == 0 && tq == 0) dbout_acc += adj[0];
+            // stashed forward jets of (layer l, chunk c) for this thread: 2 column pairs x R streams.  Loaded one
+            // chunk ahead (and across the layer boundary) so the global-load latency hides behind the previous chunk.
+            const float* sbase = stash + (size_t)(valid ? p : 0) * 512 + kCw * sub + 2 * tq;
+            auto load_stash = [&](int l, int c, float2 (&dst)[kNI][R]) {
+                const float* sp = sbase + (size_t)(l - 1) * n * 512 + 32 * c;
+#pragma unroll
+                for (int i = 0; i < kNI; ++i)
+#pragma unroll
+                    for (int s = 0; s < R; ++s) dst[i][s] = *reinterpret_cast<const float2*>(sp + 8 * i + s * 128);
+            };
+            float2 cur[kNI][R];
+            if (L > 1) load_stash(L - 1, 0, cur);
             for (int l = L - 1; l >= 0; --l) {
                 const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
                 if (l < L - 1) {
@@ -373,26 +403,23 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                 }
                 const float* bl = bias + l * 128;
 #pragma unroll
-                for (int cc = 0; cc < 2; ++cc) {
-                    const int c = half + 2 * cc;
-                    uint32_t LoHi[16], HiHi[16], LoLo[16], HiLo[16];
+                for (int c = 0; c < 4; ++c) {
+                    const int col0 = 32 * c + kCw * sub;
+                    float2 nxt[kNI][R];
+                    if (c < 3) {
+                        if (l > 0) load_stash(l, c + 1, nxt);
+                    } else if (l > 1) {
+                        load_stash(l - 1, 0, nxt);
+                    }
+                    uint32_t LoHi[4 * kNI], HiHi[4 * kNI], LoLo[4 * kNI], HiLo[4 * kNI];
                     if (l < L - 1) {
-                        tmem_ld_16x256b_x4(lane_lo + dcol + 32 * c, LoHi);
-                        tmem_ld_16x256b_x4(lane_hi + dcol + 32 * c, HiHi);
+                        IO::ld(lane_lo + dcol + col0, LoHi);
+                        IO::ld(lane_hi + dcol + col0, HiHi);
                         tmem_wait_ld();
                     }
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int f0 = 32 * c + 8 * i + 2 * tq;
-                        float stv[R][2];
-                        if (l > 0) {
-                            const float* sp = stash + ((size_t)(l - 1) * n + (valid ? p : 0)) * 512 + f0;
-#pragma unroll
-                            for (int s = 0; s < R; ++s) {
-                                const float2 v = *reinterpret_cast<const float2*>(sp + s * 128);
-                                stv[s][0] = v.x, stv[s][1] = v.y;
-                            }
-                        }
+                    for (int i = 0; i < kNI; ++i) {
+                        const int f0 = col0 + 8 * i + 2 * tq;
                         float zbv[R][2];
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
@@ -400,7 +427,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                             float st[R], ab[R];
                             if (l > 0) {
 #pragma unroll
-                                for (int s = 0; s < R; ++s) st[s] = stv[s][e];
+                                for (int s = 0; s < R; ++s) st[s] = e ? cur[i][s].y : cur[i][s].x;
                             } else {
                                 float zz[R];
                                 float z0 = bl[f];
@@ -426,13 +453,13 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                                 float a[R];
                                 act_jet_from_stash<D, JET_LAPLACIAN>(st, a, act);
                                 const float wo = wout[f];
-                                float dw = dwout_acc[cc][2 * i + e];
+                                float dw = dwout_acc[c][2 * i + e];
 #pragma unroll
                                 for (int s = 0; s < R; ++s) {
                                     dw = fmaf(adj[s], a[s], dw);
                                     ab[s] = adj[s] * wo;
                                 }
-                                dwout_acc[cc][2 * i + e] = dw;
+                                dwout_acc[c][2 * i + e] = dw;
                             }
                             act_jet_bwd<D, JET_LAPLACIAN>(st, ab, act);
 #pragma unroll
@@ -446,34 +473,38 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                         }
                     }
                     if (l > 0) {
-                        tmem_st_16x256b_x4(lane_lo + kColAHi + 32 * c, LoHi);
-                        tmem_st_16x256b_x4(lane_hi + kColAHi + 32 * c, HiHi);
-                        tmem_st_16x256b_x4(lane_lo + kColALo + 32 * c, LoLo);
-                        tmem_st_16x256b_x4(lane_hi + kColALo + 32 * c, HiLo);
+                        IO::st(lane_lo + kColAHi + col0, LoHi);
+                        IO::st(lane_hi + kColAHi + col0, HiHi);
+                        IO::st(lane_lo + kColALo + col0, LoLo);
+                        IO::st(lane_hi + kColALo + col0, HiLo);
                         tmem_wait_st();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
                     }
+#pragma unroll
+                    for (int i = 0; i < kNI; ++i)
+#pragma unroll
+                        for (int s = 0; s < R; ++s) cur[i][s] = nxt[i][s];
                 }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");   // all D reads of this tile done
         }
         // flush the output-layer gradient: sum over the 8 points of the warp, one atomic per feature
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc)
+        for (int c = 0; c < 4; ++c)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                float v = dwout_acc[cc][j];
+            for (int j = 0; j < 2 * kNI; ++j) {
+                float v = dwout_acc[c][j];
                 v += __shfl_xor_sync(0xffffffffu, v, 4);
                 v += __shfl_xor_sync(0xffffffffu, v, 8);
                 v += __shfl_xor_sync(0xffffffffu, v, 16);
-                if (pl == 0) atomicAdd(&small_acc[(D + L) * 128 + 32 * (half + 2 * cc) + 8 * (j >> 1) + 2 * tq + (j & 1)], v);
+                if (pl == 0) atomicAdd(&small_acc[(D + L) * 128 + 32 * c + kCw * sub + 8 * (j >> 1) + 2 * tq + (j & 1)], v);
             }
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 4);
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 8);
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 16);
-        if (lane == 0 && half == 0) atomicAdd(&small_acc[(D + L + 1) * 128], dbout_acc);
+        if (lane == 0 && sub == 0) atomicAdd(&small_acc[(D + L + 1) * 128], dbout_acc);
     } else if (cta == 0 && lane == 0) {
         constexpr uint32_t idesc = instr_desc(2, 256, 128, 0, 0);
         const uint32_t wbase = smem_u32(wimg_s);
@@ -582,20 +613,13 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
     const float* b0 = small + D * 128;
     const int act = P.act;
     const int my_blocks = num_blocks > (int)blockIdx.x ? (num_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    const long long items = (long long)my_blocks * L;
+    const int items = my_blocks * L;
 
     if (w < kDwConvWarps) {
         const int f = tid & 127, ph = tid >> 7;
-        for (long long it = 0; it < items; ++it) {
-            const int stg = (int)(it % kDwStages);
-            const long long blk = blockIdx.x + (it / L) * (long long)gridDim.x;
-            const int l = (int)(it % L);
-            unsigned char* ZH = smem + (size_t)stg * kDwStageBytes;
-            unsigned char* ZL = ZH + kDwZBytes;
-            unsigned char* AH = ZL + kDwZBytes;
-            unsigned char* AL = AH + kDwABytes;
-            // issue all global loads of this item first
-            float zv[4][R], sv[4][R], xv[4][D];
+        // global loads of item `it` (one item = 8 points of one layer), issued one item ahead of their use
+        auto load_item = [&](int bi, int l, float (&zv)[4][R], float (&sv)[4][R], float (&xv)[4][D]) {
+            const long long blk = blockIdx.x + (long long)bi * gridDim.x;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const long long p = blk * kDwPts + ph * 4 + j;
@@ -612,7 +636,20 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
                     for (int k = 0; k < D; ++k) xv[j][k] = valid ? x[p * D + k] : 0.f;
                 }
             }
-            if (it >= kDwStages) mbar_wait(&empty[stg], (uint32_t)((it / kDwStages - 1) & 1));
+        };
+        float zv[4][R], sv[4][R], xv[4][D];
+        if (items > 0) load_item(0, 0, zv, sv, xv);
+        int stg = 0, l = 0, bi = 0;
+        uint32_t round = 0;   // how many times the stage ring has wrapped
+        for (int it = 0; it < items; ++it) {
+            unsigned char* ZH = smem + (size_t)stg * kDwStageBytes;
+            unsigned char* ZL = ZH + kDwZBytes;
+            unsigned char* AH = ZL + kDwZBytes;
+            unsigned char* AL = AH + kDwABytes;
+            float nzv[4][R], nsv[4][R], nxv[4][D];
+            const int nl = l + 1 == L ? 0 : l + 1, nbi = l + 1 == L ? bi + 1 : bi;
+            if (it + 1 < items) load_item(nbi, nl, nzv, nsv, nxv);
+            if (round > 0) mbar_wait(&empty[stg], (round - 1) & 1u);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int kg = ph * 4 + j;
@@ -652,6 +689,15 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
             fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[stg]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                for (int s = 0; s < R; ++s) zv[j][s] = nzv[j][s], sv[j][s] = nsv[j][s];
+#pragma unroll
+                for (int k = 0; k < D; ++k) xv[j][k] = nxv[j][k];
+            }
+            l = nl, bi = nbi;
+            if (++stg == kDwStages) stg = 0, ++round;
         }
         // ---- drain: accumulators -> global (one atomic per element per CTA) ----
         mbar_wait(done, 0);
@@ -683,11 +729,11 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
         }
     } else if (lane == 0) {
         constexpr uint32_t idescN = instr_desc(2, 128, kDwN, 0, 0), idesc0 = instr_desc(2, 128, 16, 0, 0);
-        for (long long it = 0; it < items; ++it) {
-            const int stg = (int)(it % kDwStages);
-            const int l = (int)(it % L);
+        int stg = 0, l = 0;
+        uint32_t round = 0;
+        for (int it = 0; it < items; ++it) {
             const bool first = it < L;
-            mbar_wait(&full[stg], (uint32_t)((it / kDwStages) & 1));
+            mbar_wait(&full[stg], round & 1u);
             tc_fence_after();
             const uint32_t zh = smem_u32(smem + (size_t)stg * kDwStageBytes), zl = zh + kDwZBytes, ah = zl + kDwZBytes, al = ah + kDwABytes;
             const uint32_t dcol = tb + (l == 0 ? 3u * kDwN : (uint32_t)(l - 1) * kDwN);
@@ -701,6 +747,8 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
                 mma_ss<0, 1>(dcol, azh, bal, idesc, 1u);
             }
             mma_commit(&empty[stg]);
+            if (++l == L) l = 0;
+            if (++stg == kDwStages) stg = 0, ++round;
         }
         mma_commit(done);
     }
