@@ -548,9 +548,10 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
 // of one point for one feature, so the activation jets a = act(z) are again thread-local); the accumulators
 // stay in TMEM for the whole kernel and are added to global memory once at the end.
 // ------------------------------------------------------------------------------------------
-constexpr int kDwConvWarps = 8;
+constexpr int kDwConvWarps = 16;
 constexpr int kDwThreads = (kDwConvWarps + 1) * 32;
 constexpr int kDwPts = 8;                 // points per stage (K = 32 rows)
+constexpr int kDwPpt = kDwPts * 128 / (kDwConvWarps * 32);   // points per conversion thread and item
 constexpr int kDwStages = 3;
 constexpr int kDwN = 144;
 constexpr uint32_t kDwZBytes = 128 * 32 * 4, kDwABytes = kDwN * 32 * 4;
@@ -618,26 +619,29 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
     if (w < kDwConvWarps) {
         const int f = tid & 127, ph = tid >> 7;
         // global loads of item `it` (one item = 8 points of one layer), issued one item ahead of their use
-        auto load_item = [&](int bi, int l, float (&zv)[4][R], float (&sv)[4][R], float (&xv)[4][D]) {
-            const long long blk = blockIdx.x + (long long)bi * gridDim.x;
+        auto load_item = [&](int bi, int l, float (&zv)[kDwPpt][R], float (&sv)[kDwPpt][R], float (&xv)[kDwPpt][D]) {
+            const long long p0 = ((long long)blockIdx.x + (long long)bi * gridDim.x) * kDwPts + ph * kDwPpt;
+            const float* zl = zb + (size_t)l * n * 512 + f;
+            const float* sl = stash + (size_t)(l >= 2 ? l - 2 : 0) * n * 512 + f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const long long p = blk * kDwPts + ph * 4 + j;
-                const bool valid = p < n;
-                const float* zp = zb + ((size_t)l * n + (valid ? p : 0)) * 512 + f;
+            for (int j = 0; j < kDwPpt; ++j) {
+                const bool valid = p0 + j < n;
+                const long long pc = valid ? p0 + j : 0;       // clamp: loads stay in bounds, the mask zeroes zbar
+                const float vm = valid ? 1.f : 0.f;
+                const float* zp = zl + pc * 512;
 #pragma unroll
-                for (int s = 0; s < R; ++s) zv[j][s] = valid ? zp[s * 128] : 0.f;
+                for (int s = 0; s < R; ++s) zv[j][s] = zp[s * 128] * vm;
                 if (l >= 2) {
-                    const float* sp = stash + ((size_t)(l - 2) * n + (valid ? p : 0)) * 512 + f;
+                    const float* sp = sl + pc * 512;
 #pragma unroll
                     for (int s = 0; s < R; ++s) sv[j][s] = sp[s * 128];
                 } else {
 #pragma unroll
-                    for (int k = 0; k < D; ++k) xv[j][k] = valid ? x[p * D + k] : 0.f;
+                    for (int k = 0; k < D; ++k) xv[j][k] = x[pc * D + k];
                 }
             }
         };
-        float zv[4][R], sv[4][R], xv[4][D];
+        float zv[kDwPpt][R], sv[kDwPpt][R], xv[kDwPpt][D];
         if (items > 0) load_item(0, 0, zv, sv, xv);
         int stg = 0, l = 0, bi = 0;
         uint32_t round = 0;   // how many times the stage ring has wrapped
@@ -646,13 +650,13 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
             unsigned char* ZL = ZH + kDwZBytes;
             unsigned char* AH = ZL + kDwZBytes;
             unsigned char* AL = AH + kDwABytes;
-            float nzv[4][R], nsv[4][R], nxv[4][D];
+            float nzv[kDwPpt][R], nsv[kDwPpt][R], nxv[kDwPpt][D];
             const int nl = l + 1 == L ? 0 : l + 1, nbi = l + 1 == L ? bi + 1 : bi;
             if (it + 1 < items) load_item(nbi, nl, nzv, nsv, nxv);
             if (round > 0) mbar_wait(&empty[stg], (round - 1) & 1u);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int kg = ph * 4 + j;
+            for (int j = 0; j < kDwPpt; ++j) {
+                const int kg = ph * kDwPpt + j;
                 float v[4];
 #pragma unroll
                 for (int s = 0; s < 4; ++s) v[s] = s < R ? zv[j][s] : 0.f;
@@ -690,7 +694,7 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[stg]);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kDwPpt; ++j) {
 #pragma unroll
                 for (int s = 0; s < R; ++s) zv[j][s] = nzv[j][s], sv[j][s] = nsv[j][s];
 #pragma unroll
@@ -702,11 +706,11 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
         // ---- drain: accumulators -> global (one atomic per element per CTA) ----
         mbar_wait(done, 0);
         tc_fence_after();
-        const int q = w & 3, half = w >> 2, m = 32 * q + lane;
+        const int q = w & 3, grp = w >> 2, m = 32 * q + lane;
         const uint32_t tl = tb + ((uint32_t)(32 * q) << 16);
         if (my_blocks > 0) {
             for (int l = 1; l < L; ++l) {
-                for (int c0 = half * 8; c0 < kDwN - 8; c0 += 16) {
+                for (int c0 = grp * 8; c0 < kDwN - 8; c0 += 8 * (kDwConvWarps / 4)) {
                     uint32_t r[8];
                     tmem_ld_32x32b_x8(tl + (uint32_t)(l - 1) * kDwN + c0, r);
                     tmem_wait_ld();
@@ -718,7 +722,7 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
                     }
                 }
             }
-            if (half == 0) {
+            if (grp == 0) {
                 uint32_t r[8];
                 tmem_ld_32x32b_x8(tl + 3u * kDwN, r);
                 tmem_wait_ld();
