@@ -12,8 +12,12 @@ evaluation of the loss and its parameter gradient through the public module API
   value     points/s, whole job, inputs resident in HBM, optimizer excluded
   e2e       same metric through the same API from HOST buffers: per step the collocation block is copied
             from pinned host memory, Adam steps, and the loss is read back
-  roofline  dominant kernel = jet_bwd_kernel (reverse sweep); FP32-FFMA bound; algorithmic FLOPs per
-            SURVEY.md 8(d) (2/3 of F_step per point) / CUDA-event time of the backward phase
+  roofline  tensor path (default): the largest of the three tcgen05 backward kernels (stash forward, reverse
+            sweep, dW contraction), timed live with CUDA events on the launch stream (gpe_tc_profile);
+            bound "tensor"; achieved = algorithmic FLOPs (2 W^2 S (L-1) per point per
+            contraction, S = 1+2d) / that time; peak = measured bf16 dense TFLOP/s of MEASURED_PEAKS.json
+            (TF32 runs at half that rate and the 3xTF32 split issues 3 MMAs per product: both stated).
+            With GPE_TENSOR=0: jet_bwd_kernel, FP32-FFMA bound, as in the first round-1 line
   cpu_baseline  the oracle port of the reference classes on the host cores, bounded sample
 
 `--impl reference` times that CPU port alone (the reference is pure PyTorch; /root/reference does not
@@ -144,7 +148,17 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # the B200 arm
 # --------------------------------------------------------------------------------------------------
-KERNELS_PER_STEP = 12   # ours: 2x(pack_weights + jet_fwd) + gram_moments + gram_adjoints + 2x(pack + jet_bwd + finish_grads)
+KERNELS_PER_STEP = 12   # FFMA path: 2x(pack_weights + jet_fwd) + gram_moments + gram_adjoints + 2x(pack + jet_bwd + finish_grads)
+TC_CHUNK = 262144       # points per (stash forward, reverse sweep, dW) round of the tensor-path backward
+
+
+def kernels_per_step(n, tensor):
+    if not tensor:
+        return KERNELS_PER_STEP
+    chunks = (n + TC_CHUNK - 1) // TC_CHUNK
+    # boundary fwd (pack + jet_fwd) + main fwd (pack + pack_wimg + fwd_tc) + moments + adjoints
+    # + boundary bwd (pack + jet_bwd + finish) + main bwd (pack + 2 pack_wimg + 3 per chunk + finish)
+    return 2 + 3 + 2 + 3 + 4 + 3 * chunks
 
 
 def run_b200(args):
@@ -253,6 +267,16 @@ def run_b200(args):
     e2e_value = world * n / (float(e2e_ms) / args.steps * 1e-3)
     model.load_state_dict(saved)
 
+    # ---- per-kernel times of the tensor-path backward, one extra (untimed) step with event brackets
+    tensor = os.environ.get("GPE_TENSOR", "1") != "0"
+    tc_ms = None
+    if tensor:
+        ops.tc_profile(True)
+        step()
+        tc_ms = ops.tc_timings()
+        ops.tc_profile(False)
+        sync_all()
+
     if rank == 0:
         f_fwd, f_step = flops_per_point()
         f_fwd4, _ = flops_per_point(streams=4)
@@ -271,7 +295,8 @@ def run_b200(args):
                        "collectives_per_step": 0 if world == 1 else 2},
             "phase_ms": {"forward_and_losses": fwd_ms, "backward": bwd_ms},
             "step_tflops_algorithmic": f_step * n / (ms_per_step * 1e-3) / 1e12,
-            "roofline": {"bound": "fp32", "kernel": "jet_bwd_kernel<2,LAPLACIAN,128>", "achieved": bwd_alg, "peak": fp32_peak,
+            "roofline": None,
+            "roofline_ffma": {"bound": "fp32", "kernel": "jet_bwd_kernel<2,LAPLACIAN,128>", "achieved": bwd_alg, "peak": fp32_peak,
                          "unit": "TFLOP/s", "frac": bwd_alg / fp32_peak,
                          "peak_source": "FFMA/FFMA2 probe kernel timed in this run (MEASURED_PEAKS.json has no fp32 figure); "
                                         f"ffma={peak['ffma']:.1f} ffma2={peak['ffma2']:.1f} TFLOP/s",
@@ -282,9 +307,32 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": X_host.numel() * 4 * world, "d2h_bytes_per_step": 4 * world,
                     "includes": "pinned-host -> device copy of the collocation block, loss, backward, all-reduce, Adam step, loss read-back",
                     "last_loss": last},
-            "gpu_launches": KERNELS_PER_STEP * args.steps,
+            "gpu_launches": kernels_per_step(n, tensor) * args.steps,
             "clocks": clocks, "loss": float(loss),
         }
+        if tensor and tc_ms and max(tc_ms.values()) > 0:
+            d, W, L = LAYERS[0], LAYERS[1], len(LAYERS) - 2
+            f_contr = 2 * W * W * (1 + 2 * d) * (L - 1)          # one hidden-layer contraction sweep per point (algorithmic)
+            kname = max(tc_ms, key=tc_ms.get)
+            kms = tc_ms[kname]
+            alg = {"stash_forward": f_contr, "reverse_sweep": f_contr, "dw_contraction": f_contr}[kname]
+            sym = {"stash_forward": "tcp::jet_fwd_tc_kernel<2,true>", "reverse_sweep": "tcp::jet_rev_tc_kernel<2>",
+                   "dw_contraction": "tcp::dw_tc_kernel<2>"}[kname]
+            bf16 = measured.get("bf16_tflops_sustained") or 1400.0
+            achieved = alg * n / (kms * 1e-3) / 1e12
+            hbm_bytes = {"stash_forward": 8 + 6144, "reverse_sweep": 8 + 16 + 6144 + 8192, "dw_contraction": 8 + 8192 + 4096}[kname]
+            line["roofline"] = {
+                "bound": "tensor", "kernel": sym, "achieved": achieved, "peak": bf16, "unit": "TFLOP/s", "frac": achieved / bf16,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",
+                "tf32_peak": bf16 / 2, "effective_3xtf32_peak": bf16 / 6, "frac_of_3xtf32_peak": achieved / (bf16 / 6),
+                "algorithmic_flops_per_point": alg, "executed_tensor_flops_per_point": 3 * 2 * W * W * 4 * (L - 1),
+                "kernel_ms_per_step": kms, "kernel_launches_per_step": (n + TC_CHUNK - 1) // TC_CHUNK,
+                "tensor_backward_ms": tc_ms, "traffic": None,
+                "algorithmic_hbm_bytes_per_point": hbm_bytes, "hbm_gbs_achieved": hbm_bytes * n / (kms * 1e-3) / 1e9,
+                "hbm_gbs_measured": measured.get("hbm_gbs"), "fp32_ffma_peak_tflops": fp32_peak}
+            del line["roofline_ffma"]
+        else:
+            line["roofline"] = line.pop("roofline_ffma")
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             times = cpu_reference_steps(args.cpu_points, 3, 1, threads)

@@ -135,13 +135,13 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
 }
 
 // GPE_TENSOR=0 forces the FFMA kernels (the tcgen05 path is the default where it applies)
+int g_tc_enabled = -1;
 bool tc_enabled() {
-    static int v = -1;
-    if (v < 0) {
+    if (g_tc_enabled < 0) {
         const char* e = getenv("GPE_TENSOR");
-        v = (e && e[0] == '0') ? 0 : 1;
+        g_tc_enabled = (e && e[0] == '0') ? 0 : 1;
     }
-    return v != 0;
+    return g_tc_enabled != 0;
 }
 
 struct WsLayout {
@@ -365,6 +365,22 @@ int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float
     finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc), n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0,
                                                reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
     return check_launch("finish_grads_kernel");
+}
+
+int gpe_set_tensor_path(int enable) {
+    const int prev = tc_enabled() ? 1 : 0;
+    g_tc_enabled = enable ? 1 : 0;
+    return prev;
+}
+
+int gpe_tc_profile(int enable) {
+    tc_profile_enable(enable != 0);
+    return 0;
+}
+
+int gpe_tc_timings(double* ms, int n) {
+    if (!ms || n < 1) { set_error("gpe_tc_timings: bad arguments"); return -1; }
+    return tc_profile_read(ms, n);
 }
 
 int gpe_ffma_probe(int mode, int iters, float* sink, double* flops, gpe_stream_t stream) {

@@ -40,6 +40,8 @@ void set_error(const char* fmt, ...);
 bool tc_eligible(int d, int jet, int width, int L);
 size_t tc_wimg_bytes(int L);
 int tc_pack_wimg(const PtrArray& W, int L, int Wd, int transpose, float* wimg, cudaStream_t s);
+void tc_profile_enable(bool on);
+int tc_profile_read(double* ms, int n);
 size_t tc_stash_bytes(int L, long long n);
 size_t tc_zb_bytes(int L, long long n);
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,

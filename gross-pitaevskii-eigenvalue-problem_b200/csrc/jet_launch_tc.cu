@@ -1,5 +1,7 @@
 // Launch unit of the tensor-core (tcgen05) path.  Hidden width padded to 128, up to 3 resident hidden matrices.
 #include "jet_host.h"
+#include <mutex>
+#include <vector>
 #include "jet_tc_kernels.cuh"
 
 namespace gpe {
@@ -38,6 +40,42 @@ static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u,
     return 0;
 }
 
+// optional per-kernel timing of the tensor-path backward (bench.py roofline): events on the launch stream
+static bool g_tc_profile = false;
+struct TcEv { cudaEvent_t a, b; int kind; };
+static std::vector<TcEv> g_tc_events;
+static std::mutex g_tc_mu;
+
+void tc_profile_enable(bool on) {
+    std::lock_guard<std::mutex> lk(g_tc_mu);
+    g_tc_profile = on;
+    for (auto& e : g_tc_events) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    g_tc_events.clear();
+}
+// accumulated milliseconds per kernel class {stash forward, reverse sweep, dW contraction}; clears the record
+int tc_profile_read(double* ms, int n) {
+    std::lock_guard<std::mutex> lk(g_tc_mu);
+    for (int i = 0; i < n; ++i) ms[i] = 0.0;
+    for (auto& e : g_tc_events) {
+        if (cudaEventSynchronize(e.b) != cudaSuccess) { set_error("tc profile: event sync failed"); return -4; }
+        float t = 0.f;
+        cudaEventElapsedTime(&t, e.a, e.b);
+        if (e.kind < n) ms[e.kind] += t;
+        cudaEventDestroy(e.a); cudaEventDestroy(e.b);
+    }
+    g_tc_events.clear();
+    return 0;
+}
+struct TcScope {
+    bool on; TcEv ev; cudaStream_t s;
+    TcScope(int kind, cudaStream_t st) : on(g_tc_profile), s(st) {
+        if (on) { cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); ev.kind = kind; cudaEventRecord(ev.a, s); }
+    }
+    ~TcScope() {
+        if (on) { cudaEventRecord(ev.b, s); std::lock_guard<std::mutex> lk(g_tc_mu); g_tc_events.push_back(ev); }
+    }
+};
+
 static int tc_sms() {
     static int sms = 0;
     if (!sms) {
@@ -63,12 +101,23 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         long long clusters = sms / 2;
         if (pairs < clusters) clusters = pairs;
         const float* xc = x + c0 * D;
-        tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, (int)pairs);
-        tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
-            Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, (int)pairs);
+        {
+            TcScope t(0, s);
+            tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, (int)pairs);
+        }
+        {
+            TcScope t(1, s);
+            tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
+                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, (int)pairs);
+        }
         const long long blocks = (nc + tcp::kDwPts - 1) / tcp::kDwPts;
-        const int grid = (int)(blocks < sms ? blocks : sms);
-        tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(Pf, xc, nc, stash, zb, dWacc, small_acc, (int)blocks);
+        long long want = blocks * L;                       // every CTA owns one layer (dw_class)
+        if (want > sms) want = sms;
+        const int grid = (int)(want < L ? L : want);
+        {
+            TcScope t(2, s);
+            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(Pf, xc, nc, stash, zb, dWacc, small_acc, (int)blocks);
+        }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }
     }

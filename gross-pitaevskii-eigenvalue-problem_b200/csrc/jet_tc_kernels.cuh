@@ -283,15 +283,20 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                 for (int c = 0; c < 4; ++c) {
                     mbar_wait_cluster(&a_ready[c], acnt & 1u);
                     tc_fence_after();
+                    // the two small cross products of this chunk go first ...
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) {
                         const int j = 4 * c + kk;
                         const uint64_t bhi = smem_desc(bhi0 + j * 256, 128, 4096), blo = smem_desc(blo0 + j * 256, 128, 4096);
-                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
-                        mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, 1u);
+                        mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
                     }
                 }
+                // ... and the 16 hi*hi products last: the accumulator is rounded toward zero after every MMA, so
+                // the 32 correction MMAs land while it is ~2^-11 of its final size and only 16 roundings count
+#pragma unroll 4
+                for (int j = 0; j < 16; ++j)
+                    mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
                 mma_commit_pair(&d_full[l & 1], 3);
             }
         }
@@ -518,15 +523,20 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                 for (int c = 0; c < 4; ++c) {
                     mbar_wait_cluster(&a_ready[c], acnt & 1u);
                     tc_fence_after();
+                    // the two small cross products of this chunk go first ...
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) {
                         const int j = 4 * c + kk;
                         const uint64_t bhi = smem_desc(bhi0 + j * 256, 128, 4096), blo = smem_desc(blo0 + j * 256, 128, 4096);
-                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
-                        mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, 1u);
+                        mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
                     }
                 }
+                // ... and the 16 hi*hi products last: the accumulator is rounded toward zero after every MMA, so
+                // the 32 correction MMAs land while it is ~2^-11 of its final size and only 16 roundings count
+#pragma unroll 4
+                for (int j = 0; j < 16; ++j)
+                    mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
                 mma_commit_pair(&d_full[(l - 1) & 1], 3);
             }
         }
@@ -537,229 +547,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     if (w == kEpiWarps) tmem_dealloc<2>(tb, 512);
 }
 
-// ------------------------------------------------------------------------------------------
-// weight gradients: for every hidden matrix l = 1..L-1
-//     dW_l[o][i] = sum_rows zbar_l[row][o] * a_{l-1}[row][i],   db_l[o] = sum_{value rows} zbar_l[row][o]
-// and for the input layer  dW_0[o][i] = sum_points zbar_0,val[o] x_i + zbar_0,d_i[o],  db_0[o] = sum zbar_0,val[o]
-// as tensor-core contractions over rows (= points x streams) with K = 32 rows per pipeline stage.
-//   A operand: image of zbar_l^T [M = 128 features x K rows]; B operand: image of a_{l-1}^T [N x K rows] where
-//   N = 128 features + a ones-column for the bias gradient, padded to 144 (for l = 0: N = 16 holding x and ones).
-// Both operands are built in shared memory by 8 conversion warps (one 16-byte core-matrix row = the 4 streams
-// of one point for one feature, so the activation jets a = act(z) are again thread-local); the accumulators
-// stay in TMEM for the whole kernel and are added to global memory once at the end.
-// ------------------------------------------------------------------------------------------
-constexpr int kDwConvWarps = 16;
-constexpr int kDwThreads = (kDwConvWarps + 1) * 32;
-constexpr int kDwPts = 8;                 // points per stage (K = 32 rows)
-constexpr int kDwPpt = kDwPts * 128 / (kDwConvWarps * 32);   // points per conversion thread and item
-constexpr int kDwStages = 3;
-constexpr int kDwN = 144;
-constexpr uint32_t kDwZBytes = 128 * 32 * 4, kDwABytes = kDwN * 32 * 4;
-constexpr uint32_t kDwStageBytes = 2 * kDwZBytes + 2 * kDwABytes;
-__host__ __device__ constexpr size_t dw_smem_bytes(int D, int L) {
-    return (size_t)kDwStages * kDwStageBytes + ((size_t)(D + L + 1) * 128 + 4) * 4 + 128;
-}
-// [rows x 32] image: cores contiguous along k (LBO = 128 B), 8-row groups 1024 B apart (SBO)
-__device__ __forceinline__ uint32_t dw_off(int m, int kgroup) { return (uint32_t)((m >> 3) * 1024 + kgroup * 128 + (m & 7) * 16); }
-
-__device__ __forceinline__ void sts_split4(unsigned char* hi_img, unsigned char* lo_img, uint32_t off, const float (&v)[4]) {
-    uint4 h, l;
-    h.x = tf32_hi(v[0]), h.y = tf32_hi(v[1]), h.z = tf32_hi(v[2]), h.w = tf32_hi(v[3]);
-    l.x = __float_as_uint(v[0] - __uint_as_float(h.x)), l.y = __float_as_uint(v[1] - __uint_as_float(h.y));
-    l.z = __float_as_uint(v[2] - __uint_as_float(h.z)), l.w = __float_as_uint(v[3] - __uint_as_float(h.w));
-    *reinterpret_cast<uint4*>(hi_img + off) = h;
-    *reinterpret_cast<uint4*>(lo_img + off) = l;
-}
-
-template <int D>
-__global__ void __launch_bounds__(kDwThreads, 1)
-dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ stash,
-             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks) {
-    using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
-    using tc::smem_desc; using tc::instr_desc; using tc::mma_ss; using tc::mma_commit; using tc::fence_async_smem;
-    using tc::tmem_ld_32x32b_x8;
-    constexpr int R = D + 2;
-    extern __shared__ __align__(1024) unsigned char smem[];
-    const int L = P.n_hidden;
-    const int n_small = (D + L + 1) * 128 + 4;
-    float* small = reinterpret_cast<float*>(smem + (size_t)kDwStages * kDwStageBytes);
-    uint64_t* full = reinterpret_cast<uint64_t*>(small + n_small);
-    uint64_t* empty = full + kDwStages;
-    uint64_t* done = empty + kDwStages;
-    uint32_t* tbase_s = reinterpret_cast<uint32_t*>(done + 1);
-    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-
-    if (tid == 0) {
-        for (int s = 0; s < kDwStages; ++s) {
-            mbar_init(&full[s], kDwConvWarps);
-            mbar_init(&empty[s], 1);
-        }
-        mbar_init(done, 1);
-        mbar_fence_init();
-    }
-    if (w == kDwConvWarps) tmem_alloc<1>(tbase_s, 512);
-    for (int i = tid; i < n_small; i += kDwThreads) small[i] = P.small[i];
-    // constant rows 128..143 of every B image: row 128 = indicator of the value stream, the rest zero
-    for (int i = tid; i < kDwStages * 2 * 16 * 8; i += kDwThreads) {
-        const int st = i / 256, rem = i % 256, lo = rem / 128, r = (rem % 128) / 8, kg = rem % 8;
-        unsigned char* img = smem + (size_t)st * kDwStageBytes + 2 * kDwZBytes + (lo ? kDwABytes : 0);
-        const float one = (!lo && r == 0) ? 1.f : 0.f;
-        *reinterpret_cast<float4*>(img + dw_off(128 + r, kg)) = make_float4(one, 0.f, 0.f, 0.f);
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tb = *tbase_s;
-    const float* W0t = small;
-    const float* b0 = small + D * 128;
-    const int act = P.act;
-    const int my_blocks = num_blocks > (int)blockIdx.x ? (num_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    const int items = my_blocks * L;
-
-    if (w < kDwConvWarps) {
-        const int f = tid & 127, ph = tid >> 7;
-        // global loads of item `it` (one item = 8 points of one layer), issued one item ahead of their use
-        auto load_item = [&](int bi, int l, float (&zv)[kDwPpt][R], float (&sv)[kDwPpt][R], float (&xv)[kDwPpt][D]) {
-            const long long p0 = ((long long)blockIdx.x + (long long)bi * gridDim.x) * kDwPts + ph * kDwPpt;
-            const float* zl = zb + (size_t)l * n * 512 + f;
-            const float* sl = stash + (size_t)(l >= 2 ? l - 2 : 0) * n * 512 + f;
-#pragma unroll
-            for (int j = 0; j < kDwPpt; ++j) {
-                const bool valid = p0 + j < n;
-                const long long pc = valid ? p0 + j : 0;       // clamp: loads stay in bounds, the mask zeroes zbar
-                const float vm = valid ? 1.f : 0.f;
-                const float* zp = zl + pc * 512;
-#pragma unroll
-                for (int s = 0; s < R; ++s) zv[j][s] = zp[s * 128] * vm;
-                if (l >= 2) {
-                    const float* sp = sl + pc * 512;
-#pragma unroll
-                    for (int s = 0; s < R; ++s) sv[j][s] = sp[s * 128];
-                } else {
-#pragma unroll
-                    for (int k = 0; k < D; ++k) xv[j][k] = x[pc * D + k];
-                }
-            }
-        };
-        float zv[kDwPpt][R], sv[kDwPpt][R], xv[kDwPpt][D];
-        if (items > 0) load_item(0, 0, zv, sv, xv);
-        int stg = 0, l = 0, bi = 0;
-        uint32_t round = 0;   // how many times the stage ring has wrapped
-        for (int it = 0; it < items; ++it) {
-            unsigned char* ZH = smem + (size_t)stg * kDwStageBytes;
-            unsigned char* ZL = ZH + kDwZBytes;
-            unsigned char* AH = ZL + kDwZBytes;
-            unsigned char* AL = AH + kDwABytes;
-            float nzv[kDwPpt][R], nsv[kDwPpt][R], nxv[kDwPpt][D];
-            const int nl = l + 1 == L ? 0 : l + 1, nbi = l + 1 == L ? bi + 1 : bi;
-            if (it + 1 < items) load_item(nbi, nl, nzv, nsv, nxv);
-            if (round > 0) mbar_wait(&empty[stg], (round - 1) & 1u);
-#pragma unroll
-            for (int j = 0; j < kDwPpt; ++j) {
-                const int kg = ph * kDwPpt + j;
-                float v[4];
-#pragma unroll
-                for (int s = 0; s < 4; ++s) v[s] = s < R ? zv[j][s] : 0.f;
-                sts_split4(ZH, ZL, dw_off(f, kg), v);
-                if (l >= 1) {
-                    float a[R];
-                    if (l >= 2) {
-                        act_jet_from_stash<D, JET_LAPLACIAN>(sv[j], a, act);
-                    } else {
-                        float z0 = b0[f];
-#pragma unroll
-                        for (int k = 0; k < D; ++k) {
-                            const float wk = W0t[k * 128 + f];
-                            z0 = fmaf(wk, xv[j][k], z0);
-                            a[1 + k] = wk;
-                        }
-                        a[0] = z0;
-                        a[1 + D] = 0.f;
-                        float st0;
-                        act_jet_fwd<D, JET_LAPLACIAN>(a, act, st0);
-                    }
-#pragma unroll
-                    for (int s = 0; s < 4; ++s) v[s] = s < R ? a[s] : 0.f;
-                    sts_split4(AH, AL, dw_off(f, kg), v);
-                } else if (f < 16) {
-                    // input layer: B row f holds x_f on the value stream and 1 on derivative stream f (f < D); row D = ones
-#pragma unroll
-                    for (int s = 0; s < 4; ++s) v[s] = 0.f;
-                    if (f < D) v[0] = xv[j][f], v[1 + f] = 1.f;
-                    else if (f == D) v[0] = 1.f;
-                    sts_split4(AH, AL, dw_off(f, kg), v);
-                }
-            }
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full[stg]);
-#pragma unroll
-            for (int j = 0; j < kDwPpt; ++j) {
-#pragma unroll
-                for (int s = 0; s < R; ++s) zv[j][s] = nzv[j][s], sv[j][s] = nsv[j][s];
-#pragma unroll
-                for (int k = 0; k < D; ++k) xv[j][k] = nxv[j][k];
-            }
-            l = nl, bi = nbi;
-            if (++stg == kDwStages) stg = 0, ++round;
-        }
-        // ---- drain: accumulators -> global (one atomic per element per CTA) ----
-        mbar_wait(done, 0);
-        tc_fence_after();
-        const int q = w & 3, grp = w >> 2, m = 32 * q + lane;
-        const uint32_t tl = tb + ((uint32_t)(32 * q) << 16);
-        if (my_blocks > 0) {
-            for (int l = 1; l < L; ++l) {
-                for (int c0 = grp * 8; c0 < kDwN - 8; c0 += 8 * (kDwConvWarps / 4)) {
-                    uint32_t r[8];
-                    tmem_ld_32x32b_x8(tl + (uint32_t)(l - 1) * kDwN + c0, r);
-                    tmem_wait_ld();
-                    if (c0 < 128) {
-#pragma unroll
-                        for (int c = 0; c < 8; ++c) atomicAdd(&dWacc[((size_t)(l - 1) * 128 + m) * 128 + c0 + c], __uint_as_float(r[c]));
-                    } else {
-                        atomicAdd(&small_acc[(D + l) * 128 + m], __uint_as_float(r[0]));
-                    }
-                }
-            }
-            if (grp == 0) {
-                uint32_t r[8];
-                tmem_ld_32x32b_x8(tl + 3u * kDwN, r);
-                tmem_wait_ld();
-#pragma unroll
-                for (int k = 0; k < D; ++k) atomicAdd(&small_acc[k * 128 + m], __uint_as_float(r[k]));
-                atomicAdd(&small_acc[D * 128 + m], __uint_as_float(r[D]));
-            }
-        }
-    } else if (lane == 0) {
-        constexpr uint32_t idescN = instr_desc(2, 128, kDwN, 0, 0), idesc0 = instr_desc(2, 128, 16, 0, 0);
-        int stg = 0, l = 0;
-        uint32_t round = 0;
-        for (int it = 0; it < items; ++it) {
-            const bool first = it < L;
-            mbar_wait(&full[stg], round & 1u);
-            tc_fence_after();
-            const uint32_t zh = smem_u32(smem + (size_t)stg * kDwStageBytes), zl = zh + kDwZBytes, ah = zl + kDwZBytes, al = ah + kDwABytes;
-            const uint32_t dcol = tb + (l == 0 ? 3u * kDwN : (uint32_t)(l - 1) * kDwN);
-            const uint32_t idesc = l == 0 ? idesc0 : idescN;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint64_t azh = smem_desc(zh + j * 256, 128, 1024), azl = smem_desc(zl + j * 256, 128, 1024);
-                const uint64_t bah = smem_desc(ah + j * 256, 128, 1024), bal = smem_desc(al + j * 256, 128, 1024);
-                mma_ss<0, 1>(dcol, azh, bah, idesc, (first && j == 0) ? 0u : 1u);
-                mma_ss<0, 1>(dcol, azl, bah, idesc, 1u);
-                mma_ss<0, 1>(dcol, azh, bal, idesc, 1u);
-            }
-            mma_commit(&empty[stg]);
-            if (++l == L) l = 0;
-            if (++stg == kDwStages) stg = 0, ++round;
-        }
-        mma_commit(done);
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (w == kDwConvWarps) tmem_dealloc<1>(tb, 512);
-}
-
 }  // namespace tcp
 }  // namespace gpe
+
+#include "dw_tc_kernel.cuh"

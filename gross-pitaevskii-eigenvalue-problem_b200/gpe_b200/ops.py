@@ -114,3 +114,24 @@ def ffma_probe(mode: int, iters: int, device=None):
     device = torch.device("cuda") if device is None else device
     sink = torch.zeros(4, dtype=torch.float32, device=device)
     return _ops.ffma_probe(mode, iters, sink)
+
+
+def set_tensor_path(enable: bool) -> bool:
+    """Select the tcgen05 3xTF32 kernels (default where eligible) or the FFMA kernels; returns the previous setting."""
+    from . import _lib
+    return bool(_lib.lib.gpe_set_tensor_path(1 if enable else 0))
+
+
+def tc_profile(enable: bool) -> None:
+    """Bracket every tensor-path backward kernel with CUDA events (read them with tc_timings())."""
+    from . import _lib
+    _lib.check(_lib.lib.gpe_tc_profile(1 if enable else 0), "gpe_tc_profile")
+
+
+def tc_timings():
+    """Accumulated milliseconds {stash_forward, reverse_sweep, dw_contraction} since the last call (synchronises)."""
+    import ctypes
+    from . import _lib
+    ms = (ctypes.c_double * 3)()
+    _lib.check(_lib.lib.gpe_tc_timings(ms, 3), "gpe_tc_timings")
+    return {"stash_forward": ms[0], "reverse_sweep": ms[1], "dw_contraction": ms[2]}

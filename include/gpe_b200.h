@@ -124,6 +124,17 @@ int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, cons
                       const double* c, float* u_bar, float* g_bar, float* h_bar, float* nm_bar,
                       gpe_stream_t stream);
 
+/* ---- tensor-core (tcgen05) path control ----
+ * The 3xTF32 tensor path is the default wherever it applies (64 < width <= 128, Laplacian jets, <= 3 hidden
+ * matrices); GPE_TENSOR=0 in the environment or gpe_set_tensor_path(0) selects the FFMA kernels instead
+ * (north_star: tensor cores "only if TF32/BF16-split accuracy holds", otherwise register-blocked FFMA).
+ * gpe_set_tensor_path returns the previous setting.  gpe_tc_profile(1) brackets every tensor-path backward
+ * kernel with CUDA events on the launch stream; gpe_tc_timings() synchronises those events, returns the
+ * accumulated milliseconds {stash forward, reverse sweep, dW contraction} in ms[0..n) and clears the record. */
+int gpe_set_tensor_path(int enable);
+int gpe_tc_profile(int enable);
+int gpe_tc_timings(double* ms, int n);
+
 /* ---- FFMA peak probe (roofline denominator; MEASURED_PEAKS.json has no fp32 figure) ----
  * Runs `iters` dependent-chain-free FFMA (mode 0) or packed FFMA2 (mode 1) per thread on a
  * full grid; returns the number of fp32 FLOPs executed in *flops.  Time it with CUDA events. */

@@ -134,3 +134,46 @@ def test_empty_and_errors():
         ops.mlp_jet_fwd(torch.zeros((4, 1)), cW, cb, 0, ops.JET_DIAG)      # CPU tensor: no fallback
     with pytest.raises((ValueError, RuntimeError)):
         ops.mlp_jet_fwd(torch.zeros((4, 2), device="cuda"), cW, cb, 0, ops.JET_DIAG)
+
+
+# ---------------------------------------------------------------------------------------------
+# both kernel families: the tcgen05 3xTF32 path (default where eligible) and the FFMA path must each
+# meet the oracle bar on the shapes the tensor path accepts, and agree with each other
+# ---------------------------------------------------------------------------------------------
+TC_CASES = [c for c in CASES if c[1] > 64 and c[2] - 1 <= 3 and c[2] >= 2 and (c[4] == 3 or (c[0] == 1 and c[4] in (1, 2)))]
+TC_CASES += [(2, 128, 4, 1, 3, 4097), (2, 96, 2, 0, 3, 65), (1, 128, 3, 0, 1, 262144 + 77)]   # shifted tanh; ragged; two chunks
+
+
+@pytest.mark.parametrize("d,W,L,act,jet,n", TC_CASES)
+def test_tensor_and_ffma_paths(d, W, L, act, jet, n):
+    from gpe_b200 import ops
+    Ws, bs = make_net(d, W, L, seed=21 + W + L, act=act)
+    x = points(n, d, seed=n + 3)
+    m = min(n, 3000)                        # oracle (nested autograd, fp64) on a prefix; path-vs-path on everything
+    gen = torch.Generator().manual_seed(5)
+    u_bar, g_bar, h_bar = torch.randn(n, generator=gen), torch.randn((n, d), generator=gen), torch.randn((n, 1), generator=gen)
+    if n > m:                               # adjoints vanish outside the prefix, so the oracle gradient is the full one
+        u_bar[m:], g_bar[m:], h_bar[m:] = 0, 0, 0
+    cW, cb = [w.cuda() for w in Ws], [b.cuda() for b in bs]
+    out = {}
+    prev = ops.set_tensor_path(True)
+    try:
+        for name, flag in (("tensor", True), ("ffma", False)):
+            ops.set_tensor_path(flag)
+            u, g, h = ops.mlp_jet_fwd(x.cuda(), cW, cb, act, jet)
+            dWs, dbs = ops.mlp_jet_bwd(x.cuda(), cW, cb, act, jet, u_bar.cuda(), g_bar.cuda(), h_bar.cuda())
+            torch.cuda.synchronize()
+            out[name] = (u.cpu(), g.cpu(), h.cpu(), np.concatenate([t.cpu().numpy().ravel() for t in dWs + dbs]))
+    finally:
+        ops.set_tensor_path(prev)
+    ur, gr, Hr = jo.jets(x[:m], Ws, bs, act)
+    rW, rb = jo.jet_functional_param_grads(x[:m], Ws, bs, act, u_bar[:m], g_bar[:m], hbar_full(h_bar[:m], d, ops.JET_LAPLACIAN, ops))
+    ref = np.concatenate([t.numpy().ravel() for t in rW + rb])
+    for name in ("tensor", "ffma"):
+        u, g, h, grads = out[name]
+        assert rel_err(u[:m], ur) < TOL, name
+        assert rel_err(g[:m], gr) < TOL, name
+        assert rel_err(h[:m], oracle_h(Hr, d, ops.JET_LAPLACIAN, ops)) < TOL, name
+        assert rel_err(grads, ref) < TOL, name
+    for a, b in zip(out["tensor"][:3], out["ffma"][:3]):
+        assert rel_err(a, b) < TOL
