@@ -31,6 +31,7 @@ constexpr int kDwPpt = kDwPts * 128 / (kDwConvWarps * 32);    // points per conv
 constexpr int kDwStages = 2;
 constexpr int kDwGroup = 4;                                   // blocks per short accumulate chain
 constexpr int kDwN = 144;
+constexpr int kDwPf = 8;                                      // L2 prefetch distance, items
 constexpr uint32_t kDwZBytes = 128 * 32 * 4, kDwABytes = kDwN * 32 * 4;
 constexpr uint32_t kDwStageBytes = 2 * kDwZBytes + 2 * kDwABytes;
 constexpr uint32_t kDwLongBytes = 128 * kDwN * 4;             // long accumulator, [column][feature m]
@@ -52,10 +53,10 @@ __device__ __forceinline__ void sts_split4(unsigned char* hi_img, unsigned char*
 // which layer a CTA works on, and its rank / count inside that class.  The input layer converts only one
 // operand per block, so it gets about half the CTAs of a hidden layer.
 struct DwClass { int layer, rank, count; };
-__host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L) {
-    // the host launches at least L CTAs
-    int n0 = n_cta / (2 * L - 1);
+__host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n0) {
+    // the host launches at least L CTAs; n0 = CTAs of the input-layer class (host: dw_n0)
     if (n0 < 1) n0 = 1;
+    if (n0 > n_cta - (L - 1)) n0 = n_cta - (L - 1);
     if (cta < n0) return DwClass{0, cta, n0};
     const int rest = n_cta - n0, per = rest / (L - 1), extra = rest % (L - 1);
     int c = cta - n0, l = 1;
@@ -70,7 +71,7 @@ __host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L) {
 template <int D>
 __global__ void __launch_bounds__(kDwThreads, 1)
 dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ stash,
-             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks) {
+             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks, int n0_cta) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
     using tc::smem_desc; using tc::instr_desc; using tc::mma_ss; using tc::mma_commit; using tc::fence_async_smem;
     using tc::tmem_ld_32x32b_x32; using tc::tmem_ld_32x32b_x4;
@@ -86,7 +87,7 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
     uint64_t* acc_free = acc_full + 2;          // [2] short accumulator drained (one arrive per conversion warp)
     uint32_t* tbase_s = reinterpret_cast<uint32_t*>(acc_free + 2);
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-    const DwClass cls = dw_class((int)blockIdx.x, (int)gridDim.x, L);
+    const DwClass cls = dw_class((int)blockIdx.x, (int)gridDim.x, L, n0_cta);
     const int l = cls.layer;
     const int NC = l == 0 ? 16 : kDwN;          // accumulator columns of this CTA's layer
 
@@ -175,6 +176,17 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
                 }
             }
         };
+        // L2 bulk prefetch of the operand blocks kDwPf items ahead (one thread): the register prefetch above then
+        // waits on L2, not on HBM
+        auto prefetch_item = [&](int i) {
+            const long long p0 = ((long long)cls.rank + (long long)i * cls.count) * kDwPts;
+            const long long left = n - p0;
+            const uint32_t bytes = (uint32_t)(left < kDwPts ? left : kDwPts) * 512u * 4u;
+            tc::prefetch_l2_bulk(zb + ((size_t)l * n + p0) * 512, bytes);
+            if (l >= 2) tc::prefetch_l2_bulk(stash + ((size_t)(l - 2) * n + p0) * 512, bytes);
+        };
+        if (tid == 0)
+            for (int i = 0; i < kDwPf && i < items; ++i) prefetch_item(i);
         float zv[kDwPpt][R], sv[kDwPpt][R], xv[kDwPpt][D];
         if (items > 0) load_item(0, zv, sv, xv);
         int stg = 0;
@@ -185,6 +197,7 @@ dw_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* 
             unsigned char* AH = ZL + kDwZBytes;
             unsigned char* AL = AH + kDwABytes;
             float nzv[kDwPpt][R], nsv[kDwPpt][R], nxv[kDwPpt][D];
+            if (tid == 0 && it + kDwPf < items) prefetch_item(it + kDwPf);
             if (it + 1 < items) load_item(it + 1, nzv, nsv, nxv);
             if (round > 0) mbar_wait(&empty[stg], (round - 1) & 1u);
 #pragma unroll

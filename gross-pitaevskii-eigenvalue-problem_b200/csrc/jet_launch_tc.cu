@@ -1,5 +1,6 @@
 // Launch unit of the tensor-core (tcgen05) path.  Hidden width padded to 128, up to 3 resident hidden matrices.
 #include "jet_host.h"
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 #include "jet_tc_kernels.cuh"
@@ -114,9 +115,12 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         long long want = blocks * L;                       // every CTA owns one layer (dw_class)
         if (want > sms) want = sms;
         const int grid = (int)(want < L ? L : want);
+        static int n0_env = -1;   // GPE_DW_N0: CTAs of the input-layer class (tuning knob); default = an equal share
+        if (n0_env < 0) { const char* ev = getenv("GPE_DW_N0"); n0_env = ev ? atoi(ev) : 0; }
+        const int n0 = n0_env > 0 ? n0_env : grid / L;
         {
             TcScope t(2, s);
-            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(Pf, xc, nc, stash, zb, dWacc, small_acc, (int)blocks);
+            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(Pf, xc, nc, stash, zb, dWacc, small_acc, (int)blocks, n0);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }

@@ -389,6 +389,14 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             if (sub == 0 && tq == 0) dbout_acc += adj[0];
             // stashed forward jets of (layer l, chunk c) for this thread: 2 column pairs x R streams.  Loaded one
             // chunk ahead (and across the layer boundary) so the global-load latency hides behind the previous chunk.
+            if (tid == 0) {   // L2 bulk prefetch of the next tile's stash (32 points x 2 KB contiguous per layer)
+                const long long Tn = T + num_clusters;
+                const long long pn = (Tn * 2 + cta) * kTcPts;
+                if (Tn < num_pairs && pn < n) {
+                    const uint32_t bytes = (uint32_t)(n - pn < kTcPts ? n - pn : kTcPts) * 512u * 4u;
+                    for (int l = 1; l < L; ++l) tc::prefetch_l2_bulk(stash + ((size_t)(l - 1) * n + pn) * 512, bytes);
+                }
+            }
             const float* sbase = stash + (size_t)(valid ? p : 0) * 512 + kCw * sub + 2 * tq;
             auto load_stash = [&](int l, int c, float2 (&dst)[kNI][R]) {
                 const float* sp = sbase + (size_t)(l - 1) * n * 512 + 32 * c;
