@@ -158,6 +158,7 @@ def kernels_per_step(n, tensor):
     chunks = (n + TC_CHUNK - 1) // TC_CHUNK
     # boundary fwd (pack + jet_fwd) + main fwd (pack + pack_wimg + fwd_tc) + moments + adjoints
     # + boundary bwd (pack + jet_bwd + finish) + main bwd (pack + 2 pack_wimg + 3 per chunk + finish)
+    # (torch's own elementwise/reduction launches for the fp64 scalar algebra are not counted)
     return 2 + 3 + 2 + 3 + 4 + 3 * chunks
 
 
@@ -320,7 +321,10 @@ def run_b200(args):
                    "dw_contraction": "tcp::dw_tc_kernel<2>"}[kname]
             bf16 = measured.get("bf16_tflops_sustained") or 1400.0
             achieved = alg * n / (kms * 1e-3) / 1e12
-            hbm_bytes = {"stash_forward": 8 + 6144, "reverse_sweep": 8 + 16 + 6144 + 8192, "dw_contraction": 8 + 8192 + 4096}[kname]
+            # image blocks of 2 KB per point and layer: stash st_0..st_3 written once; the reverse sweep reads st_1..st_3 and
+            # writes zbar_0..zbar_3; the dW contraction reads zbar_0..zbar_3 and st_0..st_2
+            hbm_bytes = {"stash_forward": 8 + 2048 * L, "reverse_sweep": 8 + 16 + 2048 * (L - 1) + 2048 * L,
+                         "dw_contraction": 8 + 2048 * L + 2048 * (L - 1)}[kname]
             line["roofline"] = {
                 "bound": "tensor", "kernel": sym, "achieved": achieved, "peak": bf16, "unit": "TFLOP/s", "frac": achieved / bf16,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",

@@ -35,7 +35,7 @@ static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u,
     const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
     long long clusters = sms / 2;
     if (pairs < clusters) clusters = pairs;
-    tcp::jet_fwd_tc_kernel<D, STASH><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (int)pairs);
+    tcp::jet_fwd_tc_kernel<D, STASH><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, 0, (int)pairs);
     e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("jet_fwd_tc_kernel launch: %s (grid %lld, smem %zu)", cudaGetErrorString(e), 2 * clusters, smem); return -4; }
     return 0;
@@ -91,7 +91,7 @@ template <int D>
 static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
                   const float* hb, float* stash, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
     const int sms = tc_sms(), L = Pf.n_hidden;
-    const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes(D, L);
+    const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes();
     cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::jet_rev_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::dw_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dw);
@@ -102,16 +102,17 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         long long clusters = sms / 2;
         if (pairs < clusters) clusters = pairs;
         const float* xc = x + c0 * D;
+        const int nblk8 = (int)((nc + tcp::kDwPts - 1) / tcp::kDwPts);   // image blocks (8 points) per layer of this chunk
         {
             TcScope t(0, s);
-            tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, (int)pairs);
+            tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, nblk8, (int)pairs);
         }
         {
             TcScope t(1, s);
             tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
-                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, (int)pairs);
+                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, nblk8, (int)pairs);
         }
-        const long long blocks = (nc + tcp::kDwPts - 1) / tcp::kDwPts;
+        const long long blocks = nblk8;
         long long want = blocks * L;                       // every CTA owns one layer (dw_class)
         if (want > sms) want = sms;
         const int grid = (int)(want < L ? L : want);
@@ -120,7 +121,7 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         const int n0 = n0_env > 0 ? n0_env : grid / L;
         {
             TcScope t(2, s);
-            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(Pf, xc, nc, stash, zb, dWacc, small_acc, (int)blocks, n0);
+            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, xc, nc, (long long)nblk8 * tcp::kBlkFloats, stash, zb, dWacc, small_acc, nblk8, n0);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }
@@ -134,7 +135,8 @@ long long tc_bwd_chunk(long long n) {
     long long c = (n + 63) / 64 * 64;
     return c < cap ? (c > 0 ? c : 64) : cap;
 }
-size_t tc_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
+// image blocks: [layer][chunk / 8][128 features x 8 points x 4 streams]; stash holds st_0 .. st_{L-1}
+size_t tc_stash_bytes(int L, long long n) { return (size_t)L * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
 size_t tc_zb_bytes(int L, long long n) { return (size_t)L * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
 
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,

@@ -32,6 +32,7 @@ constexpr int kEpiWarps = 16;                      // 4 per TMEM lane quadrant
 constexpr int kWpq = kEpiWarps / 4;                // warps per quadrant
 constexpr int kCw = 32 / kWpq;                     // columns per warp in every 32-column chunk
 constexpr int kNI = kCw / 8;                       // 16x256b repetitions per warp and chunk
+static_assert(kCw == 8 && kNI == 1, "the image-block slot addressing assumes one 8-column group per warp and chunk");
 constexpr int kTcThreads = (kEpiWarps + 1) * 32;   // + MMA / control warp
 constexpr int kTcPts = 32;                         // points per CTA tile
 constexpr int kTcMaxMat = 3;                       // resident hidden matrices (64 KB each per CTA)
@@ -107,12 +108,28 @@ __device__ __forceinline__ void put_slots(const float* a, int i, int e, uint32_t
     }
 }
 
-// STASH: additionally write, for every hidden layer l >= 1, the pre-activation jets {tanh value | a0, z1.., z2}
-// to stash[l-1][point][stream][128] (what the reverse sweep and the dW contraction read back).
+// 32-byte vector access to one (point, feature pair) slot of an image block (dw_tc_kernel.cuh: blk_off)
+__device__ __forceinline__ void ldg_v8(const float* g, float (&v)[8]) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(g));
+}
+__device__ __forceinline__ void stg_v8(float* g, const float (&v)[8]) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(g), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]),
+                 "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
+}
+// float offset of the slot of (point p, features f0 = 8 g + 2 tq and f0 + 1) in a [block][128 x 32] image array
+__device__ __forceinline__ size_t slot_off(long long p, int g, int tq) {
+    return (size_t)(p >> 3) * 4096 + (size_t)g * 256 + (size_t)(p & 7) * 32 + 8 * tq;
+}
+
+// STASH: additionally write, for every hidden layer l, the pre-activation jets {tanh value | a0, z1.., z2} to the image
+// blocks stash[l][point / 8] (what the reverse sweep and the dW contraction read back; nblk8 = blocks per layer).
 template <int D, bool STASH>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* __restrict__ out_u, float* __restrict__ out_g,
-                  float* __restrict__ out_h, float* __restrict__ stash, int num_pairs) {
+                  float* __restrict__ out_h, float* __restrict__ stash, int nblk8, int num_pairs) {
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
@@ -227,10 +244,13 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                                 for (int s = 0; s < R; ++s) o[s] = fmaf(wo, z[s], o[s]);
                             }
                         }
-                        if (STASH && l > 0 && valid) {
-                            float* sp = stash + ((size_t)(l - 1) * n + p) * 512 + col0 + 8 * i + 2 * tq;
+                        if (STASH && (p >> 3) < nblk8) {   // whole blocks are written: the tail rows (x = 0) stay finite
+                            float sv8[8];
 #pragma unroll
-                            for (int s = 0; s < R; ++s) *reinterpret_cast<float2*>(sp + s * 128) = make_float2(sv[0][s], sv[1][s]);
+                            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                                for (int s = 0; s < 4; ++s) sv8[4 * e + s] = s < R ? sv[e][s] : 0.f;
+                            stg_v8(stash + (size_t)l * nblk8 * 4096 + slot_off(p, (col0 >> 3) + i, tq), sv8);
                         }
                     }
                     if (l < L - 1) {
@@ -318,7 +338,7 @@ template <int D>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ u_bar,
                   const float* __restrict__ g_bar, const float* __restrict__ h_bar, const float* __restrict__ stash,
-                  float* __restrict__ zb, float* __restrict__ small_acc, int num_pairs) {
+                  float* __restrict__ zb, float* __restrict__ small_acc, int nblk8, int num_pairs) {
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
@@ -387,25 +407,25 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? g_bar[p * D + i] : 0.f;
             adj[1 + D] = (valid && h_bar) ? h_bar[p] : 0.f;
             if (sub == 0 && tq == 0) dbout_acc += adj[0];
-            // stashed forward jets of (layer l, chunk c) for this thread: 2 column pairs x R streams.  Loaded one
-            // chunk ahead (and across the layer boundary) so the global-load latency hides behind the previous chunk.
-            if (tid == 0) {   // L2 bulk prefetch of the next tile's stash (32 points x 2 KB contiguous per layer)
+            const size_t lstride = (size_t)nblk8 * 4096;
+            if (tid == 0) {   // L2 bulk prefetch of the next tile's stash (4 image blocks = 64 KB contiguous per layer)
                 const long long Tn = T + num_clusters;
-                const long long pn = (Tn * 2 + cta) * kTcPts;
-                if (Tn < num_pairs && pn < n) {
-                    const uint32_t bytes = (uint32_t)(n - pn < kTcPts ? n - pn : kTcPts) * 512u * 4u;
-                    for (int l = 1; l < L; ++l) tc::prefetch_l2_bulk(stash + ((size_t)(l - 1) * n + pn) * 512, bytes);
+                const long long bn = ((Tn * 2 + cta) * kTcPts) >> 3;
+                if (Tn < num_pairs && bn < nblk8) {
+                    const uint32_t bytes = (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u;
+                    for (int l = 1; l < L; ++l) tc::prefetch_l2_bulk(stash + (size_t)l * lstride + (size_t)bn * 4096, bytes);
                 }
             }
-            const float* sbase = stash + (size_t)(valid ? p : 0) * 512 + kCw * sub + 2 * tq;
-            auto load_stash = [&](int l, int c, float2 (&dst)[kNI][R]) {
-                const float* sp = sbase + (size_t)(l - 1) * n * 512 + 32 * c;
+            const bool in_blk = (p >> 3) < nblk8;
+            // stashed forward jets of (layer l, chunk c) for this thread: one 32-byte slot per 8-column group.  Loaded one
+            // chunk ahead (and across the layer boundary) so the load latency hides behind the previous chunk.
+            const float* sbase = stash + slot_off(in_blk ? p : 0, sub, tq);
+            auto load_stash = [&](int l, int c, float (&dst)[kNI][8]) {
+                const float* sp = sbase + (size_t)l * lstride + (size_t)(4 * c) * 256;
 #pragma unroll
-                for (int i = 0; i < kNI; ++i)
-#pragma unroll
-                    for (int s = 0; s < R; ++s) dst[i][s] = *reinterpret_cast<const float2*>(sp + 8 * i + s * 128);
+                for (int i = 0; i < kNI; ++i) ldg_v8(sp + (size_t)i * 256, dst[i]);
             };
-            float2 cur[kNI][R];
+            float cur[kNI][8];
             if (L > 1) load_stash(L - 1, 0, cur);
             for (int l = L - 1; l >= 0; --l) {
                 const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
@@ -418,7 +438,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const int col0 = 32 * c + kCw * sub;
-                    float2 nxt[kNI][R];
+                    float nxt[kNI][8];
                     if (c < 3) {
                         if (l > 0) load_stash(l, c + 1, nxt);
                     } else if (l > 1) {
@@ -440,7 +460,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                             float st[R], ab[R];
                             if (l > 0) {
 #pragma unroll
-                                for (int s = 0; s < R; ++s) st[s] = e ? cur[i][s].y : cur[i][s].x;
+                                for (int s = 0; s < R; ++s) st[s] = cur[i][4 * e + s];
                             } else {
                                 float zz[R];
                                 float z0 = bl[f];
@@ -479,10 +499,13 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                             for (int s = 0; s < R; ++s) zbv[s][e] = ab[s];
                             if (l > 0) put_slots<R>(ab, i, e, LoHi, HiHi, LoLo, HiLo);
                         }
-                        if (valid) {
-                            float* zp = zb + ((size_t)l * n + p) * 512 + f0;
+                        if (in_blk) {   // whole blocks are written; rows of points >= n carry zero adjoints
+                            float zv8[8];
 #pragma unroll
-                            for (int s = 0; s < R; ++s) *reinterpret_cast<float2*>(zp + s * 128) = make_float2(zbv[s][0], zbv[s][1]);
+                            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                                for (int s = 0; s < 4; ++s) zv8[4 * e + s] = s < R ? zbv[s][e] : 0.f;
+                            stg_v8(zb + (size_t)l * lstride + slot_off(p, (col0 >> 3) + i, tq), zv8);
                         }
                     }
                     if (l > 0) {
@@ -498,7 +521,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
 #pragma unroll
                     for (int i = 0; i < kNI; ++i)
 #pragma unroll
-                        for (int s = 0; s < R; ++s) cur[i][s] = nxt[i][s];
+                        for (int s = 0; s < 8; ++s) cur[i][s] = nxt[i][s];
                 }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");   // all D reads of this tile done
