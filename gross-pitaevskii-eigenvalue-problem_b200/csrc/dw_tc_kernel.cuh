@@ -35,7 +35,7 @@ constexpr int kDwThreads = (kDwConvWarps + 2) * 32;           // + MMA warp + TM
 constexpr int kDwPts = 8;                                     // points per block (K = 32 rows)
 constexpr int kDwStages = 4;
 constexpr int kDwGroup = 4;                                   // blocks per short accumulate chain
-constexpr int kDwPf = 12;                                     // L2 prefetch distance, blocks
+constexpr int kDwPf = 0;                                      // L2 prefetch distance, blocks (0: the 4-stage TMA ring alone is best, measured)
 constexpr uint32_t kDwImgBytes = 128 * 32 * 4;                // one operand image block
 constexpr int kBlkFloats = 128 * 32;
 constexpr uint32_t kDwStageBytes = 3 * kDwImgBytes;           // raw zbar | a hi (the raw stash lands here) | a lo
@@ -76,7 +76,7 @@ __host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n0) {
 template <int D>
 __global__ void __launch_bounds__(kDwThreads, 1)
 dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long lstride, const float* __restrict__ stash,
-             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks, int n0_cta) {
+             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks, int n0_cta, int pf_dist) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
     using tc::tmem_wait_st; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit;
     using tc::fence_async_smem; using tc::tmem_ld_32x32b_x32; using tc::tmem_ld_32x32b_x16; using tc::tmem_st_32x32b_x8;
@@ -262,10 +262,10 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
             if (l != 0) tc::prefetch_l2_bulk(ssrc + off, kDwImgBytes);
             else asm volatile("prefetch.global.L2 [%0];" ::"l"(x + ((size_t)cls.rank + (size_t)i * cls.count) * kDwPts * D));
         };
-        for (int i = 0; i < kDwPf && i < items; ++i) prefetch(i);
+        for (int i = 0; i < pf_dist && i < items; ++i) prefetch(i);
         for (int it = 0; it < items; ++it) {
             const int stg = it % kDwStages;
-            if (it + kDwPf < items) prefetch(it + kDwPf);
+            if (it + pf_dist < items) prefetch(it + pf_dist);
             if (it >= kDwStages) mbar_wait(&empty[stg], (uint32_t)(((it / kDwStages) - 1) & 1));
             unsigned char* ZR = smem + (size_t)stg * kDwStageBytes;
             const size_t off = ((size_t)cls.rank + (size_t)it * cls.count) * kBlkFloats;

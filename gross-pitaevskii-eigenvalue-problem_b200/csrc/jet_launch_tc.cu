@@ -119,9 +119,11 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         static int n0_env = -1;   // GPE_DW_N0: CTAs of the input-layer class (tuning knob); default = an equal share
         if (n0_env < 0) { const char* ev = getenv("GPE_DW_N0"); n0_env = ev ? atoi(ev) : 0; }
         const int n0 = n0_env > 0 ? n0_env : grid / L;
+        static int pf_env = -1;   // GPE_DW_PF: L2 prefetch distance of the dW operand blocks (blocks ahead)
+        if (pf_env < 0) { const char* ev = getenv("GPE_DW_PF"); pf_env = ev ? atoi(ev) : tcp::kDwPf; }
         {
             TcScope t(2, s);
-            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, xc, nc, (long long)nblk8 * tcp::kBlkFloats, stash, zb, dWacc, small_acc, nblk8, n0);
+            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, xc, nc, (long long)nblk8 * tcp::kBlkFloats, stash, zb, dWacc, small_acc, nblk8, n0, pf_env);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }

@@ -408,14 +408,13 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             adj[1 + D] = (valid && h_bar) ? h_bar[p] : 0.f;
             if (sub == 0 && tq == 0) dbout_acc += adj[0];
             const size_t lstride = (size_t)nblk8 * 4096;
-            if (tid == 0) {   // L2 bulk prefetch of the next tile's stash (4 image blocks = 64 KB contiguous per layer)
-                const long long Tn = T + num_clusters;
-                const long long bn = ((Tn * 2 + cta) * kTcPts) >> 3;
-                if (Tn < num_pairs && bn < nblk8) {
-                    const uint32_t bytes = (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u;
-                    for (int l = 1; l < L; ++l) tc::prefetch_l2_bulk(stash + (size_t)l * lstride + (size_t)bn * 4096, bytes);
-                }
-            }
+            // L2 bulk prefetch of the stash images one layer ahead of their use (4 image blocks = 64 KB contiguous per
+            // tile and layer).  Not further ahead: at ~4.5 TB/s the whole L2 turns over in ~25 us.
+            auto prefetch_stash = [&](int l, long long Tt) {
+                const long long bn = ((Tt * 2 + cta) * kTcPts) >> 3;
+                if (Tt < num_pairs && bn < nblk8)
+                    tc::prefetch_l2_bulk(stash + (size_t)l * lstride + (size_t)bn * 4096, (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u);
+            };
             const bool in_blk = (p >> 3) < nblk8;
             // stashed forward jets of (layer l, chunk c) for this thread: one 32-byte slot per 8-column group.  Loaded one
             // chunk ahead (and across the layer boundary) so the load latency hides behind the previous chunk.
@@ -429,6 +428,10 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             if (L > 1) load_stash(L - 1, 0, cur);
             for (int l = L - 1; l >= 0; --l) {
                 const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
+                if (tid == 0 && L > 1) {
+                    if (l >= 2) prefetch_stash(l - 1, T);
+                    else if (l == 1) prefetch_stash(L - 1, T + num_clusters);
+                }
                 if (l < L - 1) {
                     mbar_wait(&d_full[l & 1], dcnt[l & 1] & 1u);
                     ++dcnt[l & 1];
