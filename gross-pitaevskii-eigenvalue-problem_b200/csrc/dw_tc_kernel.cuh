@@ -2,7 +2,7 @@
 //
 //   hidden matrix l = 1..L-1 :  dW_l[o][i] = sum_rows zbar_l[row][o] * a_{l-1}[row][i]
 //                               db_l[o]    = sum_{value rows} zbar_l[row][o]
-//   input layer  l = 0       :  dW_0[o][i] = sum_points zbar_0,val[o] x_i + zbar_0,d_i[o],  db_0[o] = sum zbar_0,val[o]
+//   (the input layer's 3 x 128 numbers are summed in registers by the reverse sweep, jet_rev_tc_kernel)
 //
 // i.e. a contraction over rows (= points x streams) -- what loss.backward() does with the saved activations in the
 // reference (NBroot cell 10:100, S/gross_pitaevskii_2D.py:376,422).  Here: 3xTF32 tensor-core contractions with
@@ -17,7 +17,8 @@
 //              2 points each) read the raw image, split it hi/lo and write it to TENSOR MEMORY (tcgen05.st), so the
 //              MMA reads it from TMEM and shared-memory bandwidth is spent on the B operand only.
 //   B operand (N = 128 features i, K): a_{l-1}^T.  The same warps turn the raw stash image into post-activation jets
-//              in place (hi) and write the lo image next to it.  For l = 0: a 16-row image of x_i / ones, built from x.
+//              in place (hi) and write the lo image next to it.  For l = 1 there is no stash: a_0 = act(W_0 x + b_0) is
+//              recomputed from the 8 points of the block (64 bytes of x, also TMA-fed).
 //
 // Accumulation accuracy.  tcgen05 rounds the fp32 accumulator toward zero after every MMA (measured: scripts/
 // tc_probe, scripts/tc_bign.py), a bias that grows with the length of the accumulate chain.  So every CTA owns ONE
@@ -40,7 +41,8 @@ constexpr uint32_t kDwImgBytes = 128 * 32 * 4;                // one operand ima
 constexpr int kBlkFloats = 128 * 32;
 constexpr uint32_t kDwStageBytes = 3 * kDwImgBytes;           // raw zbar | a hi (the raw stash lands here) | a lo
 constexpr uint32_t kDwColAcc = 0, kDwColZ = 256;              // TMEM: 2 x 128 accumulator columns, 4 x (32 hi + 32 lo)
-__host__ __device__ constexpr size_t dw_smem_bytes() { return (size_t)kDwStages * kDwStageBytes + 256; }
+// stages | barriers (256 B) | x blocks (kDwStages x 64 B) | W0t, b0 ((D + 1) x 128 floats)
+__host__ __device__ constexpr size_t dw_smem_bytes() { return (size_t)kDwStages * kDwStageBytes + 256 + kDwStages * 64 + 3 * 128 * 4; }
 
 // byte offset of (feature f, point-in-block p) inside an image block; the 4 streams follow contiguously.
 // cores contiguous along k (LBO = 128 B), 8-feature groups 1024 B apart (SBO)
@@ -55,31 +57,34 @@ __device__ __forceinline__ void red_add_v4(float* g, float a, float b, float c, 
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(g), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// which layer a CTA works on, and its rank / count inside that class
+// which hidden matrix l = 1..L-1 a CTA works on, and its rank / count inside that class
 struct DwClass { int layer, rank, count; };
-__host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n0) {
-    // the host launches at least L CTAs; n0 = CTAs of the input-layer class (host: bwd_tc)
-    if (n0 < 1) n0 = 1;
-    if (n0 > n_cta - (L - 1)) n0 = n_cta - (L - 1);
-    if (cta < n0) return DwClass{0, cta, n0};
-    const int rest = n_cta - n0, per = rest / (L - 1), extra = rest % (L - 1);
-    int c = cta - n0, l = 1;
+__host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n1) {
+    // the host launches at least L - 1 CTAs; n1 = CTAs of class l = 1 (it reads one operand stream, not two)
+    if (L == 2) return DwClass{1, cta, n_cta};
+    if (n1 < 1) n1 = 1;
+    if (n1 > n_cta - (L - 2)) n1 = n_cta - (L - 2);
+    if (cta < n1) return DwClass{1, cta, n1};
+    const int rest = n_cta - n1, per = rest / (L - 2), extra = rest % (L - 2);
+    int c = cta - n1, l = 2;
     for (; l < L; ++l) {
-        const int cnt = per + (l <= extra ? 1 : 0);
+        const int cnt = per + (l - 1 <= extra ? 1 : 0);
         if (c < cnt) return DwClass{l, c, cnt};
         c -= cnt;
     }
     return DwClass{L - 1, 0, 1};
 }
 
-// stash / zb: [layer][block][kBlkFloats], lstride = floats per layer.  stash[l] = st_l, zb[l] = zbar_l.
+// stash / zb: [layer][block][kBlkFloats], lstride = floats per layer.  stash[l-1] = st_l, zb[l-1] = zbar_l (l = 1..L-1).
+// small: the packed small parameters (W0t[D][128] | b[L][128] | ...), small_acc: their gradient, same layout.
 template <int D>
 __global__ void __launch_bounds__(kDwThreads, 1)
-dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long lstride, const float* __restrict__ stash,
-             const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc, int num_blocks, int n0_cta, int pf_dist) {
+dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __restrict__ x, long long n, long long lstride,
+             const float* __restrict__ stash, const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc,
+             int num_blocks, int n1_cta, int pf_dist) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
     using tc::tmem_wait_st; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit;
-    using tc::fence_async_smem; using tc::tmem_ld_32x32b_x32; using tc::tmem_ld_32x32b_x16; using tc::tmem_st_32x32b_x8;
+    using tc::fence_async_smem; using tc::tmem_ld_32x32b_x32; using tc::tmem_st_32x32b_x8;
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* raw_full = reinterpret_cast<uint64_t*>(smem + (size_t)kDwStages * kDwStageBytes);   // TMA bytes landed
     uint64_t* full = raw_full + kDwStages;      // operands converted (one arrive per conversion warp)
@@ -87,9 +92,13 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
     uint64_t* acc_full = empty + kDwStages;     // [2] short accumulator complete (tcgen05.commit)
     uint64_t* acc_free = acc_full + 2;          // [2] short accumulator drained (one arrive per conversion warp)
     uint32_t* tbase_s = reinterpret_cast<uint32_t*>(acc_free + 2);
+    float* xbuf = reinterpret_cast<float*>(smem + (size_t)kDwStages * kDwStageBytes + 256);   // [stage][8 points x D]
+    float* w0s = xbuf + kDwStages * 16;                                                         // W0t[D][128] | b0[128]
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-    const DwClass cls = dw_class((int)blockIdx.x, (int)gridDim.x, L, n0_cta);
+    const DwClass cls = dw_class((int)blockIdx.x, (int)gridDim.x, L, n1_cta);
     const int l = cls.layer;
+    if (l == 1)
+        for (int i = tid; i < (D + 1) * 128; i += kDwThreads) w0s[i] = small[i];
 
     if (tid == 0) {
         for (int s = 0; s < kDwStages; ++s) {
@@ -110,8 +119,10 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
     const uint32_t tb = *tbase_s;
     const int items = num_blocks > cls.rank ? (num_blocks - cls.rank + cls.count - 1) / cls.count : 0;   // blocks of this CTA
     const int groups = (items + kDwGroup - 1) / kDwGroup;
-    const float* zsrc = zb + (size_t)l * lstride;
-    const float* ssrc = stash + (size_t)(l > 0 ? l - 1 : 0) * lstride;
+    const float* zsrc = zb + (size_t)(l - 1) * lstride;
+    const float* ssrc = stash + (size_t)(l > 1 ? l - 2 : 0) * lstride;
+    // block `i` of this CTA: all 8 points exist (then its 8 x D coordinates come by TMA; the one ragged block is read directly)
+    auto blk_first = [&](int i) -> long long { return ((long long)cls.rank + (long long)i * cls.count) * kDwPts; };
 
     if (w < kDwConvWarps) {
         const int q = w & 3, grp = w >> 2;
@@ -125,29 +136,15 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
             mbar_wait(&acc_full[buf], (uint32_t)((g >> 1) & 1));
             tc_fence_after();
             const uint32_t tl = tb + ((uint32_t)(32 * q) << 16) + kDwColAcc + (uint32_t)buf * 128;
-            if (l != 0) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(tl + 32 * grp, r);
-                tmem_wait_ld();
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(tl + 32 * grp, r);
+            tmem_wait_ld();
 #pragma unroll
-                for (int c = 0; c < 32; ++c) acc[c] += __uint_as_float(r[c]);
-            } else if (grp == 0) {
-                uint32_t r[16];
-                tmem_ld_32x32b_x16(tl, r);
-                tmem_wait_ld();
-#pragma unroll
-                for (int c = 0; c < 16; ++c) acc[c] += __uint_as_float(r[c]);
-            }
+            for (int c = 0; c < 32; ++c) acc[c] += __uint_as_float(r[c]);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_free[buf]);
         };
-        // input-layer class: coordinate (tid >> 3) of point (tid & 7) of block i, for the threads that own an x row
-        auto load_x = [&](int i) -> float {
-            const long long p = ((long long)cls.rank + (long long)i * cls.count) * kDwPts + (tid & 7);
-            return (i < items && p < n) ? x[p * D + (tid >> 3)] : 0.f;
-        };
-        float xcur = (l == 0 && (tid >> 3) < D) ? load_x(0) : 0.f;
         for (int it = 0; it < items; ++it) {
             const int stg = it % kDwStages;
             const uint32_t par = (uint32_t)((it / kDwStages) & 1);
@@ -176,7 +173,7 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
                 bcomp = (t - bsum) - y;
                 bsum = t;
             }
-            if (l != 0) {
+            if (l != 1) {
                 // ---- stash image -> post-activation jets, hi in place, lo next to it ----
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
@@ -190,20 +187,31 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
                     *reinterpret_cast<uint4*>(AH + 16 * r) = h;
                     *reinterpret_cast<uint4*>(AL + 16 * r) = lw;
                 }
-            } else if (tid < 16 * kDwPts) {
-                // ---- input layer: 16-row image, row f < D = (x_f | 1 on derivative stream f), other rows zero ----
-                const int f = tid >> 3, pp = tid & 7;
-                float v[4] = {0.f, 0.f, 0.f, 0.f};
-                if (f < D) {
-                    v[0] = xcur;
+            } else {
+                // ---- l = 1: a_0 = act(W_0 x + b_0) of point pp, features f and f + 64, recomputed from x ----
+                const int pp = (tid >> 3) & 7, f = (tid >> 6) * 8 + (tid & 7);
+                const long long p0 = blk_first(it);
+                float xv[D];
 #pragma unroll
-                    for (int k = 0; k < D; ++k) v[1 + k] = f == k ? 1.f : 0.f;
-                    xcur = load_x(it + 1);          // one block ahead: the (L2-prefetched) load completes under this block
+                for (int k = 0; k < D; ++k)
+                    xv[k] = p0 + kDwPts <= n ? xbuf[stg * 16 + pp * D + k] : (p0 + pp < n ? x[(p0 + pp) * D + k] : 0.f);
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int fj = f + 64 * j;
+                    float z[4] = {w0s[D * 128 + fj], 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int k = 0; k < D; ++k) {
+                        const float wk = w0s[k * 128 + fj];
+                        z[0] = fmaf(wk, xv[k], z[0]);
+                        z[1 + k] = wk;
+                    }
+                    float st0;
+                    act_jet_fwd<D, JET_LAPLACIAN>(z, act, st0);
+                    uint4 h, lw;
+                    split4(make_float4(z[0], z[1], z[2], z[3]), h, lw);
+                    *reinterpret_cast<uint4*>(AH + blk_off(fj, pp)) = h;
+                    *reinterpret_cast<uint4*>(AL + blk_off(fj, pp)) = lw;
                 }
-                uint4 h, lw;
-                split4(make_float4(v[0], v[1], v[2], v[3]), h, lw);
-                *reinterpret_cast<uint4*>(AH + blk_off(f, pp)) = h;
-                *reinterpret_cast<uint4*>(AL + blk_off(f, pp)) = lw;
             }
             fence_async_smem();
             tmem_wait_st();
@@ -220,20 +228,15 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
         // ---- register accumulators -> global (vector RED, one per 4 elements and CTA) ----
         if (items > 0) {
             const int o = 32 * q + lane;
-            if (l != 0) {
-                float* dst = dWacc + ((size_t)(l - 1) * 128 + o) * 128 + 32 * grp;
+            float* dst = dWacc + ((size_t)(l - 1) * 128 + o) * 128 + 32 * grp;
 #pragma unroll
-                for (int c = 0; c < 32; c += 4) red_add_v4(dst + c, acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
-            } else if (grp == 0) {
-#pragma unroll
-                for (int c = 0; c < D; ++c) atomicAdd(&small_acc[c * 128 + o], acc[c]);
-            }
+            for (int c = 0; c < 32; c += 4) red_add_v4(dst + c, acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
             atomicAdd(&small_acc[(D + l) * 128 + o], bsum);
         }
     } else if (w == kDwConvWarps) {
         if (lane == 0) {
             // ---- MMA issue thread ----
-            const uint32_t idesc = l == 0 ? instr_desc(2, 128, 16, 0, 0) : instr_desc(2, 128, 128, 0, 0);
+            const uint32_t idesc = instr_desc(2, 128, 128, 0, 0);
             for (int it = 0; it < items; ++it) {
                 const int stg = it % kDwStages, g = it / kDwGroup, buf = g & 1;
                 const bool first = it % kDwGroup == 0;
@@ -255,23 +258,25 @@ dw_tc_kernel(int L, int act, const float* __restrict__ x, long long n, long long
             }
         }
     } else if (lane == 0) {
-        // ---- TMA producer: one bulk copy per operand image, L2 bulk prefetch kDwPf blocks ahead ----
+        // ---- TMA producer: one bulk copy per operand image (optionally an L2 bulk prefetch pf_dist blocks ahead) ----
         auto prefetch = [&](int i) {
-            const size_t off = ((size_t)cls.rank + (size_t)i * cls.count) * kBlkFloats;
+            const size_t off = (size_t)blk_first(i) / kDwPts * kBlkFloats;
             tc::prefetch_l2_bulk(zsrc + off, kDwImgBytes);
-            if (l != 0) tc::prefetch_l2_bulk(ssrc + off, kDwImgBytes);
-            else asm volatile("prefetch.global.L2 [%0];" ::"l"(x + ((size_t)cls.rank + (size_t)i * cls.count) * kDwPts * D));
+            if (l != 1) tc::prefetch_l2_bulk(ssrc + off, kDwImgBytes);
         };
         for (int i = 0; i < pf_dist && i < items; ++i) prefetch(i);
         for (int it = 0; it < items; ++it) {
             const int stg = it % kDwStages;
-            if (it + pf_dist < items) prefetch(it + pf_dist);
+            if (pf_dist > 0 && it + pf_dist < items) prefetch(it + pf_dist);
             if (it >= kDwStages) mbar_wait(&empty[stg], (uint32_t)(((it / kDwStages) - 1) & 1));
             unsigned char* ZR = smem + (size_t)stg * kDwStageBytes;
-            const size_t off = ((size_t)cls.rank + (size_t)it * cls.count) * kBlkFloats;
-            mbar_arrive_expect_tx(&raw_full[stg], l != 0 ? 2 * kDwImgBytes : kDwImgBytes);
+            const long long p0 = blk_first(it);
+            const size_t off = (size_t)p0 / kDwPts * kBlkFloats;
+            const bool xtma = l == 1 && p0 + kDwPts <= n;
+            mbar_arrive_expect_tx(&raw_full[stg], (l != 1 ? 2 * kDwImgBytes : kDwImgBytes) + (xtma ? kDwPts * D * 4u : 0u));
             tma_bulk_g2s(ZR, zsrc + off, kDwImgBytes, &raw_full[stg]);
-            if (l != 0) tma_bulk_g2s(ZR + kDwImgBytes, ssrc + off, kDwImgBytes, &raw_full[stg]);
+            if (l != 1) tma_bulk_g2s(ZR + kDwImgBytes, ssrc + off, kDwImgBytes, &raw_full[stg]);
+            else if (xtma) tma_bulk_g2s(xbuf + stg * 16, x + p0 * D, kDwPts * D * 4u, &raw_full[stg]);
         }
     }
     tc_fence_before();

@@ -113,17 +113,17 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
                 Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, nblk8, (int)pairs);
         }
         const long long blocks = nblk8;
-        long long want = blocks * L;                       // every CTA owns one layer (dw_class)
+        long long want = blocks * (L - 1);                 // every CTA owns one hidden matrix (dw_class)
         if (want > sms) want = sms;
-        const int grid = (int)(want < L ? L : want);
-        static int n0_env = -1;   // GPE_DW_N0: CTAs of the input-layer class (tuning knob); default = an equal share
-        if (n0_env < 0) { const char* ev = getenv("GPE_DW_N0"); n0_env = ev ? atoi(ev) : 0; }
-        const int n0 = n0_env > 0 ? n0_env : grid / L;
+        const int grid = (int)(want < L - 1 ? L - 1 : want);
+        static int n1_env = -1;   // GPE_DW_N1: CTAs of class l = 1 (tuning knob); default = an equal share
+        if (n1_env < 0) { const char* ev = getenv("GPE_DW_N1"); n1_env = ev ? atoi(ev) : 0; }
+        const int n0 = n1_env > 0 ? n1_env : grid / (L - 1);
         static int pf_env = -1;   // GPE_DW_PF: L2 prefetch distance of the dW operand blocks (blocks ahead)
         if (pf_env < 0) { const char* ev = getenv("GPE_DW_PF"); pf_env = ev ? atoi(ev) : tcp::kDwPf; }
         {
             TcScope t(2, s);
-            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, xc, nc, (long long)nblk8 * tcp::kBlkFloats, stash, zb, dWacc, small_acc, nblk8, n0, pf_env);
+            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, Pf.small, xc, nc, (long long)nblk8 * tcp::kBlkFloats, stash, zb, dWacc, small_acc, nblk8, n0, pf_env);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }
@@ -137,9 +137,9 @@ long long tc_bwd_chunk(long long n) {
     long long c = (n + 63) / 64 * 64;
     return c < cap ? (c > 0 ? c : 64) : cap;
 }
-// image blocks: [layer][chunk / 8][128 features x 8 points x 4 streams]; stash holds st_0 .. st_{L-1}
-size_t tc_stash_bytes(int L, long long n) { return (size_t)L * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
-size_t tc_zb_bytes(int L, long long n) { return (size_t)L * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
+// image blocks: [layer][chunk / 8][128 features x 8 points x 4 streams]; st_l and zbar_l of the hidden matrices l = 1..L-1
+size_t tc_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
+size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
 
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, float* zb, float* dWacc,

@@ -46,9 +46,12 @@ struct TcParams {
     const float* small;    // W0t[D][128], b[L][128], wout[128], bout[4]   (same pack as the FFMA path)
 };
 
-__host__ __device__ constexpr size_t tc_smem_bytes(int D, int L) {
+constexpr int kDw0Stride = 12;   // floats per (row, feature) of the input-layer accumulator: 8 point slots, conflict-free banks
+__host__ __device__ constexpr size_t tc_smem_base_bytes(int D, int L) {
     return (size_t)(L - 1) * 2 * kImgFloats * 4 + ((size_t)(D + L + 1) * 128 + 4) * 4 + kEpiWarps * 32 * 4 * 4 + 128;
 }
+// + the reverse sweep's shared-memory accumulator of the input-layer gradient, [D + 1][128][kDw0Stride]
+__host__ __device__ constexpr size_t tc_smem_bytes(int D, int L) { return tc_smem_base_bytes(D, L) + (size_t)(D + 1) * 128 * kDw0Stride * 4; }
 
 // byte offset of element (r, c) of a [rows x 128] matrix image: 8-row x 16-byte core matrices, cores of one
 // row group contiguous along c (LBO = 128 B), row groups 4096 B apart (SBO)
@@ -124,8 +127,9 @@ __device__ __forceinline__ size_t slot_off(long long p, int g, int tq) {
     return (size_t)(p >> 3) * 4096 + (size_t)g * 256 + (size_t)(p & 7) * 32 + 8 * tq;
 }
 
-// STASH: additionally write, for every hidden layer l, the pre-activation jets {tanh value | a0, z1.., z2} to the image
-// blocks stash[l][point / 8] (what the reverse sweep and the dW contraction read back; nblk8 = blocks per layer).
+// STASH: additionally write, for every hidden layer l >= 1, the pre-activation jets {tanh value | a0, z1.., z2} to the
+// image blocks stash[l-1][point / 8] (what the reverse sweep and the dW contraction read back; nblk8 = blocks per layer).
+// Layer 0 is recomputed from x by both consumers.
 template <int D, bool STASH>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* __restrict__ out_u, float* __restrict__ out_g,
@@ -244,13 +248,13 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                                 for (int s = 0; s < R; ++s) o[s] = fmaf(wo, z[s], o[s]);
                             }
                         }
-                        if (STASH && (p >> 3) < nblk8) {   // whole blocks are written: the tail rows (x = 0) stay finite
+                        if (STASH && l > 0 && (p >> 3) < nblk8) {   // whole blocks are written: the tail rows (x = 0) stay finite
                             float sv8[8];
 #pragma unroll
                             for (int e = 0; e < 2; ++e)
 #pragma unroll
                                 for (int s = 0; s < 4; ++s) sv8[4 * e + s] = s < R ? sv[e][s] : 0.f;
-                            stg_v8(stash + (size_t)l * nblk8 * 4096 + slot_off(p, (col0 >> 3) + i, tq), sv8);
+                            stg_v8(stash + (size_t)(l - 1) * nblk8 * 4096 + slot_off(p, (col0 >> 3) + i, tq), sv8);
                         }
                     }
                     if (l < L - 1) {
@@ -330,9 +334,10 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
 // ------------------------------------------------------------------------------------------
 // reverse sweep: given the adjoints (u_bar, g_bar, h_bar) of the per-point outputs and the stashed forward
 // jets, propagate  abar_{l-1} = zbar_l . W_l  down the layers on the tensor cores (B = images of W_l^T) and
-// write zbar_l (adjoint of the pre-activation jets, all streams) for every layer to zb[l][point][stream][128].
-// The weight gradients dW_l = zbar_l^T a_{l-1} are a contraction over points: dw_tc_kernel.
-// Also accumulates the output-layer gradient (dwout, dbout) into small_acc (layout of `small`).
+// write zbar_l (adjoint of the pre-activation jets, all streams) of every hidden matrix layer l >= 1 to the image blocks
+// zb[l-1][point / 8].  The weight gradients dW_l = zbar_l^T a_{l-1} are a contraction over points: dw_tc_kernel.
+// Also accumulates the output-layer gradient (dwout, dbout) and the input-layer gradient (dW_0, db_0: 3 x 128 numbers,
+// summed in registers over the tiles of the CTA) into small_acc (layout of `small`).
 // ------------------------------------------------------------------------------------------
 template <int D>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
@@ -354,6 +359,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     uint64_t* d_full = a_ready + 4;
     uint64_t* w_full = d_full + 2;
     uint32_t* tbase_s = reinterpret_cast<uint32_t*>(w_full + 1);
+    float* dw0s = reinterpret_cast<float*>(smem + tc_smem_base_bytes(D, P.n_hidden));
 
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const uint32_t cta = cluster_ctarank();
@@ -373,6 +379,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
         mbar_wait(w_full, 0);
     }
     if (w == kEpiWarps) tmem_alloc<2>(tbase_s, 512);
+    for (int i = tid; i < (D + 1) * 128 * kDw0Stride; i += kTcThreads) dw0s[i] = 0.f;
     for (int i = tid; i < n_small; i += kTcThreads) small[i] = P.small[i];
     tc_fence_before();
     __syncthreads();
@@ -413,14 +420,14 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             auto prefetch_stash = [&](int l, long long Tt) {
                 const long long bn = ((Tt * 2 + cta) * kTcPts) >> 3;
                 if (Tt < num_pairs && bn < nblk8)
-                    tc::prefetch_l2_bulk(stash + (size_t)l * lstride + (size_t)bn * 4096, (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u);
+                    tc::prefetch_l2_bulk(stash + (size_t)(l - 1) * lstride + (size_t)bn * 4096, (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u);
             };
             const bool in_blk = (p >> 3) < nblk8;
             // stashed forward jets of (layer l, chunk c) for this thread: one 32-byte slot per 8-column group.  Loaded one
             // chunk ahead (and across the layer boundary) so the load latency hides behind the previous chunk.
             const float* sbase = stash + slot_off(in_blk ? p : 0, sub, tq);
             auto load_stash = [&](int l, int c, float (&dst)[kNI][8]) {
-                const float* sp = sbase + (size_t)l * lstride + (size_t)(4 * c) * 256;
+                const float* sp = sbase + (size_t)(l - 1) * lstride + (size_t)(4 * c) * 256;
 #pragma unroll
                 for (int i = 0; i < kNI; ++i) ldg_v8(sp + (size_t)i * 256, dst[i]);
             };
@@ -502,13 +509,23 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                             for (int s = 0; s < R; ++s) zbv[s][e] = ab[s];
                             if (l > 0) put_slots<R>(ab, i, e, LoHi, HiHi, LoLo, HiLo);
                         }
-                        if (in_blk) {   // whole blocks are written; rows of points >= n carry zero adjoints
+                        if (l == 0) {
+                            // input layer: dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val -- shared-memory
+                            // accumulator (the 4 warps of a feature group share an address: red.shared)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                float* dq = dw0s + (size_t)(f0 + e) * kDw0Stride + pl;   // slot of this lane's point: no bank conflicts
+#pragma unroll
+                                for (int k = 0; k < D; ++k) atomicAdd(dq + k * 128 * kDw0Stride, fmaf(zbv[0][e], xin[k], zbv[1 + k][e]));
+                                atomicAdd(dq + D * 128 * kDw0Stride, zbv[0][e]);
+                            }
+                        } else if (in_blk) {   // whole blocks are written; rows of points >= n carry zero adjoints
                             float zv8[8];
 #pragma unroll
                             for (int e = 0; e < 2; ++e)
 #pragma unroll
                                 for (int s = 0; s < 4; ++s) zv8[4 * e + s] = s < R ? zbv[s][e] : 0.f;
-                            stg_v8(zb + (size_t)l * lstride + slot_off(p, (col0 >> 3) + i, tq), zv8);
+                            stg_v8(zb + (size_t)(l - 1) * lstride + slot_off(p, (col0 >> 3) + i, tq), zv8);
                         }
                     }
                     if (l > 0) {
@@ -540,6 +557,12 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                 v += __shfl_xor_sync(0xffffffffu, v, 16);
                 if (pl == 0) atomicAdd(&small_acc[(D + L) * 128 + 32 * c + kCw * sub + 8 * (j >> 1) + 2 * tq + (j & 1)], v);
             }
+        // input-layer gradient: sum the 8 point slots, one atomic per element and CTA (rows 0..D-1: dW_0^T, row D: b_0)
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+        for (int i = tid; i < (D + 1) * 128; i += kEpiWarps * 32) {
+            const float* dq = dw0s + (size_t)i * kDw0Stride;
+            atomicAdd(&small_acc[i], ((dq[0] + dq[1]) + (dq[2] + dq[3])) + ((dq[4] + dq[5]) + (dq[6] + dq[7])));
+        }
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 4);
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 8);
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 16);
