@@ -321,17 +321,21 @@ def run_b200(args):
                    "dw_contraction": "tcp::dw_tc_kernel<2>"}[kname]
             bf16 = measured.get("bf16_tflops_sustained") or 1400.0
             achieved = alg * n / (kms * 1e-3) / 1e12
-            # image blocks of 2 KB per point and layer: stash st_0..st_3 written once; the reverse sweep reads st_1..st_3 and
-            # writes zbar_0..zbar_3; the dW contraction reads zbar_0..zbar_3 and st_0..st_2
-            hbm_bytes = {"stash_forward": 8 + 2048 * L, "reverse_sweep": 8 + 16 + 2048 * (L - 1) + 2048 * L,
-                         "dw_contraction": 8 + 2048 * L + 2048 * (L - 1)}[kname]
+            # image blocks of 2 KB per point and hidden matrix l = 1..L-1: st_l written by the stash forward, read by the
+            # reverse sweep (all) and the dW contraction (l <= L-2); zbar_l written by the reverse sweep, read by dW
+            hbm_bytes = {"stash_forward": 8 + 2048 * (L - 1), "reverse_sweep": 8 + 16 + 2 * 2048 * (L - 1),
+                         "dw_contraction": 8 + 2048 * (L - 1) + 2048 * (L - 2)}[kname]
+            # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch (= one 262 144-point chunk) from the committed
+            # `ncu --set full` captures (profiles/r1b_tc_*_ncu_full_raw.csv); algorithmic bytes for the same launch beside it
+            ncu_traffic = {"stash_forward": 1.554e9, "reverse_sweep": 3.194e9, "dw_contraction": 2.690e9}[kname]
             line["roofline"] = {
                 "bound": "tensor", "kernel": sym, "achieved": achieved, "peak": bf16, "unit": "TFLOP/s", "frac": achieved / bf16,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",
                 "tf32_peak": bf16 / 2, "effective_3xtf32_peak": bf16 / 6, "frac_of_3xtf32_peak": achieved / (bf16 / 6),
                 "algorithmic_flops_per_point": alg, "executed_tensor_flops_per_point": 3 * 2 * W * W * 4 * (L - 1),
                 "kernel_ms_per_step": kms, "kernel_launches_per_step": (n + TC_CHUNK - 1) // TC_CHUNK,
-                "tensor_backward_ms": tc_ms, "traffic": None,
+                "tensor_backward_ms": tc_ms, "traffic": ncu_traffic, "traffic_unit": "bytes per launch (262144 points), ncu",
+                "algorithmic_bytes_per_launch": hbm_bytes * min(n, TC_CHUNK),
                 "algorithmic_hbm_bytes_per_point": hbm_bytes, "hbm_gbs_achieved": hbm_bytes * n / (kms * 1e-3) / 1e9,
                 "hbm_gbs_measured": measured.get("hbm_gbs"), "fp32_ffma_peak_tflops": fp32_peak}
             del line["roofline_ffma"]

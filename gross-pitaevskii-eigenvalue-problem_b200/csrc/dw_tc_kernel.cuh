@@ -123,6 +123,7 @@ dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __res
     const float* ssrc = stash + (size_t)(l > 1 ? l - 2 : 0) * lstride;
     // block `i` of this CTA: all 8 points exist (then its 8 x D coordinates come by TMA; the one ragged block is read directly)
     auto blk_first = [&](int i) -> long long { return ((long long)cls.rank + (long long)i * cls.count) * kDwPts; };
+    const bool x_aligned = (reinterpret_cast<uintptr_t>(x) & 15) == 0;   // cp.async.bulk needs a 16-byte aligned source
 
     if (w < kDwConvWarps) {
         const int q = w & 3, grp = w >> 2;
@@ -194,7 +195,7 @@ dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __res
                 float xv[D];
 #pragma unroll
                 for (int k = 0; k < D; ++k)
-                    xv[k] = p0 + kDwPts <= n ? xbuf[stg * 16 + pp * D + k] : (p0 + pp < n ? x[(p0 + pp) * D + k] : 0.f);
+                    xv[k] = (x_aligned && p0 + kDwPts <= n) ? xbuf[stg * 16 + pp * D + k] : (p0 + pp < n ? x[(p0 + pp) * D + k] : 0.f);
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     const int fj = f + 64 * j;
@@ -272,7 +273,7 @@ dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __res
             unsigned char* ZR = smem + (size_t)stg * kDwStageBytes;
             const long long p0 = blk_first(it);
             const size_t off = (size_t)p0 / kDwPts * kBlkFloats;
-            const bool xtma = l == 1 && p0 + kDwPts <= n;
+            const bool xtma = l == 1 && x_aligned && p0 + kDwPts <= n;
             mbar_arrive_expect_tx(&raw_full[stg], (l != 1 ? 2 * kDwImgBytes : kDwImgBytes) + (xtma ? kDwPts * D * 4u : 0u));
             tma_bulk_g2s(ZR, zsrc + off, kDwImgBytes, &raw_full[stg]);
             if (l != 1) tma_bulk_g2s(ZR + kDwImgBytes, ssrc + off, kDwImgBytes, &raw_full[stg]);

@@ -21,6 +21,8 @@ int tc_pack_wimg(const PtrArray& W, int L, int Wd, int transpose, float* wimg, c
     return 0;
 }
 
+static int tc_interleave();
+
 template <int D, bool STASH>
 static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
     static int sms = 0;
@@ -77,6 +79,12 @@ struct TcScope {
     }
 };
 
+static int tc_interleave() {   // GPE_TC_INTERLEAVE=1: see TcParams::interleave
+    static int v = -1;
+    if (v < 0) { const char* ev = getenv("GPE_TC_INTERLEAVE"); v = (ev && ev[0] == '1') ? 1 : 0; }
+    return v;
+}
+
 static int tc_sms() {
     static int sms = 0;
     if (!sms) {
@@ -96,6 +104,8 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::jet_rev_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::dw_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dw);
     if (e != cudaSuccess) { set_error("tc bwd smem attr: %s", cudaGetErrorString(e)); return -3; }
+    static int rev_pf = -1;   // GPE_REV_PF: L2 prefetch distance of the reverse sweep, in (tile, layer) steps
+    if (rev_pf < 0) { const char* ev = getenv("GPE_REV_PF"); rev_pf = ev ? atoi(ev) : 1; if (rev_pf < 1) rev_pf = 1; }
     for (long long c0 = 0; c0 < n; c0 += chunk) {
         const long long nc = n - c0 < chunk ? n - c0 : chunk;
         const long long pairs = (nc + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
@@ -110,7 +120,7 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         {
             TcScope t(1, s);
             tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
-                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, nblk8, (int)pairs);
+                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, nblk8, (int)pairs, rev_pf);
         }
         const long long blocks = nblk8;
         long long want = blocks * (L - 1);                 // every CTA owns one hidden matrix (dw_class)
@@ -144,7 +154,7 @@ size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, float* zb, float* dWacc,
                   float* small_acc, cudaStream_t s) {
-    tcp::TcParams Pf{L, act, wimg_fwd, small}, Pr{L, act, wimg_rev, small};
+    tcp::TcParams Pf{L, act, wimg_fwd, small, tc_interleave()}, Pr{L, act, wimg_rev, small, tc_interleave()};
     const long long chunk = tc_bwd_chunk(n);
     return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, zb, dWacc, small_acc, chunk, s)
                   : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, zb, dWacc, small_acc, chunk, s);
@@ -152,7 +162,7 @@ int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wim
 
 int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
                   float* g, float* h, cudaStream_t s) {
-    tcp::TcParams P{L, act, wimg, small};
+    tcp::TcParams P{L, act, wimg, small, tc_interleave()};
     return d == 1 ? fwd_tc<1, false>(P, x, n, u, g, h, nullptr, s) : fwd_tc<2, false>(P, x, n, u, g, h, nullptr, s);
 }
 

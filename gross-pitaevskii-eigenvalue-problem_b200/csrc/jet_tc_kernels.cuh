@@ -44,6 +44,8 @@ struct TcParams {
     int act;
     const float* wimg;     // [L-1][cta 2][hi,lo][kImgFloats]
     const float* small;    // W0t[D][128], b[L][128], wout[128], bout[4]   (same pack as the FFMA path)
+    int interleave;        // 1: issue the hi*hi MMAs of a chunk right after its correction MMAs (shorter exposed tail,
+                           //    more accumulator roundings at full magnitude); 0: all corrections first (default)
 };
 
 constexpr int kDw0Stride = 12;   // floats per (row, feature) of the input-layer accumulator: 8 point slots, conflict-free banks
@@ -315,12 +317,21 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                         mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
                     }
+                    if (P.interleave) {
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {
+                            const int j = 4 * c + kk;
+                            mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
+                        }
+                    }
                 }
                 // ... and the 16 hi*hi products last: the accumulator is rounded toward zero after every MMA, so
                 // the 32 correction MMAs land while it is ~2^-11 of its final size and only 16 roundings count
+                if (!P.interleave) {
 #pragma unroll 4
-                for (int j = 0; j < 16; ++j)
-                    mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
+                    for (int j = 0; j < 16; ++j)
+                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
+                }
                 mma_commit_pair(&d_full[l & 1], 3);
             }
         }
@@ -343,7 +354,7 @@ template <int D>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ u_bar,
                   const float* __restrict__ g_bar, const float* __restrict__ h_bar, const float* __restrict__ stash,
-                  float* __restrict__ zb, float* __restrict__ small_acc, int nblk8, int num_pairs) {
+                  float* __restrict__ zb, float* __restrict__ small_acc, int nblk8, int num_pairs, int pf_dist) {
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
@@ -431,13 +442,15 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
 #pragma unroll
                 for (int i = 0; i < kNI; ++i) ldg_v8(sp + (size_t)i * 256, dst[i]);
             };
+            if (tid == 0 && it == 0)   // the first tile's images that the rolling prefetch below does not cover
+                for (int j = 0; j < pf_dist && j < L - 1; ++j) prefetch_stash(L - 1 - j, T);
             float cur[kNI][8];
             if (L > 1) load_stash(L - 1, 0, cur);
             for (int l = L - 1; l >= 0; --l) {
                 const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
-                if (tid == 0 && L > 1) {
-                    if (l >= 2) prefetch_stash(l - 1, T);
-                    else if (l == 1) prefetch_stash(L - 1, T + num_clusters);
+                if (tid == 0 && l >= 1) {   // the stash image consumed pf_dist (tile, layer) steps from now
+                    const int tgt = (L - 1 - l) + pf_dist;
+                    prefetch_stash(L - 1 - tgt % (L - 1), T + (long long)(tgt / (L - 1)) * num_clusters);
                 }
                 if (l < L - 1) {
                     mbar_wait(&d_full[l & 1], dcnt[l & 1] & 1u);
@@ -588,12 +601,21 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                         mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
                     }
+                    if (P.interleave) {
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {
+                            const int j = 4 * c + kk;
+                            mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
+                        }
+                    }
                 }
                 // ... and the 16 hi*hi products last: the accumulator is rounded toward zero after every MMA, so
                 // the 32 correction MMAs land while it is ~2^-11 of its final size and only 16 roundings count
+                if (!P.interleave) {
 #pragma unroll 4
-                for (int j = 0; j < 16; ++j)
-                    mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
+                    for (int j = 0; j < 16; ++j)
+                        mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
+                }
                 mma_commit_pair(&d_full[(l - 1) & 1], 3);
             }
         }
