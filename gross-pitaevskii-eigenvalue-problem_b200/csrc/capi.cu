@@ -276,9 +276,9 @@ int gpe_workspace_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* fwd_bytes, 
     return 0;
 }
 
-int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
-                    const gpe_xform* xform, float* u, float* g, float* h, void* ws, size_t ws_bytes,
-                    gpe_stream_t stream) {
+static int jet_fwd_impl(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                        const gpe_xform* xform, float* u, float* g, float* h, float* resident, size_t resident_bytes, void* ws,
+                        size_t ws_bytes, gpe_stream_t stream) {
     JetPlan p;
     int wp;
     int rc = get_plan(desc, &p, &wp);
@@ -301,17 +301,46 @@ int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float
         for (int l = 0; l <= desc->n_hidden; ++l) Wp.p[l] = W[l];
         float* wimg = reinterpret_cast<float*>(base + w.wimg);
         if ((rc = tc_pack_wimg(Wp, desc->n_hidden, desc->width, 0, wimg, s))) return rc;
-        return launch_fwd_tc(desc->d, desc->n_hidden, desc->act, wimg, P.small, x, n, u, g, h, s);
+        if (resident && resident_bytes < tc_resident_stash_bytes(desc->n_hidden, n)) {
+            set_error("stash too small: %zu < %zu", resident_bytes, tc_resident_stash_bytes(desc->n_hidden, n));
+            return -1;
+        }
+        return launch_fwd_tc(desc->d, desc->n_hidden, desc->act, wimg, P.small, x, n, u, g, h, resident, s);
     }
+    if (resident) { set_error("this descriptor has no stash (gpe_stash_bytes = 0): use gpe_mlp_jet_fwd"); return -1; }
     rc = wp == 64 ? launch_fwd_wp64(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s)
                   : launch_fwd_wp128(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s);
     if (rc) return rc;
     return check_launch("jet_fwd_kernel");
 }
 
-int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
-                    const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar,
-                    float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream) {
+int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                    const gpe_xform* xform, float* u, float* g, float* h, void* ws, size_t ws_bytes,
+                    gpe_stream_t stream) {
+    return jet_fwd_impl(desc, W, b, x, n, xform, u, g, h, nullptr, 0, ws, ws_bytes, stream);
+}
+
+int gpe_stash_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* bytes) {
+    JetPlan p;
+    int wp;
+    const int rc = get_plan(desc, &p, &wp);
+    if (rc) return rc;
+    if (n < 0 || !bytes) { set_error("gpe_stash_bytes: bad arguments"); return -1; }
+    const bool tc = tc_enabled() && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
+    *bytes = (tc && n > 0) ? tc_resident_stash_bytes(desc->n_hidden, n) : 0;
+    return 0;
+}
+
+int gpe_mlp_jet_fwd_stash(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                          float* u, float* g, float* h, void* stash, size_t stash_bytes, void* ws, size_t ws_bytes,
+                          gpe_stream_t stream) {
+    if (!stash) { set_error("null stash"); return -1; }
+    return jet_fwd_impl(desc, W, b, x, n, nullptr, u, g, h, static_cast<float*>(stash), stash_bytes, ws, ws_bytes, stream);
+}
+
+static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                        const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar, const float* resident,
+                        size_t resident_bytes, float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream) {
     JetPlan p;
     int wp;
     int rc = get_plan(desc, &p, &wp);
@@ -340,11 +369,16 @@ int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float
         float* wimg_r = reinterpret_cast<float*>(base + w.wimg_rev);
         if ((rc = tc_pack_wimg(Wp, L, desc->width, 0, wimg_f, s))) return rc;
         if ((rc = tc_pack_wimg(Wp, L, desc->width, 1, wimg_r, s))) return rc;
+        if (resident && resident_bytes < tc_resident_stash_bytes(L, n)) {
+            set_error("stash too small: %zu < %zu", resident_bytes, tc_resident_stash_bytes(L, n));
+            return -1;
+        }
         rc = launch_bwd_tc(desc->d, L, desc->act, wimg_f, wimg_r, P.small, x, n, u_bar, g_bar, h_bar,
-                           reinterpret_cast<float*>(base + w.stash), reinterpret_cast<float*>(base + w.zb),
+                           reinterpret_cast<float*>(base + w.stash), resident, reinterpret_cast<float*>(base + w.zb),
                            reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc), s);
         if (rc) return rc;
     } else if (n > 0) {
+        if (resident) { set_error("this descriptor has no stash (gpe_stash_bytes = 0): use gpe_mlp_jet_bwd"); return -1; }
         rc = wp == 64 ? launch_bwd_wp64(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, reinterpret_cast<float*>(base + w.stash),
                                         reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc),
                                         w.grid_bwd, w.tiles, s)
@@ -365,6 +399,20 @@ int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float
     finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc), n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0,
                                                reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
     return check_launch("finish_grads_kernel");
+}
+
+int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                    const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar,
+                    float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream) {
+    return jet_bwd_impl(desc, W, b, x, n, xform, u_bar, g_bar, h_bar, nullptr, 0, dW, db, ws, ws_bytes, stream);
+}
+
+int gpe_mlp_jet_bwd_stashed(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                            const float* u_bar, const float* g_bar, const float* h_bar, const void* stash, size_t stash_bytes,
+                            float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream) {
+    if (!stash) { set_error("null stash"); return -1; }
+    return jet_bwd_impl(desc, W, b, x, n, nullptr, u_bar, g_bar, h_bar, static_cast<const float*>(stash), stash_bytes, dW, db, ws,
+                        ws_bytes, stream);
 }
 
 int gpe_set_tensor_path(int enable) {

@@ -75,11 +75,11 @@ __host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n1) {
     return DwClass{L - 1, 0, 1};
 }
 
-// stash / zb: [layer][block][kBlkFloats], lstride = floats per layer.  stash[l-1] = st_l, zb[l-1] = zbar_l (l = 1..L-1).
+// stash / zb: [layer][block][kBlkFloats]; stash_ls / lstride = floats per layer of the stash / the zbar chunk buffer.  stash[l-1] = st_l, zb[l-1] = zbar_l (l = 1..L-1).
 // small: the packed small parameters (W0t[D][128] | b[L][128] | ...), small_acc: their gradient, same layout.
 template <int D>
 __global__ void __launch_bounds__(kDwThreads, 1)
-dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __restrict__ x, long long n, long long lstride,
+dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __restrict__ x, long long n, long long stash_ls, long long lstride,
              const float* __restrict__ stash, const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc,
              int num_blocks, int n1_cta, int pf_dist) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
@@ -120,7 +120,7 @@ dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __res
     const int items = num_blocks > cls.rank ? (num_blocks - cls.rank + cls.count - 1) / cls.count : 0;   // blocks of this CTA
     const int groups = (items + kDwGroup - 1) / kDwGroup;
     const float* zsrc = zb + (size_t)(l - 1) * lstride;
-    const float* ssrc = stash + (size_t)(l > 1 ? l - 2 : 0) * lstride;
+    const float* ssrc = stash + (size_t)(l > 1 ? l - 2 : 0) * stash_ls;
     // block `i` of this CTA: all 8 points exist (then its 8 x D coordinates come by TMA; the one ragged block is read directly)
     auto blk_first = [&](int i) -> long long { return ((long long)cls.rank + (long long)i * cls.count) * kDwPts; };
     const bool x_aligned = (reinterpret_cast<uintptr_t>(x) & 15) == 0;   // cp.async.bulk needs a 16-byte aligned source

@@ -37,7 +37,7 @@ static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u,
     const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
     long long clusters = sms / 2;
     if (pairs < clusters) clusters = pairs;
-    tcp::jet_fwd_tc_kernel<D, STASH><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, 0, (int)pairs);
+    tcp::jet_fwd_tc_kernel<D, STASH><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (long long)((n + 7) / 8) * tcp::kBlkFloats, STASH ? (int)((n + 7) / 8) : 0, (int)pairs);
     e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("jet_fwd_tc_kernel launch: %s (grid %lld, smem %zu)", cudaGetErrorString(e), 2 * clusters, smem); return -4; }
     return 0;
@@ -97,7 +97,7 @@ static int tc_sms() {
 
 template <int D>
 static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
-                  const float* hb, float* stash, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
+                  const float* hb, float* stash, const float* resident, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
     const int sms = tc_sms(), L = Pf.n_hidden;
     const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes();
     cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -113,14 +113,18 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         if (pairs < clusters) clusters = pairs;
         const float* xc = x + c0 * D;
         const int nblk8 = (int)((nc + tcp::kDwPts - 1) / tcp::kDwPts);   // image blocks (8 points) per layer of this chunk
-        {
+        // resident stash (written by the forward of the same inputs, all n points): skip the recomputation and read the
+        // chunk's blocks in place; otherwise recompute this chunk's stash into the workspace
+        const long long stash_ls = resident ? (long long)((n + 7) / 8) * tcp::kBlkFloats : (long long)nblk8 * tcp::kBlkFloats;
+        const float* st = resident ? resident + (size_t)(c0 / tcp::kDwPts) * tcp::kBlkFloats : stash;
+        if (!resident) {
             TcScope t(0, s);
-            tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, nblk8, (int)pairs);
+            tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, stash_ls, nblk8, (int)pairs);
         }
         {
             TcScope t(1, s);
             tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
-                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, stash, zb, small_acc, nblk8, (int)pairs, rev_pf);
+                Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, st, zb, small_acc, stash_ls, nblk8, (int)pairs, rev_pf);
         }
         const long long blocks = nblk8;
         long long want = blocks * (L - 1);                 // every CTA owns one hidden matrix (dw_class)
@@ -133,7 +137,7 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         if (pf_env < 0) { const char* ev = getenv("GPE_DW_PF"); pf_env = ev ? atoi(ev) : tcp::kDwPf; }
         {
             TcScope t(2, s);
-            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, Pf.small, xc, nc, (long long)nblk8 * tcp::kBlkFloats, stash, zb, dWacc, small_acc, nblk8, n0, pf_env);
+            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, Pf.small, xc, nc, stash_ls, (long long)nblk8 * tcp::kBlkFloats, st, zb, dWacc, small_acc, nblk8, n0, pf_env);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }
@@ -152,17 +156,21 @@ size_t tc_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_
 size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd_chunk(n) * 512 * sizeof(float); }
 
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
-                  long long n, const float* ub, const float* gb, const float* hb, float* stash, float* zb, float* dWacc,
-                  float* small_acc, cudaStream_t s) {
+                  long long n, const float* ub, const float* gb, const float* hb, float* stash, const float* resident, float* zb,
+                  float* dWacc, float* small_acc, cudaStream_t s) {
     tcp::TcParams Pf{L, act, wimg_fwd, small, tc_interleave()}, Pr{L, act, wimg_rev, small, tc_interleave()};
     const long long chunk = tc_bwd_chunk(n);
-    return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, zb, dWacc, small_acc, chunk, s)
-                  : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, zb, dWacc, small_acc, chunk, s);
+    return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s)
+                  : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s);
 }
 
+// bytes of a resident stash of ALL n points: st_l image blocks of the hidden matrices l = 1..L-1
+size_t tc_resident_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)((n + 7) / 8) * tcp::kBlkFloats * sizeof(float); }
+
 int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
-                  float* g, float* h, cudaStream_t s) {
+                  float* g, float* h, float* resident, cudaStream_t s) {
     tcp::TcParams P{L, act, wimg, small, tc_interleave()};
+    if (resident) return d == 1 ? fwd_tc<1, true>(P, x, n, u, g, h, resident, s) : fwd_tc<2, true>(P, x, n, u, g, h, resident, s);
     return d == 1 ? fwd_tc<1, false>(P, x, n, u, g, h, nullptr, s) : fwd_tc<2, false>(P, x, n, u, g, h, nullptr, s);
 }
 

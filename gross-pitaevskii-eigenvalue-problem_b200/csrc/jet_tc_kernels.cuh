@@ -130,12 +130,13 @@ __device__ __forceinline__ size_t slot_off(long long p, int g, int tq) {
 }
 
 // STASH: additionally write, for every hidden layer l >= 1, the pre-activation jets {tanh value | a0, z1.., z2} to the
-// image blocks stash[l-1][point / 8] (what the reverse sweep and the dW contraction read back; nblk8 = blocks per layer).
+// image blocks stash[l-1][point / 8] (what the reverse sweep and the dW contraction read back; nblk8 = blocks of this
+// launch, stash_ls = floats per layer of the stash array -- larger than nblk8 * 4096 when the stash of ALL points is resident).
 // Layer 0 is recomputed from x by both consumers.
 template <int D, bool STASH>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* __restrict__ out_u, float* __restrict__ out_g,
-                  float* __restrict__ out_h, float* __restrict__ stash, int nblk8, int num_pairs) {
+                  float* __restrict__ out_h, float* __restrict__ stash, long long stash_ls, int nblk8, int num_pairs) {
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
@@ -256,7 +257,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                             for (int e = 0; e < 2; ++e)
 #pragma unroll
                                 for (int s = 0; s < 4; ++s) sv8[4 * e + s] = s < R ? sv[e][s] : 0.f;
-                            stg_v8(stash + (size_t)(l - 1) * nblk8 * 4096 + slot_off(p, (col0 >> 3) + i, tq), sv8);
+                            stg_v8(stash + (size_t)(l - 1) * stash_ls + slot_off(p, (col0 >> 3) + i, tq), sv8);
                         }
                     }
                     if (l < L - 1) {
@@ -354,7 +355,7 @@ template <int D>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ u_bar,
                   const float* __restrict__ g_bar, const float* __restrict__ h_bar, const float* __restrict__ stash,
-                  float* __restrict__ zb, float* __restrict__ small_acc, int nblk8, int num_pairs, int pf_dist) {
+                  float* __restrict__ zb, float* __restrict__ small_acc, long long stash_ls, int nblk8, int num_pairs, int pf_dist) {
     using tc::cluster_ctarank; using tc::cluster_sync; using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before;
     using tc::tc_fence_after; using tc::tmem_wait_ld; using tc::tmem_wait_st; using tc::mbar_arrive_cluster;
     using tc::mbar_wait_cluster; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit_pair;
@@ -425,20 +426,20 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? g_bar[p * D + i] : 0.f;
             adj[1 + D] = (valid && h_bar) ? h_bar[p] : 0.f;
             if (sub == 0 && tq == 0) dbout_acc += adj[0];
-            const size_t lstride = (size_t)nblk8 * 4096;
+            const size_t lstride = (size_t)nblk8 * 4096;   // zbar chunk buffer: floats per layer
             // L2 bulk prefetch of the stash images one layer ahead of their use (4 image blocks = 64 KB contiguous per
             // tile and layer).  Not further ahead: at ~4.5 TB/s the whole L2 turns over in ~25 us.
             auto prefetch_stash = [&](int l, long long Tt) {
                 const long long bn = ((Tt * 2 + cta) * kTcPts) >> 3;
                 if (Tt < num_pairs && bn < nblk8)
-                    tc::prefetch_l2_bulk(stash + (size_t)(l - 1) * lstride + (size_t)bn * 4096, (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u);
+                    tc::prefetch_l2_bulk(stash + (size_t)(l - 1) * stash_ls + (size_t)bn * 4096, (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u);
             };
             const bool in_blk = (p >> 3) < nblk8;
             // stashed forward jets of (layer l, chunk c) for this thread: one 32-byte slot per 8-column group.  Loaded one
             // chunk ahead (and across the layer boundary) so the load latency hides behind the previous chunk.
             const float* sbase = stash + slot_off(in_blk ? p : 0, sub, tq);
             auto load_stash = [&](int l, int c, float (&dst)[kNI][8]) {
-                const float* sp = sbase + (size_t)(l - 1) * lstride + (size_t)(4 * c) * 256;
+                const float* sp = sbase + (size_t)(l - 1) * stash_ls + (size_t)(4 * c) * 256;
 #pragma unroll
                 for (int i = 0; i < kNI; ++i) ldg_v8(sp + (size_t)i * 256, dst[i]);
             };

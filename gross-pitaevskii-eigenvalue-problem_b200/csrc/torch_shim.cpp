@@ -10,6 +10,9 @@
 // task_should_compute_output), so the parameter-reverse kernel runs exactly once, in the final
 // loss.backward().
 #include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDACachingAllocator.h>
+#include <cuda_runtime_api.h>
+#include <cstdlib>
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/autograd.h>
 #include <torch/library.h>
@@ -144,6 +147,88 @@ std::vector<Tensor> mlp_jet_bwd(const Tensor& x, at::TensorList W, at::TensorLis
 }
 
 // ------------------------------------------------------------------------------------------
+// resident stash (include/gpe_b200.h): the forward keeps the pre-activation jets of ALL points in device
+// memory so the backward does not recompute them.  Policy: used by the autograd node when the stash fits
+// GPE_STASH_MAX_GB (default 128, 0 = never) and 80 % of the memory that is free right now (outside the
+// caching allocator + cached-but-unused blocks inside it); otherwise the backward recomputes chunk by chunk.
+// ------------------------------------------------------------------------------------------
+size_t stash_budget(const at::Device& dev) {
+    static double cap_gb = -1.0;
+    if (cap_gb < 0) {
+        const char* e = std::getenv("GPE_STASH_MAX_GB");
+        cap_gb = e ? std::atof(e) : 128.0;
+    }
+    if (cap_gb <= 0) return 0;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 0;
+    const auto st = c10::cuda::CUDACachingAllocator::getDeviceStats(dev.index());
+    const int64_t cached = st.reserved_bytes[0].current - st.allocated_bytes[0].current;
+    const double avail = (double)free_b + (double)(cached > 0 ? cached : 0);
+    const double cap = cap_gb * 1073741824.0;
+    return (size_t)std::min(cap, 0.8 * avail);
+}
+
+// forward that also fills `stash` (uint8 tensor of gpe_stash_bytes); backward that consumes it
+std::tuple<Tensor, Tensor, Tensor, Tensor> mlp_jet_fwd_stash(const Tensor& x, at::TensorList W, at::TensorList b, int64_t act,
+                                                             int64_t jet, int64_t precision) {
+    gpe_mlp_desc desc = make_desc(x, W, b, act, jet, precision);
+    const int64_t n = x.size(0), d = x.size(1);
+    const int H = jet_hess(d, jet);
+    c10::cuda::CUDAGuard guard(x.device());
+    size_t sb = 0;
+    check_rc(gpe_stash_bytes(&desc, n, &sb), "gpe_stash_bytes");
+    TORCH_CHECK(sb > 0, "gpe_b200: this network/jet has no stash (FFMA path); use mlp_jet_fwd");
+    auto opt = x.options();
+    Tensor u = at::empty({n}, opt), g = at::empty({n, d}, opt), h = at::empty({n, H}, opt);
+    Tensor stash = at::empty({(int64_t)sb}, opt.dtype(at::kByte));
+    size_t fwd = 0, bwd = 0;
+    check_rc(gpe_workspace_bytes(&desc, n, &fwd, &bwd), "gpe_workspace_bytes");
+    Tensor ws = at::empty({(int64_t)std::max<size_t>(fwd, 16)}, opt.dtype(at::kByte));
+    auto Wp = ptrs(W), bp = ptrs(b);
+    auto stream = reinterpret_cast<gpe_stream_t>(at::cuda::getCurrentCUDAStream().stream());
+    check_rc(gpe_mlp_jet_fwd_stash(&desc, Wp.data(), bp.data(), x.data_ptr<float>(), n, u.data_ptr<float>(), g.data_ptr<float>(),
+                                   h.data_ptr<float>(), stash.data_ptr(), sb, ws.data_ptr(), fwd, stream),
+             "gpe_mlp_jet_fwd_stash");
+    return {u, g, h, stash};
+}
+
+std::vector<Tensor> mlp_jet_bwd_stashed(const Tensor& x, at::TensorList W, at::TensorList b, int64_t act, int64_t jet,
+                                        const c10::optional<Tensor>& u_bar, const c10::optional<Tensor>& g_bar,
+                                        const c10::optional<Tensor>& h_bar, const Tensor& stash, int64_t precision) {
+    gpe_mlp_desc desc = make_desc(x, W, b, act, jet, precision);
+    const int64_t n = x.size(0), d = x.size(1);
+    const int H = jet_hess(d, jet);
+    TORCH_CHECK(stash.is_cuda() && stash.scalar_type() == at::kByte && stash.is_contiguous() && stash.device() == x.device(),
+                "gpe_b200: `stash` must be the uint8 CUDA tensor returned by mlp_jet_fwd_stash");
+    auto chk = [&](const c10::optional<Tensor>& t, const char* name, std::vector<int64_t> shape) -> const float* {
+        if (!t.has_value() || !t->defined()) return nullptr;
+        check_f32_cuda(*t, name);
+        TORCH_CHECK(t->sizes().vec() == shape, "gpe_b200: `", name, "` has shape ", t->sizes(), ", expected ", shape);
+        return t->data_ptr<float>();
+    };
+    const float* ub = chk(u_bar, "u_bar", {n});
+    const float* gb = chk(g_bar, "g_bar", {n, d});
+    const float* hb = H ? chk(h_bar, "h_bar", {n, (int64_t)H}) : nullptr;
+    c10::cuda::CUDAGuard guard(x.device());
+    std::vector<Tensor> out;
+    for (const auto& w : W) out.push_back(at::empty_like(w));
+    for (const auto& bb : b) out.push_back(at::empty_like(bb));
+    size_t fwd = 0, bwd = 0;
+    check_rc(gpe_workspace_bytes(&desc, n, &fwd, &bwd), "gpe_workspace_bytes");
+    Tensor ws = at::empty({(int64_t)std::max<size_t>(bwd, 16)}, x.options().dtype(at::kByte));
+    auto Wp = ptrs(W), bp = ptrs(b);
+    std::vector<float*> dWp, dbp;
+    const size_t nl = W.size();
+    for (size_t l = 0; l < nl; ++l) dWp.push_back(out[l].data_ptr<float>());
+    for (size_t l = 0; l < nl; ++l) dbp.push_back(out[nl + l].data_ptr<float>());
+    auto stream = reinterpret_cast<gpe_stream_t>(at::cuda::getCurrentCUDAStream().stream());
+    check_rc(gpe_mlp_jet_bwd_stashed(&desc, Wp.data(), bp.data(), x.data_ptr<float>(), n, ub, gb, hb, stash.data_ptr(),
+                                     (size_t)stash.numel(), dWp.data(), dbp.data(), ws.data_ptr(), bwd, stream),
+             "gpe_mlp_jet_bwd_stashed");
+    return out;
+}
+
+// ------------------------------------------------------------------------------------------
 // gpe::gram_moments / gpe::gram_adjoints  (plain CUDA ops, no autograd)
 // ------------------------------------------------------------------------------------------
 struct LossIn {
@@ -235,16 +320,30 @@ double ffma_probe(int64_t mode, int64_t iters, const Tensor& sink) {
 struct JetFunction : public torch::autograd::Function<JetFunction> {
     // tensor arguments first, so autograd edge index == argument index
     static variable_list forward(AutogradContext* ctx, const Tensor& x, at::TensorList params, int64_t act, int64_t jet,
-                                 int64_t precision, std::vector<double> xa, std::vector<double> xb, bool has_xf) {
+                                 int64_t precision, std::vector<double> xa, std::vector<double> xb, bool has_xf, bool allow_stash) {
         const size_t nl = params.size() / 2;
         at::TensorList W = params.slice(0, nl), b = params.slice(nl, nl);
         c10::optional<at::ArrayRef<double>> oa, ob;
         if (has_xf) oa = at::ArrayRef<double>(xa), ob = at::ArrayRef<double>(xb);
-        auto [u, g, h] = mlp_jet_fwd(x, W, b, act, jet, oa, ob, precision);
+        Tensor u, g, h, stash;
+        bool stashed = false;
+        if (allow_stash && !has_xf && x.size(0) > 0) {   // the caller will differentiate w.r.t. the parameters
+            gpe_mlp_desc desc = make_desc(x, W, b, act, jet, precision);
+            size_t sb = 0;
+            c10::cuda::CUDAGuard guard(x.device());
+            check_rc(gpe_stash_bytes(&desc, x.size(0), &sb), "gpe_stash_bytes");
+            if (sb > 0 && sb <= stash_budget(x.device())) {
+                std::tie(u, g, h, stash) = mlp_jet_fwd_stash(x, W, b, act, jet, precision);
+                stashed = true;
+            }
+        }
+        if (!stashed) std::tie(u, g, h) = mlp_jet_fwd(x, W, b, act, jet, oa, ob, precision);
         variable_list saved{x};
         for (const auto& p : params) saved.push_back(p);
         saved.push_back(g);   // outputs: unpacked with grad_fn = this node, which keeps
         saved.push_back(h);   //   x_bar = u_bar*g + H g_bar differentiable under create_graph
+        if (stashed) saved.push_back(stash);
+        ctx->saved_data["stashed"] = stashed;
         ctx->save_for_backward(saved);
         ctx->saved_data["act"] = act;
         ctx->saved_data["jet"] = jet;
@@ -268,7 +367,7 @@ struct JetFunction : public torch::autograd::Function<JetFunction> {
         const Tensor& h = saved[2 + np];
         const int64_t d = x.size(1);
         const Tensor &ub = grads[0], &gb = grads[1], &hb = grads[2];
-        variable_list out(1 + np + 6);
+        variable_list out(1 + np + 7);
 
         if (ctx->needs_input_grad(0) && jet != GPE_JET_VALUE) {
             // dL/dx from the node's own outputs (plain torch ops: differentiable w.r.t. g and h).
@@ -318,7 +417,9 @@ struct JetFunction : public torch::autograd::Function<JetFunction> {
             };
             c10::optional<at::ArrayRef<double>> oa, ob;
             if (has_xf) oa = at::ArrayRef<double>(xa), ob = at::ArrayRef<double>(xb);
-            auto gr = mlp_jet_bwd(x.detach(), W, b, act, jet, opt_c(ub), opt_c(gb), opt_c(hb), oa, ob, precision);
+            const bool stashed = ctx->saved_data["stashed"].toBool();
+            auto gr = stashed ? mlp_jet_bwd_stashed(x.detach(), W, b, act, jet, opt_c(ub), opt_c(gb), opt_c(hb), saved[3 + np], precision)
+                              : mlp_jet_bwd(x.detach(), W, b, act, jet, opt_c(ub), opt_c(gb), opt_c(hb), oa, ob, precision);
             for (int64_t i = 0; i < np; ++i) out[1 + i] = gr[i];
         }
         return out;
@@ -343,7 +444,12 @@ std::tuple<Tensor, Tensor, Tensor> mlp_jets(const Tensor& x, at::TensorList W, a
         if (xa.has_value() && i < (int)xa->size()) va[i] = (*xa)[i];
         if (xb.has_value() && i < (int)xb->size()) vb[i] = (*xb)[i];
     }
-    auto out = JetFunction::apply(x, at::TensorList(params), act, jet, precision, va, vb, has_xf);
+    bool allow_stash = at::GradMode::is_enabled();
+    if (allow_stash) {
+        allow_stash = false;
+        for (const auto& p : params) allow_stash = allow_stash || p.requires_grad();
+    }
+    auto out = JetFunction::apply(x, at::TensorList(params), act, jet, precision, va, vb, has_xf, allow_stash);
     return {out[0], out[1], out[2]};
 }
 
@@ -356,6 +462,9 @@ TORCH_LIBRARY(gpe, m) {
           "float[]? xform_a=None, float[]? xform_b=None, int precision=2) -> Tensor[]");
     m.def("mlp_jets(Tensor x, Tensor[] W, Tensor[] b, int act, int jet, float[]? xform_a=None, float[]? xform_b=None, "
           "int precision=2) -> (Tensor, Tensor, Tensor)");
+    m.def("mlp_jet_fwd_stash(Tensor x, Tensor[] W, Tensor[] b, int act, int jet, int precision=2) -> (Tensor, Tensor, Tensor, Tensor)");
+    m.def("mlp_jet_bwd_stashed(Tensor x, Tensor[] W, Tensor[] b, int act, int jet, Tensor? u_bar, Tensor? g_bar, Tensor? h_bar, "
+          "Tensor stash, int precision=2) -> Tensor[]");
     m.def("gram_moments(Tensor? x, Tensor u, Tensor? g, Tensor? h, Tensor? base, Tensor? V, Tensor? q, Tensor? nm, int d, "
           "int nl_kind, float nl_power, float scale, int bfactor, int sym_sign, int lap_cols) -> Tensor");
     m.def("gram_adjoints(Tensor? x, Tensor u, Tensor? g, Tensor? h, Tensor? base, Tensor? V, Tensor? q, Tensor? nm, int d, "
@@ -367,6 +476,8 @@ TORCH_LIBRARY(gpe, m) {
 TORCH_LIBRARY_IMPL(gpe, CUDA, m) {
     m.impl("mlp_jet_fwd", &mlp_jet_fwd);
     m.impl("mlp_jet_bwd", &mlp_jet_bwd);
+    m.impl("mlp_jet_fwd_stash", &mlp_jet_fwd_stash);
+    m.impl("mlp_jet_bwd_stashed", &mlp_jet_bwd_stashed);
     m.impl("gram_moments", &gram_moments);
     m.impl("gram_adjoints", &gram_adjoints);
     m.impl("ffma_probe", &ffma_probe);

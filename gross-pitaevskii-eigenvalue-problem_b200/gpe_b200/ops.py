@@ -71,11 +71,28 @@ def mlp_jet_bwd(x: torch.Tensor, Ws: Sequence[torch.Tensor], bs: Sequence[torch.
     return list(out[:n]), list(out[n:])
 
 
+def mlp_jet_fwd_stash(x: torch.Tensor, Ws: Sequence[torch.Tensor], bs: Sequence[torch.Tensor], act: int, jet: int,
+                      precision: int = PREC_AUTO):
+    """(u, g, h, stash): the forward that also keeps the pre-activation jets of all points (uint8 tensor of
+    gpe_stash_bytes; tensor path only) for `mlp_jet_bwd_stashed` -- memory instead of recomputation."""
+    return _ops.mlp_jet_fwd_stash(x, list(Ws), list(bs), act, jet, precision)
+
+
+def mlp_jet_bwd_stashed(x: torch.Tensor, Ws: Sequence[torch.Tensor], bs: Sequence[torch.Tensor], act: int, jet: int,
+                        u_bar: Optional[torch.Tensor], g_bar: Optional[torch.Tensor], h_bar: Optional[torch.Tensor],
+                        stash: torch.Tensor, precision: int = PREC_AUTO):
+    """`mlp_jet_bwd` from the stash of `mlp_jet_fwd_stash` (same x, Ws, bs)."""
+    out = _ops.mlp_jet_bwd_stashed(x, list(Ws), list(bs), act, jet, u_bar, g_bar, h_bar, stash, precision)
+    n = len(Ws)
+    return list(out[:n]), list(out[n:])
+
+
 def mlp_jets(x: torch.Tensor, Ws: Sequence[torch.Tensor], bs: Sequence[torch.Tensor], act: int, jet: int,
              xform=None, precision: int = PREC_AUTO):
     """Differentiable (u [N], g [N,d], h [N,H]).  Gradients w.r.t. the parameters come from the
     reverse kernel; gradients w.r.t. x are assembled from g and h, so nested
-    `torch.autograd.grad(u, x, create_graph=True)` calls reproduce the reference idiom."""
+    `torch.autograd.grad(u, x, create_graph=True)` calls reproduce the reference idiom.  When the parameters require grad and the stash of all points fits
+    (GPE_STASH_MAX_GB, default 128; 80 % of the free device memory), the node keeps it between forward and backward."""
     xa, xb = _xf(xform)
     return _ops.mlp_jets(x, list(Ws), list(bs), act, jet, xa, xb, precision)
 

@@ -86,6 +86,22 @@ int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float
                     int64_t n, const gpe_xform* xform, const float* u_bar, const float* g_bar, const float* h_bar,
                     float* const* dW, float* const* db, void* ws, size_t ws_bytes, gpe_stream_t stream);
 
+/* ---- resident stash (memory for recompute) --------------------------------------------------
+ * loss.backward() in the reference re-uses the activations autograd saved during the forward
+ * (NBroot cell 10:100, S/gross_pitaevskii_2D.py:376).  gpe_mlp_jet_bwd recomputes them chunk by chunk
+ * instead.  Where the caller can keep gpe_stash_bytes() of device memory alive between the forward and the
+ * backward call of the SAME x, W, b (6 KB per point for [2,128x4,1]: 103 GB at 16M points, a B200 has
+ * 180 GB), the forward writes the pre-activation jets once and the backward skips the recomputation.
+ * *bytes = 0: this descriptor has no stash (FFMA path) -- use the plain calls. */
+int gpe_stash_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* bytes);
+int gpe_mlp_jet_fwd_stash(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
+                          int64_t n, float* u, float* g, float* h, void* stash, size_t stash_bytes, void* ws,
+                          size_t ws_bytes, gpe_stream_t stream);
+int gpe_mlp_jet_bwd_stashed(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
+                            int64_t n, const float* u_bar, const float* g_bar, const float* h_bar, const void* stash,
+                            size_t stash_bytes, float* const* dW, float* const* db, void* ws, size_t ws_bytes,
+                            gpe_stream_t stream);
+
 /* ---- fused loss epilogue ------------------------------------------------------------------
  * Full solution per point (1-D factor forms follow R/box_pinn_simulation.py:119-180):
  *     u   = base0 + s * F(x) * N

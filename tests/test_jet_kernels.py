@@ -177,3 +177,26 @@ def test_tensor_and_ffma_paths(d, W, L, act, jet, n):
         assert rel_err(grads, ref) < TOL, name
     for a, b in zip(out["tensor"][:3], out["ffma"][:3]):
         assert rel_err(a, b) < TOL
+
+
+@pytest.mark.parametrize("d,W,L,n", [(2, 128, 4, 70001), (1, 100, 3, 4099), (2, 128, 2, 13)])
+def test_resident_stash_matches_recompute(d, W, L, n):
+    """gpe_mlp_jet_fwd_stash + gpe_mlp_jet_bwd_stashed (memory) against gpe_mlp_jet_fwd + gpe_mlp_jet_bwd (recompute):
+    the same kernels on the same numbers -- jets bit-identical, gradients equal up to the order of the fp32 atomics."""
+    from gpe_b200 import ops
+    Ws, bs = make_net(d, W, L, seed=3, act=ops.ACT_TANH)
+    Ws, bs = [w.cuda() for w in Ws], [b.cuda() for b in bs]
+    x = points(n, d, seed=5).cuda()
+    jet = ops.JET_LAPLACIAN
+    u0, g0, h0 = ops.mlp_jet_fwd(x, Ws, bs, ops.ACT_TANH, jet)
+    u1, g1, h1, stash = ops.mlp_jet_fwd_stash(x, Ws, bs, ops.ACT_TANH, jet)
+    assert torch.equal(u0, u1) and torch.equal(g0, g1) and torch.equal(h0, h1)
+    assert stash.dtype == torch.uint8 and stash.numel() == (L - 1) * ((n + 7) // 8) * 16384
+    torch.manual_seed(1)
+    ub, gb, hb = torch.randn(n, device="cuda"), torch.randn(n, d, device="cuda"), torch.randn(n, 1, device="cuda")
+    dW0, db0 = ops.mlp_jet_bwd(x, Ws, bs, ops.ACT_TANH, jet, ub, gb, hb)
+    dW1, db1 = ops.mlp_jet_bwd_stashed(x, Ws, bs, ops.ACT_TANH, jet, ub, gb, hb, stash)
+    for a, b in zip(dW0 + db0, dW1 + db1):
+        assert rel_err(a.cpu(), b.cpu()) < 2e-6
+    with pytest.raises(RuntimeError):   # a stash of the wrong size is refused, not read out of bounds
+        ops.mlp_jet_bwd_stashed(x, Ws, bs, ops.ACT_TANH, jet, ub, gb, hb, stash[:-16384].contiguous())
