@@ -152,10 +152,12 @@ KERNELS_PER_STEP = 12   # FFMA path: 2x(pack_weights + jet_fwd) + gram_moments +
 TC_CHUNK = 262144       # points per (stash forward, reverse sweep, dW) round of the tensor-path backward
 
 
-def kernels_per_step(n, tensor):
+def kernels_per_step(n, tensor, resident=False):
     if not tensor:
         return KERNELS_PER_STEP
     chunks = (n + TC_CHUNK - 1) // TC_CHUNK
+    if resident:   # the loss forward writes the stash: 2 kernels per chunk in the backward
+        return 2 + 3 + 2 + 3 + 4 + 2 * chunks
     # boundary fwd (pack + jet_fwd) + main fwd (pack + pack_wimg + fwd_tc) + moments + adjoints
     # + boundary bwd (pack + jet_bwd + finish) + main bwd (pack + 2 pack_wimg + 3 per chunk + finish)
     # (torch's own elementwise/reduction launches for the fp64 scalar algebra are not counted)
@@ -292,6 +294,8 @@ def run_b200(args):
             "config": {"workload": "BASELINE config 4: 2-D GPE harmonic trap eta=100, tanh MLP [2,128x4,1], N_f=16M LHS per GPU, "
                                    "loss = 10*bc + pde(+L_f+L_lambda) + Riesz, pointwise semantics",
                        "layers": LAYERS, "points_per_gpu": n, "boundary_points": N_BC, "parallelism": f"points-dp{world}",
+                       "stash": "resident (forward keeps 6 KB/point of pre-activation jets, backward does not recompute)"
+                                if (tensor and tc_ms and tc_ms.get("stash_forward", 1.0) == 0.0) else "recomputed per chunk in the backward",
                        "l2_policy": "inputs (128 MB of points + 512 MB of jets/adjoints per step) exceed the 126 MB L2",
                        "collectives_per_step": 0 if world == 1 else 2},
             "phase_ms": {"forward_and_losses": fwd_ms, "backward": bwd_ms},
@@ -308,7 +312,7 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": X_host.numel() * 4 * world, "d2h_bytes_per_step": 4 * world,
                     "includes": "pinned-host -> device copy of the collocation block, loss, backward, all-reduce, Adam step, loss read-back",
                     "last_loss": last},
-            "gpu_launches": kernels_per_step(n, tensor) * args.steps,
+            "gpu_launches": kernels_per_step(n, tensor, bool(tc_ms) and tc_ms.get("stash_forward", 1.0) == 0.0) * args.steps,
             "clocks": clocks, "loss": float(loss),
         }
         if tensor and tc_ms and max(tc_ms.values()) > 0:
