@@ -177,6 +177,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) off it
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     n = args.points
     model = init_weights(gpe_b200.GPE2D(LAYERS, g=ETA, potential="harmonic", semantics="pointwise")).to(dev)
@@ -252,7 +255,7 @@ def run_b200(args):
         loss.backward()
         gdist.all_reduce_gradients(params)
         opt.step()
-        return float(loss)            # device -> host read of the step's result
+        return float(loss.detach())   # device -> host read of the step's result
 
     saved = {k: v.clone() for k, v in model.state_dict().items()}
     for _ in range(2):
@@ -313,7 +316,7 @@ def run_b200(args):
                     "includes": "pinned-host -> device copy of the collocation block, loss, backward, all-reduce, Adam step, loss read-back",
                     "last_loss": last},
             "gpu_launches": kernels_per_step(n, tensor, bool(tc_ms) and tc_ms.get("stash_forward", 1.0) == 0.0) * args.steps,
-            "clocks": clocks, "loss": float(loss),
+            "clocks": clocks, "loss": float(loss.detach()),
         }
         if tensor and tc_ms and max(tc_ms.values()) > 0:
             d, W, L = LAYERS[0], LAYERS[1], len(LAYERS) - 2
