@@ -303,6 +303,9 @@ def run_b200(args):
                        "collectives_per_step": 0 if world == 1 else 2},
             "phase_ms": {"forward_and_losses": fwd_ms, "backward": bwd_ms},
             "step_tflops_algorithmic": f_step * n / (ms_per_step * 1e-3) / 1e12,
+            # the whole step against the FP32 FFMA roofline the reference's arithmetic (fp32) would be bound by: > 1 because
+            # the contractions run as 3xTF32 on the tensor cores
+            "step_frac_of_fp32_ffma_peak": f_step * n / (ms_per_step * 1e-3) / 1e12 / fp32_peak,
             "roofline": None,
             "roofline_ffma": {"bound": "fp32", "kernel": "jet_bwd_kernel<2,LAPLACIAN,128>", "achieved": bwd_alg, "peak": fp32_peak,
                          "unit": "TFLOP/s", "frac": bwd_alg / fp32_peak,
