@@ -105,7 +105,7 @@ std::mutex g_plan_mu;
 PlanEntry g_plans[64];
 int g_n_plans = 0;
 
-int padded_width(int w) { return w <= 64 ? 64 : w <= 128 ? 128 : 0; }
+int padded_width(int w) { return w <= 64 ? 64 : w <= 128 ? 128 : w <= 256 ? 256 : 0; }
 
 int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
     if (!desc) { set_error("null descriptor"); return -1; }
@@ -114,7 +114,7 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
     if (desc->act < 0 || desc->act > 2) { set_error("unknown activation %d", desc->act); return -1; }
     if (desc->jet < 0 || desc->jet > 3) { set_error("unknown jet kind %d", desc->jet); return -1; }
     const int wp = padded_width(desc->width);
-    if (desc->width < 1 || !wp) { set_error("hidden width %d unsupported (1..128)", desc->width); return -1; }
+    if (desc->width < 1 || !wp) { set_error("hidden width %d unsupported (1..256)", desc->width); return -1; }
     int dev = -1;
     if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device (this library has no CPU fallback)"); return -2; }
     *wp_out = wp;
@@ -127,7 +127,9 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
         }
     }
     JetPlan p;
-    const int rc = wp == 64 ? plan_wp64(desc->d, desc->jet, desc->n_hidden, &p) : plan_wp128(desc->d, desc->jet, desc->n_hidden, &p);
+    const int rc = wp == 64    ? plan_wp64(desc->d, desc->jet, desc->n_hidden, &p)
+                   : wp == 128 ? plan_wp128(desc->d, desc->jet, desc->n_hidden, &p)
+                               : plan_wp256(desc->d, desc->jet, desc->n_hidden, &p);
     if (rc) return rc;
     if (g_n_plans < 64) g_plans[g_n_plans++] = PlanEntry{PlanKey{desc->d, desc->jet, wp, desc->n_hidden, dev}, p};
     *out = p;
@@ -308,8 +310,9 @@ static int jet_fwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
         return launch_fwd_tc(desc->d, desc->n_hidden, desc->act, wimg, P.small, x, n, u, g, h, resident, s);
     }
     if (resident) { set_error("this descriptor has no stash (gpe_stash_bytes = 0): use gpe_mlp_jet_fwd"); return -1; }
-    rc = wp == 64 ? launch_fwd_wp64(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s)
-                  : launch_fwd_wp128(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s);
+    rc = wp == 64    ? launch_fwd_wp64(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s)
+         : wp == 128 ? launch_fwd_wp128(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s)
+                     : launch_fwd_wp256(desc->d, desc->jet, P, x, n, xf, u, g, h, w.grid_fwd, w.tiles, s);
     if (rc) return rc;
     return check_launch("jet_fwd_kernel");
 }
@@ -379,12 +382,12 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
         if (rc) return rc;
     } else if (n > 0) {
         if (resident) { set_error("this descriptor has no stash (gpe_stash_bytes = 0): use gpe_mlp_jet_bwd"); return -1; }
-        rc = wp == 64 ? launch_bwd_wp64(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, reinterpret_cast<float*>(base + w.stash),
-                                        reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc),
-                                        w.grid_bwd, w.tiles, s)
-                      : launch_bwd_wp128(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, reinterpret_cast<float*>(base + w.stash),
-                                         reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc),
-                                         w.grid_bwd, w.tiles, s);
+        float* st = reinterpret_cast<float*>(base + w.stash);
+        float* da = reinterpret_cast<float*>(base + w.dWacc);
+        float* sa = reinterpret_cast<float*>(base + w.small_acc);
+        rc = wp == 64    ? launch_bwd_wp64(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, st, da, sa, w.grid_bwd, w.tiles, s)
+             : wp == 128 ? launch_bwd_wp128(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, st, da, sa, w.grid_bwd, w.tiles, s)
+                         : launch_bwd_wp256(desc->d, desc->jet, P, x, n, xf, u_bar, g_bar, h_bar, st, da, sa, w.grid_bwd, w.tiles, s);
         if (rc) return rc;
         if ((rc = check_launch("jet_bwd_kernel"))) return rc;
     }

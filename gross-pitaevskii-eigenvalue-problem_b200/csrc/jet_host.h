@@ -32,6 +32,7 @@ struct JetPlan {          // resolved launch geometry for (d, jet, WP, L)
                           float* small_acc, int grid, int num_tiles, cudaStream_t s);
 GPE_DECL_WP(64)
 GPE_DECL_WP(128)
+GPE_DECL_WP(256)
 #undef GPE_DECL_WP
 
 void set_error(const char* fmt, ...);

@@ -71,6 +71,9 @@ CASES = [
     (2, 128, 2, 0, 2, 999),
     (2, 100, 3, 2, 3, 800),
     (2, 64, 1, 0, 3, 100),
+    (2, 200, 3, 0, 3, 700),     # the reference's own Helmholtz default [2,200,200,200,1] (S/helmholtz_2D.py:378): WP = 256
+    (2, 200, 3, 2, 2, 333),     # ... with its LeakyReLU and the full Hessian
+    (1, 256, 2, 0, 1, 129),
     (2, 50, 5, 0, 0, 31),
     (1, 8, 2, 0, 1, 1),
 ]

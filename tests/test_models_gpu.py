@@ -219,3 +219,23 @@ def test_cpu_tensor_raises():
     model = gpe_b200.RootGPE1D([1, 16, 16, 1])
     with pytest.raises(RuntimeError):
         model.forward(torch.zeros(4, 1))
+
+
+def test_helmholtz_reference_default_width_200():
+    """The reference's own main (S/helmholtz_2D.py:378) uses [2,200,200,200,1] with LeakyReLU: hidden width padded to
+    256 (FFMA kernels).  Loss (reference [N,N] semantics) and gradients against the fp64 oracle on the same weights."""
+    import gpe_b200
+    torch.manual_seed(0)
+    layers = [2, 200, 200, 200, 1]
+    ref = po.Helmholtz2D(layers).double()
+    gpu = gpe_b200.Helmholtz2D(layers, semantics="reference")
+    gpu.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    gpu = gpu.cuda()
+    X = torch.rand(500, 2, dtype=torch.float64) * np.pi
+    Xu, U = torch.rand(80, 2, dtype=torch.float64) * np.pi, torch.rand(80, 1, dtype=torch.float64)
+    k = float(np.sqrt(2) * np.pi)
+    lr = ref.compute_loss(X.clone().requires_grad_(True), Xu, U, k)
+    lg = gpu.compute_loss(X.float().cuda().requires_grad_(True), Xu.float().cuda(), U.float().cuda(), k)
+    assert close(lg, lr)
+    gr = [p.grad.numpy() for p in ref.parameters()] if lr.backward() is None else None
+    assert rel_err(flat(model_grads(gpu, lg)), flat(gr)) < GTOL
