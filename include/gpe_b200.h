@@ -55,7 +55,7 @@ enum { GPE_PREC_FP32 = 0, GPE_PREC_TF32X3 = 1, GPE_PREC_AUTO = 2 };
 typedef struct {
     int d;        /* input dimension: 1 or 2                                     */
     int n_hidden; /* L: number of hidden layers (>= 1, <= 8)                      */
-    int width;    /* W: hidden width, uniform, <= 128                             */
+    int width;    /* W: hidden width, uniform, <= 256                             */
     int act;      /* GPE_ACT_*                                                    */
     int jet;      /* GPE_JET_*                                                    */
     int precision; /* GPE_PREC_*: arithmetic of the hidden-layer contractions      */
