@@ -164,3 +164,44 @@ def test_baseline_size_forward_is_pointwise():
     idx = torch.randint(0, n, (5000,), device="cuda")
     u2, g2, h2 = ops.mlp_jet_fwd(x[idx].contiguous(), Ws, bs, 0, ops.JET_LAPLACIAN)
     assert torch.equal(u[idx], u2) and torch.equal(g[idx], g2) and torch.equal(h[idx], h2)
+
+
+def test_cuda_graph_replay_of_a_training_step():
+    """gpe_b200.graphs.GraphedStep: the root-notebook loop body (NBroot cell 10:88-100) incl. clip + Adam captured once
+    and replayed; the replayed trajectory follows the eager one (same kernels; fp32 atomics order may differ)."""
+    import gpe_b200
+    from gpe_b200.graphs import GraphedStep
+    layers, lb, ub, n, gamma, p = [1, 100, 100, 100, 1], -10.0, 10.0, 4000, 1.0, 3
+    X = torch.linspace(lb, ub, n, device="cuda").view(-1, 1).requires_grad_(True)
+    dx = (ub - lb) / (n - 1)
+    bp, bv = torch.tensor([[lb], [ub]], device="cuda"), torch.zeros(2, 1, device="cuda")
+    hist = {}
+    for mode in ("eager", "graph"):
+        model = _xavier(gpe_b200.RootGPE1D(layers, mode=0, gamma=gamma), 2).cuda()
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3, capturable=True)
+
+        def body():
+            opt.zero_grad(set_to_none=False)
+            total, pde, bc, nrm, sym, mu = po.root_train_terms(model, X, bp, bv, dx, gamma, p, lb, ub)
+            total.backward()
+            torch.nn.utils.clip_grad_norm_(model.parameters(), max_norm=1.0)
+            opt.step()
+            return total.detach(), mu.detach()
+
+        if mode == "graph":
+            state = {k: v.clone() for k, v in model.state_dict().items()}
+            step = GraphedStep(body, opt, warmup=3)        # warm-up + capture run the body 4 times: rewind
+            model.load_state_dict(state)
+            for st in opt.state.values():                  # reset Adam's step / moments in place (the graph holds these buffers)
+                for v in st.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+        else:
+            step = body
+        out = []
+        for _ in range(8):
+            total, mu = step()
+            out.append((float(total), float(mu)))
+        hist[mode] = np.array(out)
+    assert np.isfinite(hist["graph"]).all()
+    assert rel_err(hist["graph"], hist["eager"]) < 1e-4, (hist["graph"][-1], hist["eager"][-1])
