@@ -165,6 +165,12 @@ def kernels_per_step(n, tensor, resident=False):
 
 
 def run_b200(args):
+    # stdout carries exactly ONE JSON line: native libraries write to fd 1 behind python's back (NCCL prints its
+    # "NCCL version ..." banner there at communicator creation), so fd 1 is pointed at stderr for the run and the line
+    # goes to the saved descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch.distributed as dist
     import gpe_b200
     from gpe_b200 import collocation, distributed as gdist, ops
@@ -177,9 +183,6 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) off it
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     n = args.points
     model = init_weights(gpe_b200.GPE2D(LAYERS, g=ETA, potential="harmonic", semantics="pointwise")).to(dev)
@@ -358,7 +361,8 @@ def run_b200(args):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{args.cpu_points} of the 16M points per step x 3 steps, oracle/pinn_oracle.GPE2D "
                                               "(restated reference class) on the host cores"}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 
