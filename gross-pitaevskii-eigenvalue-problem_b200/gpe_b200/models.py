@@ -227,6 +227,21 @@ def box_base_jets(x, n, length):
     return torch.stack([c * s, c * k * co, -c * k * k * s], dim=1).float().contiguous()
 
 
+def airy_base_jets(x, n):
+    """[N,3] = (psi, psi', psi'') of the gravity-well base psi_n = Ai(x + alpha_n) / sqrt(sum(Ai^2) dx), exactly as
+    R/gravity_well_pinn_simulation.py:135-160 builds it: scipy on the host in fp64, dx = x[1] - x[0] of the grid it is
+    given, psi'' = np.gradient(psi', dx) (a finite difference, not the Airy equation), cast to float32.  The host
+    round trip is the reference's own; it is O(N) and outside the timed kernels."""
+    from scipy.special import ai_zeros, airy
+    xn = x.detach().reshape(-1).cpu().numpy()
+    ai_val, aip_val, _, _ = airy(xn + ai_zeros(n + 1)[0][n])
+    dx = xn[1] - xn[0] if len(xn) > 1 else 0.01
+    nf = np.sqrt(np.sum(ai_val ** 2) * dx)
+    d2 = np.gradient(aip_val / nf, dx) if len(xn) > 1 else np.zeros_like(aip_val)
+    out = np.stack([ai_val / nf, aip_val / nf, d2], axis=1).astype(np.float32)
+    return torch.from_numpy(out).to(x.device).contiguous()
+
+
 class _GPE1DBase(JetMLP):
     def _pde_outputs(self, inputs, base, V, scale, kinetic, eta, nl_kind, p, mu_kind, bfactor=0):
         """Shared fused pde_loss: returns (mse, mu, Moments)."""
@@ -323,7 +338,8 @@ class RootGPE1D(_GPE1DBase):
 
 class FinalGPE1D(_GPE1DBase):
     """`GrossPitaevskiiPINN(layers, hbar, m, mode, gamma, use_perturbation)` of
-    R/harmonic_pinn_simulation.py:52-217; `potential='box'` follows R/box_pinn_simulation.py:52-262."""
+    R/harmonic_pinn_simulation.py:52-217; `potential='box'` follows R/box_pinn_simulation.py:52-262,
+    `potential='gravity_well'` R/gravity_well_pinn_simulation.py:53-256 (Airy base, V = x)."""
 
     def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, use_perturbation=True, potential="harmonic", L=1.0):
         super().__init__()
@@ -344,8 +360,13 @@ class FinalGPE1D(_GPE1DBase):
             out = out * torch.sin(torch.pi * inputs)
         return out
 
+    def airy_solution(self, x, n):
+        return airy_base_jets(x, n)[:, :1]
+
     def _base(self, x, n=None):
         n = self.mode if n is None else n
+        if self.potential == "gravity_well":
+            return airy_base_jets(x, n)
         return box_base_jets(x, n, self.L) if self.potential == "box" else hermite_base_jets(x, n, const_h=False)
 
     def get_complete_solution(self, x, perturbation, mode=None):
@@ -356,6 +377,8 @@ class FinalGPE1D(_GPE1DBase):
             return x ** 2
         if potential_type == "box":          # R/box_pinn_simulation.py:182-190
             return torch.zeros_like(x)
+        if potential_type == "gravity_well":  # R/gravity_well_pinn_simulation.py:175-184
+            return x.clone()
         raise ValueError(f"Unknown potential type: {potential_type}")
 
     def pde_loss(self, inputs, predictions, gamma, p, potential_type=None, precomputed_potential=None):

@@ -176,7 +176,9 @@ def root_train_terms(model, X, boundary_points, boundary_values, dx, gamma, powe
 class FinalGPE1D(nn.Module):
     """R/harmonic_pinn_simulation.py:52-217 `GrossPitaevskiiPINN(layers, hbar, m, mode, gamma,
     use_perturbation)`; `potential='box'` follows R/box_pinn_simulation.py:52-262 (sin(pi x)
-    boundary factor in forward, analytic base derivatives)."""
+    boundary factor in forward, analytic base derivatives); `potential='gravity_well'` follows
+    R/gravity_well_pinn_simulation.py:53-256 (Airy base from scipy on the host, normalised on the grid it is
+    given, its second derivative by np.gradient; V = x)."""
 
     def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, use_perturbation=True,
                  potential="harmonic", L=1.0):
@@ -194,6 +196,17 @@ class FinalGPE1D(nn.Module):
         """R/box_pinn_simulation.py:99-117."""
         return torch.sqrt(torch.tensor(2.0 / self.L)) * torch.sin((n + 1) * torch.pi * x / self.L)
 
+    def airy_solution(self, x, n):
+        """R/gravity_well_pinn_simulation.py:97-118: Ai(x + alpha_n) / sqrt(sum(Ai^2) dx), dx from the points given
+        (also for the two boundary points), float32 result whatever the dtype of x."""
+        from scipy.special import ai_zeros, airy
+        x_np = x.detach().cpu().numpy()
+        alpha_n = ai_zeros(n + 1)[0][n]
+        psi = airy(x_np + alpha_n)[0]
+        dx = x_np[1] - x_np[0] if len(x_np) > 1 else 0.01
+        psi = psi / np.sqrt(np.sum(psi ** 2) * dx)
+        return torch.tensor(psi, dtype=torch.float32).to(x.device)
+
     def forward(self, inputs):
         out = self.network(inputs)
         if self.potential == "box":                      # R/box_pinn_simulation.py:119-130
@@ -202,6 +215,8 @@ class FinalGPE1D(nn.Module):
 
     def get_complete_solution(self, x, perturbation, mode=None):
         n = self.mode if mode is None else mode
+        if self.potential == "gravity_well":
+            return self.airy_solution(x, n) + perturbation
         base = self.box_eigenfunction(x, n) if self.potential == "box" else self.weighted_hermite(x, n)
         return base + perturbation
 
@@ -210,6 +225,8 @@ class FinalGPE1D(nn.Module):
             return x ** 2
         if potential_type == "box":                      # R/box_pinn_simulation.py:182-190
             return torch.zeros_like(x)
+        if potential_type == "gravity_well":             # R/gravity_well_pinn_simulation.py:175-184
+            return x.clone()
         raise ValueError(f"Unknown potential type: {potential_type}")
 
     def _jets(self, inputs, predictions):
@@ -226,12 +243,24 @@ class FinalGPE1D(nn.Module):
             p_x = d_dx(predictions, inputs)
             p_xx = d_dx(p_x, inputs)
             return b0 + predictions, b1 + p_x, b2 + p_xx
+        if self.potential == "gravity_well":             # R/gravity_well_pinn_simulation.py:135-173
+            from scipy.special import ai_zeros, airy
+            xn = inputs.detach().cpu().numpy().flatten()
+            ai_val, aip_val, _, _ = airy(xn + ai_zeros(self.mode + 1)[0][self.mode])
+            dx = xn[1] - xn[0] if len(xn) > 1 else 0.01
+            nf = np.sqrt(np.sum(ai_val ** 2) * dx)
+            as_col = lambda a: torch.tensor(a, dtype=torch.float32).reshape(-1, 1).to(inputs.device)
+            b0, b1, b2 = as_col(ai_val / nf), as_col(aip_val / nf), as_col(np.gradient(aip_val / nf, dx))
+            p_x = d_dx(predictions, inputs)
+            p_xx = d_dx(p_x, inputs)
+            return b0 + predictions, b1 + p_x, b2 + p_xx
         u = self.get_complete_solution(inputs, predictions)
         u_x = d_dx(u, inputs)
         return u, u_x, d_dx(u_x, inputs)
 
     def pde_loss(self, inputs, predictions, gamma, p, potential_type=None, precomputed_potential=None):
-        """R/harmonic_pinn_simulation.py:146-196: Hu = -u'' + V u + gamma u**p."""
+        """R/harmonic_pinn_simulation.py:146-196: Hu = -u'' + V u + gamma u**p.  (The gravity-well script forms
+        mu as sum/sum, :227-229 -- the same number.)"""
         potential_type = potential_type or self.potential
         u, _, u_xx = self._jets(inputs, predictions)
         V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)

@@ -100,12 +100,20 @@ def case_final_fixture(kind):
         mod = rl.load_script("final/refine/harmonic_pinn_simulation.py")
         data = rl.load_pickle("harmonic_test/harmonic_mode_zero_plot_data.pkl")
         lb, ub, ptype = -10.0, 10.0, "harmonic"
-    else:
+    elif kind == "box":
         mod = rl.load_script("final/refine/box_pinn_simulation.py")
         data = rl.load_pickle("box_test/box_mode_zero_plot_data.pkl")
         lb, ub, ptype = 0.0, 1.0, "box"
+    else:
+        mod = rl.load_script("final/refine/gravity_well_pinn_simulation.py")
+        data = rl.load_pickle("gravity_well_test/gravity_well_zero_plot_data.pkl")
+        lb, ub, ptype = 0.0, 35.0, "gravity_well"
     mod.device = torch.device("cpu")
     Xn = np.linspace(lb, ub, 4000).reshape(-1, 1)
+    if kind == "gravity_well":
+        # the Airy base's second derivative is np.gradient on the grid it is given: the float64 run must see the same
+        # (float32-representable) abscissae as a float32 run, or the two differ by the grid's rounding jitter / dx
+        Xn = Xn.astype(np.float32).astype(np.float64)
     dx = float(Xn[1, 0] - Xn[0, 0])
     out = dict(X=Xn, dx=dx, lb=lb, ub=ub, perturb_const=0.01)
     for mode in range(6):
@@ -133,11 +141,14 @@ def case_final_fixture(kind):
 
 
 def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic"):
-    script = "final/refine/harmonic_pinn_simulation.py" if kind == "harmonic" else "final/refine/box_pinn_simulation.py"
+    script = {"harmonic": "final/refine/harmonic_pinn_simulation.py", "box": "final/refine/box_pinn_simulation.py",
+              "gravity_well": "final/refine/gravity_well_pinn_simulation.py"}[kind]
     mod = rl.load_script(script)
     mod.device = torch.device("cpu")
-    lb, ub = (-10.0, 10.0) if kind == "harmonic" else (0.0, 1.0)
+    lb, ub = {"harmonic": (-10.0, 10.0), "box": (0.0, 1.0), "gravity_well": (0.0, 35.0)}[kind]
     Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
+    if kind == "gravity_well":
+        Xn = Xn.astype(np.float32).astype(np.float64)      # see case_final_fixture
     dx = float(Xn[1, 0] - Xn[0, 0])
     const, pc = 0.37, 0.01
 
@@ -259,6 +270,8 @@ def main():
         "final_harmonic_g20_p3_m1": lambda: case_final_random(20.0, 3, 1, [1, 64, 64, 64, 1], 900),
         "final_harmonic_g5_p4_m2": lambda: case_final_random(5.0, 4, 2, [1, 48, 48, 1], 500),
         "final_box_g10_p3_m0": lambda: case_final_random(10.0, 3, 0, [1, 64, 64, 64, 1], 800, kind="box"),
+        "final_gravity_fixture": lambda: case_final_fixture("gravity_well"),
+        "final_gravity_g10_p3_m1": lambda: case_final_random(10.0, 3, 1, [1, 64, 64, 64, 1], 1200, kind="gravity_well"),
         "opt_m0_eta10": lambda: case_opt(0, 10.0, [1, 64, 64, 64, 1], 900),
         "opt_m1_eta50": lambda: case_opt(1, 50.0, [1, 128, 128, 128, 128, 1], 500),
         "g2d_g100": lambda: case_g2d([2, 48, 48, 48, 1], 300, 40, 100.0),

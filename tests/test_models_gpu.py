@@ -46,7 +46,7 @@ def test_root(golden, name):
 
 
 @pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
-                                       ("final_box_g10_p3_m0", "box")])
+                                       ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well")])
 def test_final_random(golden, name, kind):
     import gpe_b200
     g = golden(name)
@@ -65,12 +65,12 @@ def test_final_random(golden, name, kind):
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
-@pytest.mark.parametrize("kind", ["harmonic", "box"])
+@pytest.mark.parametrize("kind", ["harmonic", "box", "gravity_well"])
 def test_final_fixture_mu_table(golden, kind):
     """Shipped trained weights: the fused path must reproduce the pickled mu_table (SURVEY 8c-1);
     converged mu within 1e-4 (north-star) -- in fact ~1e-6."""
     import gpe_b200
-    g = golden(f"final_{kind}_fixture")
+    g = golden(f"final_{kind.split('_')[0]}_fixture")
     lb, ub = float(g["lb"]), float(g["ub"])
     X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
     bp = torch.tensor([[lb], [ub]], device="cuda")
