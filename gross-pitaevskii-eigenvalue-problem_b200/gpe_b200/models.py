@@ -66,6 +66,19 @@ class JetMLP(nn.Module):
     precision = ops.PREC_AUTO
     #: optional torch.distributed process group (None = default group if initialised)
     group = None
+    #: optional min-max feature scaling x -> (x - lb) / (ub - lb) in front of the first layer
+    #: (S/helmholtz_2D_circle.py:89-94); sequences of length d, folded into (W_0, b_0) per call
+    input_lb = None
+    input_ub = None
+
+    def _first_layer_folded(self, W0, b0):
+        """W_0 ((x - lb) s) + b_0 = (W_0 diag(s)) x + (b_0 - W_0 (lb s)),  s = 1 / (ub - lb): the kernels see a plain
+        first layer, so u, grad u and the Laplacian come out w.r.t. the unscaled x; autograd carries the two
+        products back to the leaves."""
+        lb = torch.as_tensor(self.input_lb, dtype=W0.dtype, device=W0.device).reshape(-1)
+        ub = torch.as_tensor(self.input_ub, dtype=W0.dtype, device=W0.device).reshape(-1)
+        s = 1.0 / (ub - lb)
+        return W0 * s.unsqueeze(0), b0 - W0 @ (lb * s)
 
     def _linears(self):
         return [m for m in self.modules() if isinstance(m, nn.Linear)]
@@ -103,8 +116,10 @@ class JetMLP(nn.Module):
         if hit is not None and hit[0] is x:
             return hit[1]
         xin = x if x.is_contiguous() and x.dtype == torch.float32 else x.contiguous().float()
-        out = ops.mlp_jets(xin, [lin.weight for lin in lins], [lin.bias for lin in lins], self._act_kind(), kind, xform,
-                           self.precision)
+        Ws, bs = [lin.weight for lin in lins], [lin.bias for lin in lins]
+        if self.input_lb is not None:
+            Ws[0], bs[0] = self._first_layer_folded(Ws[0], bs[0])
+        out = ops.mlp_jets(xin, Ws, bs, self._act_kind(), kind, xform, self.precision)
         cache[key] = (x, out)
 
         def _invalidate(_grad, cache=cache, key=key):
@@ -571,10 +586,15 @@ class GPE2D(JetMLP):
 class Helmholtz2D(JetMLP):
     """`HelmholtzPINN` of S/helmholtz_2D.py:19-132 (config 3).  activation='leaky_relu' is the
     reference default (:31), 'tanh' follows S/helmholtz_2D_circle_3.py:31; a1, a2 generalise the source
-    to sin(a1 pi x) sin(a2 pi y).  semantics as in GPE2D."""
+    to sin(a1 pi x) sin(a2 pi y).  semantics as in GPE2D.  lb / ub switch on the min-max feature scaling of
+    S/helmholtz_2D_circle.py:89-94 (there module-level globals)."""
 
-    def __init__(self, layers, activation="leaky_relu", a1=1, a2=1, semantics="reference"):
+    def __init__(self, layers, activation="leaky_relu", a1=1, a2=1, semantics="reference", lb=None, ub=None):
         super().__init__()
+        if (lb is None) != (ub is None):
+            raise ValueError("give both lb and ub, or neither")
+        if lb is not None:
+            self.input_lb, self.input_ub = [float(v) for v in lb], [float(v) for v in ub]
         self.activation = nn.LeakyReLU() if activation == "leaky_relu" else nn.Tanh()
         self.loss_function = nn.MSELoss()
         self.linears = nn.ModuleList([nn.Linear(layers[i], layers[i + 1]) for i in range(len(layers) - 1)])
@@ -603,19 +623,24 @@ class Helmholtz2D(JetMLP):
         return self.loss_pde(x_f, k) + self.loss_data(x_u, u_true)
 
 
-def patch(model, jet_mode="full", precision=ops.PREC_AUTO):
+def patch(model, jet_mode="full", precision=ops.PREC_AUTO, input_lb=None, input_ub=None):
     """Compat path: reroute `model.forward` of a reference-style module -- a plain
     tanh / ShiftedTanh / LeakyReLU MLP held in `network` (nn.Sequential) or `linears` (ModuleList) --
     through the fused jet node and leave every loss method untouched.  The reference's own
     `torch.autograd.grad(u, x, create_graph=True)` calls then read the kernel's derivatives, and
     `loss.backward()` runs the reverse kernel once.  Returns the same object (its class is replaced by
-    a subclass that mixes JetMLP in)."""
+    a subclass that mixes JetMLP in).  input_lb / input_ub: the bounds of a forward that min-max scales its
+    input first (S/helmholtz_2D_circle.py:89-94 reads them from module globals)."""
     if isinstance(model, JetMLP):
         return model
+    if (input_lb is None) != (input_ub is None):
+        raise ValueError("give both input_lb and input_ub, or neither")
     cls = model.__class__
 
     def forward(self, x):
         return self._net(x)
 
     model.__class__ = type(cls.__name__ + "B200", (JetMLP, cls), {"forward": forward, "jet_mode": jet_mode, "precision": precision})
+    if input_lb is not None:
+        model.input_lb, model.input_ub = [float(v) for v in input_lb], [float(v) for v in input_ub]
     return model

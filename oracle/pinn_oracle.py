@@ -444,10 +444,12 @@ def gpe2d_pointwise_terms(model, x, x_bc):
 class Helmholtz2D(nn.Module):
     """S/helmholtz_2D.py:19-132.  `activation='leaky_relu'` is the reference default (:31);
     'tanh' follows S/helmholtz_2D_circle_3.py:31.  a1,a2 generalise the source to
-    sin(a1 pi x) sin(a2 pi y) (BASELINE config 3); a1=a2=1 is the reference."""
+    sin(a1 pi x) sin(a2 pi y) (BASELINE config 3); a1=a2=1 is the reference.  lb / ub: the min-max feature
+    scaling of S/helmholtz_2D_circle.py:89-94 (module globals there)."""
 
-    def __init__(self, layers, activation="leaky_relu", a1=1, a2=1):
+    def __init__(self, layers, activation="leaky_relu", a1=1, a2=1, lb=None, ub=None):
         super().__init__()
+        self.lb, self.ub = lb, ub
         self.activation = nn.LeakyReLU() if activation == "leaky_relu" else nn.Tanh()
         self.loss_function = nn.MSELoss()
         self.linears = nn.ModuleList([nn.Linear(layers[i], layers[i + 1]) for i in range(len(layers) - 1)])
@@ -457,6 +459,10 @@ class Helmholtz2D(nn.Module):
             nn.init.zeros_(lin.bias)
 
     def forward(self, x):
+        if self.lb is not None:                                   # helmholtz_2D_circle.py:89-94
+            l_b = torch.as_tensor(self.lb, dtype=x.dtype, device=x.device)
+            u_b = torch.as_tensor(self.ub, dtype=x.dtype, device=x.device)
+            x = (x - l_b) / (u_b - l_b)
         for lin in self.linears[:-1]:
             x = self.activation(lin(x))
         return self.linears[-1](x)
@@ -486,6 +492,45 @@ class Helmholtz2D(nn.Module):
 
     def compute_loss(self, x_f, x_u, u_true, k):
         return self.loss_pde(x_f, k) + self.loss_data(x_u, u_true)
+
+
+class HelmholtzCircle(Helmholtz2D):
+    """`HelmholtzPINN` of S/helmholtz_2D_circle.py:28-172: tanh MLP (:53) behind the min-max feature scaling of
+    :89-94, Helmholtz residual on the disc written in polar form from Cartesian derivatives.  The shapes are the
+    reference's: coordinates and u are [N,1], the autograd columns are [N], so every product of the two is an
+    [N,N] table (row = the point the coordinate belongs to, column = the point the derivative belongs to) and the
+    MSE runs over all N^2 entries."""
+
+    def __init__(self, layers, lb=(-1.0, -1.0), ub=(1.0, 1.0)):
+        super().__init__(layers, activation="tanh", lb=list(lb), ub=list(ub))
+
+    def loss_PDE(self, x_f, k=None):
+        """:112-172.  The argument k is ignored by the reference, which recomputes k = pi sqrt(m^2 + n^2), m = n = 1."""
+        from scipy.special import jn
+        X = x_f.clone().requires_grad_(True)
+        xc, yc = X[:, [0]], X[:, [1]]                                    # [N,1]
+        r = torch.clamp(torch.sqrt(xc ** 2 + yc ** 2), min=1e-8)
+        theta = torch.atan2(yc, xc)
+        u = self.forward(X)                                              # [N,1]
+        du = d_dx(u, X)                                                  # [N,2]
+        ux, uy = du[:, 0], du[:, 1]                                      # [N]
+        d2 = d_dx(du, X)                    # grad of sum(u_x + u_y): columns u_xx + u_xy, u_xy + u_yy   (:137-140)
+        s0, s1 = d2[:, 0], d2[:, 1]
+        u_r = (xc / r) * ux + (yc / r) * uy                              # [N,N]
+        u_rr = (xc ** 2 / r ** 2) * s0 + (2 * xc * yc / r ** 2) * s1 + (yc ** 2 / r ** 2) * s1   # (:144-145) as written
+        u_th = -yc * ux + xc * uy                                        # [N,N]
+        dth = d_dx(u_th, X)                                              # sum over the whole table  (:149-150)
+        u_thth = -yc * dth[:, 0] + xc * dth[:, 1]                        # [N,N]
+        n_ang, m_rad = 1, 1
+        kk = math.sqrt(math.pi ** 2 * (m_rad ** 2 + n_ang ** 2))
+        # the reference builds k as a float32 tensor and J_n as float64 values of the float32 product k r  (:156-159)
+        k32 = torch.sqrt(torch.tensor(np.pi ** 2 * (m_rad ** 2 + n_ang ** 2), device=x_f.device))
+        kr = k32.cpu().numpy() * r.detach().cpu().numpy()
+        bessel = torch.tensor(jn(n_ang, kr), dtype=torch.float64, device=x_f.device)
+        kt = k32 if x_f.dtype == torch.float32 else torch.tensor(kk, dtype=x_f.dtype, device=x_f.device)
+        q = kt ** 2 * bessel * torch.cos(n_ang * theta)                  # [N,1] float64
+        f = u_rr + (1 / r) * u_r + (1 / r ** 2) * u_thth + kt ** 2 * u - q
+        return self.loss_function(f.view(-1), torch.zeros_like(f).view(-1))
 
 
 # --------------------------------------------------------------------------------------

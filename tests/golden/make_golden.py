@@ -259,6 +259,30 @@ def case_helmholtz(layers, n_pts, n_bc, act):
     return out
 
 
+def case_helmholtz_circle(layers, n_pts):
+    """S/helmholtz_2D_circle.py: scaled forward (:69-106), its autograd columns as loss_PDE takes them (:131-140)
+    and loss_PDE itself (:112-172).  The reference's forward casts to float32 (:97), so there is no float64 run of
+    the real class; the float32 outputs pin the oracle, whose float64 run is then the truth for the GPU tests."""
+    mod = rl.load_script("helmholtz_2D_circle.py")
+    mod.device = torch.device("cpu")
+    mod.lb, mod.ub = np.array([-1.0, -1.0]), np.array([1.0, 1.0])
+    rng = np.random.default_rng(29)
+    rad, ang = np.sqrt(rng.random(n_pts)), rng.random(n_pts) * 2 * np.pi
+    Xn = np.stack([rad * np.cos(ang), rad * np.sin(ang)], 1).astype(np.float32).astype(np.float64)
+    torch.manual_seed(1234)
+    model = mod.HelmholtzPINN(layers)
+    out = {}
+    _pack("w.", _state(model), out)
+    X = torch.tensor(Xn, dtype=torch.float32).requires_grad_(True)
+    u = model(X)
+    du = torch.autograd.grad(u, X, torch.ones_like(u), create_graph=True)[0]
+    d2 = torch.autograd.grad(du, X, torch.ones_like(du), create_graph=True)[0]
+    loss = model.loss_PDE(torch.tensor(Xn, dtype=torch.float32), None)
+    _pack("f32.", dict(u=_np(u), du=_np(du), d2=_np(d2), pde=_np(loss), grads=_grads(model, loss)), out)
+    out.update(X=Xn, layers=np.array(layers), lb=mod.lb, ub=mod.ub)
+    return out
+
+
 def main():
     torch.set_num_threads(8)
     cases = {
@@ -278,6 +302,7 @@ def main():
         "g2d_g1_w128": lambda: case_g2d([2, 128, 128, 128, 128, 1], 160, 24, 1.0),
         "helmholtz_leaky": lambda: case_helmholtz([2, 40, 40, 40, 1], 300, 40, "leaky_relu"),
         "helmholtz_tanh": lambda: case_helmholtz([2, 100, 100, 100, 1], 200, 40, "tanh"),
+        "helmholtz_circle": lambda: case_helmholtz_circle([2, 64, 64, 64, 1], 150),
     }
     only = sys.argv[1:]
     for name, fn in cases.items():

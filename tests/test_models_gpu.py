@@ -197,6 +197,50 @@ def test_compat_g2d_and_helmholtz(golden):
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
 
 
+def test_compat_helmholtz_circle(golden):
+    """S/helmholtz_2D_circle.py through patch(): the forward's min-max scaling (:89-94) is folded into the first
+    layer, the reference's polar loss (:112-172; three nested autograd.grad calls, [N,N] tables) runs unchanged on
+    the kernel's u, grad u and Hessian.  Truth: the oracle in float64 (pinned to the real class in
+    test_oracle_golden.test_helmholtz_circle)."""
+    from gpe_b200.models import patch
+    g = golden("helmholtz_circle")
+    layers = [int(v) for v in g["layers"]]
+    ref = load_weights(po.HelmholtzCircle(layers, lb=g["lb"], ub=g["ub"]), g).double()
+    X64 = torch.tensor(g["X"], dtype=torch.float64)
+    want = ref.loss_PDE(X64)
+    want_g = flat(model_grads(ref, want))
+    model = patch(load_weights(po.HelmholtzCircle(layers, lb=g["lb"], ub=g["ub"]), g).cuda(), input_lb=g["lb"], input_ub=g["ub"])
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda")
+    xg = X.clone().requires_grad_(True)
+    u = model(xg)
+    du = po.d_dx(u, xg)
+    d2 = po.d_dx(du, xg)
+    assert rel_err(u.detach().cpu().numpy(), g["f32.u"]) < 1e-5
+    assert rel_err(du.detach().cpu().numpy(), g["f32.du"]) < 1e-5
+    assert rel_err(d2.detach().cpu().numpy(), g["f32.d2"]) < 1e-5
+    got = model.loss_PDE(X)
+    assert close(got, want, 2e-5), (float(got), float(want))
+    assert rel_err(flat(model_grads(model, got)), want_g) < 5e-5
+
+
+def test_helmholtz2d_input_scaling():
+    """gpe_b200.Helmholtz2D(lb=, ub=): fused loss_pde with the scaling folded into (W_0, b_0); gradients reach the
+    unscaled leaves.  Against the fp64 oracle with the scaling applied as the reference writes it."""
+    import gpe_b200
+    torch.manual_seed(3)
+    layers, lb, ub = [2, 128, 128, 128, 1], [-1.0, -2.0], [3.0, 1.5]
+    ref = po.Helmholtz2D(layers, activation="tanh", lb=lb, ub=ub).double()
+    gpu = gpe_b200.Helmholtz2D(layers, activation="tanh", lb=lb, ub=ub)
+    gpu.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    gpu = gpu.cuda()
+    X64 = torch.rand(500, 2, dtype=torch.float64) * torch.tensor([4.0, 3.5]) + torch.tensor(lb)
+    k = float(np.sqrt(2.0) * np.pi)
+    want = ref.loss_pde(X64, k)
+    got = gpu.loss_pde(X64.float().cuda().requires_grad_(True), k)
+    assert close(got, want, 2e-5), (float(got), float(want))
+    assert rel_err(flat(model_grads(gpu, got)), flat(model_grads(ref, want))) < 5e-5
+
+
 def test_reverse_kernel_runs_once_per_step(golden):
     """The C++ node must not run the parameter-reverse kernel during the nested autograd.grad(u, x)
     visits (SURVEY 8b-A note ii): count launches through the profiler-free route of a call counter."""

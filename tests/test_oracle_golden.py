@@ -139,6 +139,24 @@ def test_helmholtz(golden, name, tag):
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
 
 
+def test_helmholtz_circle(golden):
+    """S/helmholtz_2D_circle.py: scaled forward (:69-106), the autograd columns its loss takes (:131-140) and
+    loss_PDE (:112-172, [N,N] tables) of the real class (float32 only: its forward casts to float32) against the
+    oracle in float32 and float64."""
+    g = golden("helmholtz_circle")
+    for dt, tol in ((torch.float32, 1e-6), (torch.float64, 1e-5)):
+        model = load_weights(po.HelmholtzCircle([int(v) for v in g["layers"]], lb=g["lb"], ub=g["ub"]), g).to(dt)
+        X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+        u = model(X)
+        du = po.d_dx(u, X)
+        d2 = po.d_dx(du, X)
+        for key, val in dict(u=u, du=du, d2=d2).items():
+            assert rel_err(val.detach().numpy(), g[f"f32.{key}"]) < tol, key
+        loss = model.loss_PDE(torch.tensor(g["X"], dtype=dt))
+        assert close(loss, g["f32.pde"], tol)
+        assert rel_err(flat(model_grads(model, loss)), flat(golden_grads(g, "f32.grads"))) < tol
+
+
 def test_nn_moment_identity(golden):
     """the [N,N] mean factorises into O(N) moments (what lets the CUDA path
     reproduce the reference semantics at N = 4M..64M)."""
