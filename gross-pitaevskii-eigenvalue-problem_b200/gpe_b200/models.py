@@ -369,9 +369,14 @@ class FinalGPE1D(_GPE1DBase):
     def box_eigenfunction(self, x, n):
         return box_base_jets(x, n, self.L)[:, :1]
 
+    @property
+    def _has_factor(self):
+        """forward() multiplies the network by sin(pi x) (R/box_pinn_simulation.py:119-130)."""
+        return self.potential == "box"
+
     def forward(self, inputs):
         out = self._net(inputs)
-        if self.potential == "box":          # R/box_pinn_simulation.py:119-130
+        if self._has_factor:
             out = out * torch.sin(torch.pi * inputs)
         return out
 
@@ -400,7 +405,7 @@ class FinalGPE1D(_GPE1DBase):
         """R/harmonic_pinn_simulation.py:146-196 -> (pde_loss, lambda_pde)."""
         potential_type = potential_type or self.potential
         V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs.detach(), potential_type)
-        box = self.potential == "box"
+        box = self._has_factor
         scale = trace_scale(predictions, allow_factor=box)
         if scale is None:
             u = self.get_complete_solution(inputs, predictions) if self.use_perturbation else predictions
@@ -421,6 +426,81 @@ class FinalGPE1D(_GPE1DBase):
 
     def normalization_loss(self, u, dx):
         return (gdist.all_reduce_sum(torch.sum(u ** 2), self.group) * dx - 1.0) ** 2
+
+
+class VaryPotentialGPE1D(FinalGPE1D):
+    """The beta-sweep classes `GrossPitaevskiiPINN(layers, hbar, m, mode, beta, [L], use_residual, use_perturbation)`:
+
+    family='harmonic'          R/vary_potential_parameter_harmonic.py:51-342: box-sine base with L = 5, plain forward,
+                               V = beta/2 omega^2 (x - c)^2 from compute_potential(x, beta) (:231-246), term V u;
+    family='box_and_gaussian'  R/vary_potential_parameter_box_and_gaussian.py:52-229: box-sine base with L = 1, forward
+                               times sin(pi x), V in {0, exp(-x^2/2)} (:141-151), term beta V u (:189);
+    family='gravity_well'      R/vary_potential_parameter_gravity_well.py:52-261: Airy base, V = x, term beta V u.
+
+    pde_loss(inputs, predictions, gamma, beta, p, potential_type, precomputed_potential) -> (pde_loss, lambda_pde);
+    the fused epilogue takes beta V as its potential stream."""
+
+    _DEFAULT_PT = {"harmonic": "harmonic", "box_and_gaussian": "gaussian", "gravity_well": "gravity_well"}
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, beta=1.0, L=None, use_residual=True, use_perturbation=True,
+                 family="harmonic"):
+        if family not in self._DEFAULT_PT:
+            raise ValueError(f"Unknown family: {family}")
+        L = {"harmonic": 5.0, "box_and_gaussian": 1.0, "gravity_well": 1.0}[family] if L is None else L
+        super().__init__(layers, hbar, m, mode, 0.0, use_perturbation,
+                         potential="gravity_well" if family == "gravity_well" else "box", L=L)
+        self.family, self.beta, self.use_residual = family, beta, use_residual
+
+    @property
+    def _has_factor(self):
+        return self.family == "box_and_gaussian"
+
+    def compute_potential(self, x, *args, **kw):
+        if self.family == "harmonic":                    # (x, beta, potential_type="harmonic", omega=10, center=2.5)
+            beta = args[0]
+            pt = args[1] if len(args) > 1 else kw.get("potential_type", "harmonic")
+            if pt != "harmonic":
+                raise ValueError(f"Unknown potential type: {pt}")
+            return beta * 0.5 * kw.get("omega", 10.0) ** 2 * (x - kw.get("center", 2.5)) ** 2
+        pt = args[0] if args else kw.get("potential_type", self._DEFAULT_PT[self.family])
+        if self.family == "box_and_gaussian":
+            if pt == "box":
+                return torch.zeros_like(x)
+            if pt == "gaussian":
+                return torch.exp((-x ** 2) / 2)
+        elif pt == "gravity_well":
+            return x.clone()
+        raise ValueError(f"Unknown potential type: {pt}")
+
+    def pde_loss(self, inputs, predictions, gamma, beta, p, potential_type=None, precomputed_potential=None):
+        pt = potential_type or self._DEFAULT_PT[self.family]
+        if precomputed_potential is not None:
+            V = precomputed_potential
+        elif self.family == "harmonic":
+            V = self.compute_potential(inputs.detach(), beta, pt)
+        else:
+            V = self.compute_potential(inputs.detach(), pt)
+        if self.family != "harmonic":
+            V = beta * V
+        return FinalGPE1D.pde_loss(self, inputs, predictions, gamma, p, precomputed_potential=V)
+
+
+class PerturbGammaBetaGPE1D(FinalGPE1D):
+    """R/test_perturbing_gamma_and_beta.py:53-198 `GrossPitaevskiiPINN(layers, hbar, m, mode, beta, gamma,
+    use_perturbation)`: Hermite base, V = self.beta x^2 (:126-135), interaction self.gamma u**p (:171);
+    pde_loss(inputs, predictions, p, potential_type, precomputed_potential) (:137-181)."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, beta=1.0, gamma=0.0, use_perturbation=True):
+        super().__init__(layers, hbar, m, mode, gamma, use_perturbation, potential="harmonic")
+        self.beta = beta
+
+    def compute_potential(self, x, potential_type="harmonic", **kw):
+        if potential_type != "harmonic":
+            raise ValueError(f"Unknown potential type: {potential_type}")
+        return self.beta * (x ** 2)
+
+    def pde_loss(self, inputs, predictions, p, potential_type="harmonic", precomputed_potential=None):
+        return FinalGPE1D.pde_loss(self, inputs, predictions, self.gamma, p, potential_type, precomputed_potential)
 
 
 class OptGPE1D(_GPE1DBase):

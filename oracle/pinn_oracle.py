@@ -287,6 +287,104 @@ def final_train_terms(model, X, boundary_points, boundary_values, dx, gamma, p, 
     return pde + 10.0 * bc + 20.0 * nrm, pde, bc, nrm, mu
 
 
+class VaryPotentialGPE1D(FinalGPE1D):
+    """The beta-sweep classes `GrossPitaevskiiPINN(layers, hbar, m, mode, beta, [L], use_residual, use_perturbation)`
+    (use_residual is stored and never read):
+
+    family='harmonic'          R/vary_potential_parameter_harmonic.py:51-342 -- base = box sine with L = 5 (:152-160),
+                               plain forward (:145-149), V = beta/2 omega^2 (x - c)^2 with omega = 10, c = 2.5 built in
+                               compute_potential(x, beta) (:231-246), potential term V u (:296);
+    family='box_and_gaussian'  R/vary_potential_parameter_box_and_gaussian.py:52-229 -- base = box sine with L = 1,
+                               forward times sin(pi x) (:119-130), V in {0, exp(-x^2/2)} (:141-151), term beta V u (:189);
+    family='gravity_well'      R/vary_potential_parameter_gravity_well.py:52-261 -- Airy base with the np.gradient
+                               second derivative (:135-173), V = x, term beta V u, mu as sum/sum (:227-229).
+
+    pde_loss(inputs, predictions, gamma, beta, p, potential_type, precomputed_potential) -> (pde_loss, lambda_pde)."""
+
+    _DEFAULT_PT = {"harmonic": "harmonic", "box_and_gaussian": "gaussian", "gravity_well": "gravity_well"}
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, beta=1.0, L=None, use_residual=True, use_perturbation=True,
+                 family="harmonic"):
+        L = {"harmonic": 5.0, "box_and_gaussian": 1.0, "gravity_well": 1.0}[family] if L is None else L
+        super().__init__(layers, hbar, m, mode, 0.0, use_perturbation,
+                         potential="gravity_well" if family == "gravity_well" else "box", L=L)
+        self.family, self.beta, self.use_residual = family, beta, use_residual
+
+    def forward(self, inputs):
+        out = self.network(inputs)
+        if self.family == "box_and_gaussian":
+            out = out * torch.sin(torch.pi * inputs)
+        return out
+
+    def compute_potential(self, x, *args, **kw):
+        if self.family == "harmonic":                    # (x, beta, potential_type="harmonic", omega=10, center=2.5)
+            beta = args[0]
+            pt = args[1] if len(args) > 1 else kw.get("potential_type", "harmonic")
+            if pt != "harmonic":
+                raise ValueError(f"Unknown potential type: {pt}")
+            return beta * 0.5 * kw.get("omega", 10.0) ** 2 * (x - kw.get("center", 2.5)) ** 2
+        pt = args[0] if args else kw.get("potential_type", self._DEFAULT_PT[self.family])
+        if self.family == "box_and_gaussian":
+            if pt == "box":
+                return torch.zeros_like(x)
+            if pt == "gaussian":
+                return torch.exp((-x ** 2) / 2)
+        elif pt == "gravity_well":
+            return x.clone()
+        raise ValueError(f"Unknown potential type: {pt}")
+
+    def _jets(self, inputs, predictions):
+        if self.family == "gravity_well":
+            return FinalGPE1D._jets(self, inputs, predictions)
+        # the two box-base scripts differentiate base + perturbation by autograd (harmonic :283-299)
+        u = self.get_complete_solution(inputs, predictions) if self.use_perturbation else predictions
+        u_x = d_dx(u, inputs)
+        return u, u_x, d_dx(u_x, inputs)
+
+    def pde_loss(self, inputs, predictions, gamma, beta, p, potential_type=None, precomputed_potential=None):
+        pt = potential_type or self._DEFAULT_PT[self.family]
+        u, _, u_xx = self._jets(inputs, predictions)
+        if precomputed_potential is not None:
+            V = precomputed_potential
+        else:
+            V = self.compute_potential(inputs, beta, pt) if self.family == "harmonic" else self.compute_potential(inputs, pt)
+        pot = V * u if self.family == "harmonic" else beta * V * u
+        hu = -u_xx + pot + gamma * u ** p
+        if self.family == "gravity_well":
+            mu = torch.sum(u * hu) / torch.sum(u ** 2)
+        else:
+            mu = torch.mean(u * hu) / torch.mean(u ** 2)
+        return torch.mean((hu - mu * u) ** 2), mu
+
+
+class PerturbGammaBetaGPE1D(FinalGPE1D):
+    """R/test_perturbing_gamma_and_beta.py:53-198 `GrossPitaevskiiPINN(layers, hbar, m, mode, beta, gamma,
+    use_perturbation)`: Hermite base, V = self.beta x^2 (:126-135), interaction self.gamma u**p (:171);
+    pde_loss(inputs, predictions, p, potential_type, precomputed_potential) (:137-181)."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, beta=1.0, gamma=0.0, use_perturbation=True):
+        super().__init__(layers, hbar, m, mode, gamma, use_perturbation, potential="harmonic")
+        self.beta = beta
+
+    def compute_potential(self, x, potential_type="harmonic", **kw):
+        if potential_type != "harmonic":
+            raise ValueError(f"Unknown potential type: {potential_type}")
+        return self.beta * (x ** 2)
+
+    def pde_loss(self, inputs, predictions, p, potential_type="harmonic", precomputed_potential=None):
+        return FinalGPE1D.pde_loss(self, inputs, predictions, self.gamma, p, potential_type, precomputed_potential)
+
+
+def variant_train_terms(model, X, boundary_points, boundary_values, dx, pde_args, perturb_const, normal_const):
+    """Loop body shared by the beta-sweep scripts (R/vary_potential_parameter_harmonic.py:455-480,
+    R/test_perturbing_gamma_and_beta.py:402-429): as final_train_terms, pde_loss(X, u_pred, *pde_args)."""
+    u_pred = perturb_const * model.forward(X) / normal_const
+    bc = model.boundary_loss(boundary_points, boundary_values)
+    nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+    pde, mu = model.pde_loss(X, u_pred, *pde_args)
+    return pde + 10.0 * bc + 20.0 * nrm, pde, bc, nrm, mu
+
+
 # --------------------------------------------------------------------------------------
 # F-opt: S/gross_pitaevskii_1D_Different_Optimizers.py (BASELINE config 2 family)
 # --------------------------------------------------------------------------------------

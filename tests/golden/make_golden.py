@@ -169,6 +169,66 @@ def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic"):
     return out
 
 
+# ------------------------------------------------------------------------------ beta-sweep variants
+_VARIANTS = {
+    # family: (script, (lb, ub), ctor kwargs -> model, pde_loss args after (X, u_pred))
+    "harmonic": ("final/refine/vary_potential_parameter_harmonic.py", (0.0, 5.0)),
+    "box_and_gaussian": ("final/refine/vary_potential_parameter_box_and_gaussian.py", (0.0, 1.0)),
+    "gravity_well": ("final/refine/vary_potential_parameter_gravity_well.py", (0.0, 35.0)),
+    "perturb": ("final/refine/test_perturbing_gamma_and_beta.py", (-10.0, 10.0)),
+}
+
+
+def case_variant(family, mode, beta, gamma, p, n_pts, shipped=None, ptype=None):
+    """The beta-sweep classes: R/vary_potential_parameter_{harmonic,box_and_gaussian,gravity_well}.py
+    and R/test_perturbing_gamma_and_beta.py, loop body of :455-480 / :402-429.  shipped = (pickle, key of the beta
+    entry): trained weights and normalisation constant from the reference's own result files; else seeded Xavier."""
+    script, (lb, ub) = _VARIANTS[family]
+    mod = rl.load_script(script)
+    mod.device = torch.device("cpu")
+    Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
+    if family == "gravity_well":
+        Xn = Xn.astype(np.float32).astype(np.float64)      # see case_final_fixture
+    dx = float(Xn[1, 0] - Xn[0, 0])
+    const, pc, layers, state, mu_logged = 0.37, 0.01, [1, 64, 64, 64, 1], None, np.nan
+    if shipped is not None:
+        data = rl.load_pickle(shipped[0])
+        entry = data["models_state_dicts"][mode][shipped[1]]
+        layers, state, const = entry["layers"], entry["state_dict"], float(data["constant_history"][mode])
+        mu_logged = dict(data["lambda_table"][mode])[shipped[1]]
+    if family == "perturb":
+        ctor = lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, beta=beta, gamma=gamma)
+        pde_args = (p,) if ptype is None else (p, ptype)
+    else:
+        ctor = lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, beta=beta)
+        pde_args = (gamma, beta, p) if ptype is None else (gamma, beta, p, ptype)
+
+    def build():
+        torch.manual_seed(1234)
+        m = ctor()
+        if state is not None:
+            m.load_state_dict(state)
+        else:
+            m.apply(xavier)
+        return m
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        bp = torch.tensor([[lb], [ub]], dtype=dt)
+        bv = torch.zeros((2, 1), dtype=dt)
+        u_pred = pc * model.forward(X) / const
+        bc = model.boundary_loss(bp, bv)
+        nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+        pde, mu = model.pde_loss(X, u_pred, *pde_args)
+        total = pde + 10.0 * bc + 20.0 * nrm
+        return dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), total=_np(total), mu=_np(mu), grads=_grads(model, total))
+
+    out = _both_dtypes(build, run)
+    out.update(X=Xn, dx=dx, lb=lb, ub=ub, mode=mode, p=p, gamma=gamma, beta=beta, const=const, perturb_const=pc,
+               layers=np.array(layers), family=family, ptype=ptype or "", mu_logged=mu_logged)
+    return out
+
+
 # ------------------------------------------------------------------------------ F-opt
 def case_opt(mode, eta, layers, n_pts):
     ns = rl.load_class_by_lines("gross_pitaevskii_1D_Different_Optimizers.py", 27, 440)
@@ -296,6 +356,16 @@ def main():
         "final_box_g10_p3_m0": lambda: case_final_random(10.0, 3, 0, [1, 64, 64, 64, 1], 800, kind="box"),
         "final_gravity_fixture": lambda: case_final_fixture("gravity_well"),
         "final_gravity_g10_p3_m1": lambda: case_final_random(10.0, 3, 1, [1, 64, 64, 64, 1], 1200, kind="gravity_well"),
+        "vary_harmonic_b0.6_g5_p3_m1": lambda: case_variant("harmonic", 1, 0.6, 5.0, 3, 900),
+        "vary_gaussian_b20_g10_p3_m0": lambda: case_variant("box_and_gaussian", 0, 20.0, 10.0, 3, 800, ptype="gaussian"),
+        "vary_boxpot_b3_g4_p4_m2": lambda: case_variant("box_and_gaussian", 2, 3.0, 4.0, 4, 600, ptype="box"),
+        "vary_gravity_shipped_b20_m2": lambda: case_variant(
+            "gravity_well", 2, 20, 0, 3, 4000,
+            shipped=("vary_potential_parameter_p3_gravity_well/vary_potential_parameter_p3_gravity_well.pkl", 20)),
+        "perturb_shipped_b20_m3": lambda: case_variant(
+            "perturb", 3, 20, 0.0, 3, 4000,
+            shipped=("vary_potential_parameter_p3_harmonic/vary_potential_parameter_p3_harmonic.pkl", 20)),
+        "perturb_b4_gm4_p3_m1": lambda: case_variant("perturb", 1, 4.0, -4.0, 3, 1000),
         "opt_m0_eta10": lambda: case_opt(0, 10.0, [1, 64, 64, 64, 1], 900),
         "opt_m1_eta50": lambda: case_opt(1, 50.0, [1, 128, 128, 128, 128, 1], 500),
         "g2d_g100": lambda: case_g2d([2, 48, 48, 48, 1], 300, 40, 100.0),

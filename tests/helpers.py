@@ -31,3 +31,23 @@ def model_grads(model, total):
     model.zero_grad()
     total.backward()
     return [p.grad.detach().cpu().numpy() if p.grad is not None else np.zeros(tuple(p.shape)) for p in model.parameters()]
+
+
+VARIANT_GOLDENS = ["vary_harmonic_b0.6_g5_p3_m1", "vary_gaussian_b20_g10_p3_m0", "vary_boxpot_b3_g4_p4_m2",
+                   "vary_gravity_shipped_b20_m2", "perturb_shipped_b20_m3", "perturb_b4_gm4_p3_m1"]
+
+
+def variant_model_and_args(ns, g):
+    """(model, pde_loss arguments after (X, u_pred)) of a beta-sweep golden (tests/golden/make_golden.case_variant);
+    ns is the module holding the classes: oracle.pinn_oracle or gpe_b200."""
+    family, mode, beta, gamma, p = str(g["family"]), int(g["mode"]), float(g["beta"]), float(g["gamma"]), int(g["p"])
+    layers, ptype = [int(v) for v in g["layers"]], str(g["ptype"])
+    if family == "perturb":
+        model = ns.PerturbGammaBetaGPE1D(layers, mode=mode, beta=beta, gamma=gamma)
+        args = (p,)
+    else:
+        model = ns.VaryPotentialGPE1D(layers, mode=mode, beta=beta, family=family)
+        args = (gamma, beta, p)
+    if ptype:
+        args = args + (ptype,)
+    return load_weights(model, g), args

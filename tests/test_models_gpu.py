@@ -10,7 +10,7 @@ import pytest
 import torch
 
 from oracle import pinn_oracle as po
-from helpers import load_weights, golden_grads, flat, rel_err, model_grads
+from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
@@ -85,6 +85,34 @@ def test_final_fixture_mu_table(golden, kind):
         for key, val in dict(pde=pde, total=total).items():
             ref = float(g[f"m{mode}.f64.{key}"])
             assert abs(float(val) - ref) <= 0.3 * abs(ref) + 1e-9, (mode, key, float(val), ref)
+
+
+@pytest.mark.parametrize("name", VARIANT_GOLDENS)
+def test_beta_sweep_variants(golden, name):
+    """gpe_b200.VaryPotentialGPE1D / PerturbGammaBetaGPE1D (R/vary_potential_parameter_*.py,
+    R/test_perturbing_gamma_and_beta.py) against the float64 runs of the real classes."""
+    import gpe_b200
+    g = golden(name)
+    model, pde_args = variant_model_and_args(gpe_b200, g)
+    model = model.cuda()
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    total, pde, bc, nrm, mu = po.variant_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                     pde_args, float(g["perturb_const"]), float(g["const"]))
+    shipped = "shipped" in name
+    assert close(mu, g["f64.mu"], 2e-5), (float(mu), float(g["f64.mu"]))
+    if shipped:      # converged weights: losses are ~1e-6 differences of O(1) numbers (see test_final_fixture_mu_table)
+        for key, val in dict(pde=pde, total=total).items():
+            ref = float(g[f"f64.{key}"])
+            assert abs(float(val) - ref) <= 0.3 * abs(ref) + 1e-9, (key, float(val), ref)
+        assert abs(float(mu) - float(g["mu_logged"])) < 2e-3 * abs(float(g["mu_logged"]))
+        return
+    for key, val in dict(pde=pde, total=total).items():
+        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
+    assert abs(float(bc) - float(g["f64.bc"])) <= 2 * TOL * abs(float(g["f64.bc"])) + 1e-12
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 @pytest.mark.parametrize("name", ["opt_m0_eta10", "opt_m1_eta50"])
