@@ -351,6 +351,55 @@ class RootGPE1D(_GPE1DBase):
         return (gdist.all_reduce_sum(torch.sum(u ** 2), self.group) * dx - 1.0) ** 2
 
 
+def _abs_pow(p):
+    return lambda u: torch.abs(u) ** (p - 1) * u
+
+
+class PaperGPE1D(RootGPE1D):
+    """`GrossPitaevskiiPINN(layers, hbar, m, mode, gamma)` of NBP/Gross_Pitaevskii_1D_Harmonic.ipynb cell 6: the root
+    notebook's network and constant-H Hermite base; interaction gamma |u|^(p-1) u, lambda returned as mu + mode,
+    normalised Riesz energy, symmetry term on base + network."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0):
+        super().__init__(layers, hbar, m, mode, gamma)
+
+    def get_complete_solution(self, x, perturbation, mode=None):
+        return self.weighted_hermite(x, self.mode if mode is None else mode) + perturbation
+
+    def _paper_moments(self, inputs, predictions, p, potential_type, precomputed_potential):
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs.detach(), potential_type)
+        scale = trace_scale(predictions)
+        if scale is None:
+            raise RuntimeError("gpe_b200: `predictions` must be (a scalar multiple of) model.forward(inputs)")
+        base = hermite_base_jets(inputs, self.mode, const_h=True)
+        M = self._moments(inputs, base=base, V=_col(V), scale=scale, nl_kind=ops.NL_ABSPOW, nl_power=p)
+        return M, base, _col(V), scale
+
+    def pde_loss(self, inputs, predictions, gamma, p, potential_type="harmonic", precomputed_potential=None):
+        """cell 6:82-131 -> (pde_loss, pde_residual [N,1], lambda_pde + mode, u [N,1])."""
+        M, base, V, scale = self._paper_moments(inputs, predictions, p, potential_type, precomputed_potential)
+        wH = L.hamiltonian_weights(-0.5, gamma)
+        mu = L.rayleigh_mu(M, wH)
+        res, full = self._full_fields(inputs, base, V, scale, -0.5, gamma, _abs_pow(p), mu)
+        return L.residual_mse(M, wH, mu).float(), res, (mu + self.mode).float(), full
+
+    def riesz_loss(self, inputs, predictions, gamma, p, potential_type="harmonic", precomputed_potential=None):
+        """cell 6:133-183 -> (E, E + mode, u); the grid spacing cancels between the sums and the norm factor."""
+        M, base, V, scale = self._paper_moments(inputs, predictions, p, potential_type, precomputed_potential)
+        e = (0.5 * M.grad2 + M.P(L.F_U, L.F_VU) + (gamma / (p + 1)) * M.P(L.F_U, L.F_NL)) / M.P(L.F_U, L.F_U)
+        full = scale * self.jets(inputs)[0].unsqueeze(1) + base[:, :1]
+        return e.float(), (e + self.mode).float(), full
+
+    def boundary_loss(self, boundary_points, boundary_values):
+        full = self.get_complete_solution(boundary_points, self.forward(boundary_points))
+        return torch.mean((full - boundary_values) ** 2)
+
+    def symmetry_loss(self, collocation_points, lb, ub):
+        """cell 6:193-214, on base + network: psi_n(-x) = (-1)^n psi_n(x) holds bit for bit (Horner in +-x, even
+        weight), so the base cancels and the term is the network-only one of the root notebook."""
+        return RootGPE1D.symmetry_loss(self, collocation_points, lb, ub)
+
+
 class FinalGPE1D(_GPE1DBase):
     """`GrossPitaevskiiPINN(layers, hbar, m, mode, gamma, use_perturbation)` of
     R/harmonic_pinn_simulation.py:52-217; `potential='box'` follows R/box_pinn_simulation.py:52-262,

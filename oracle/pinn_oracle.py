@@ -170,6 +170,69 @@ def root_train_terms(model, X, boundary_points, boundary_values, dx, gamma, powe
     return pde + 10.0 * bc + 20.0 * nrm + 5.0 * sym, pde, bc, nrm, sym, mu
 
 
+class PaperGPE1D(RootGPE1D):
+    """NBP/Gross_Pitaevskii_1D_Harmonic.ipynb cell 6 `GrossPitaevskiiPINN(layers, hbar, m, mode, gamma)`: the root
+    notebook's network and constant-H Hermite base with gamma |u|^(p-1) u, mu returned as mu + mode, a normalised
+    Riesz energy and the symmetry term on the full solution."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0):
+        super().__init__(layers, hbar, m, mode, gamma)
+
+    def get_complete_solution(self, x, perturbation, mode=None):
+        return self.weighted_hermite(x, self.mode if mode is None else mode) + perturbation
+
+    def pde_loss(self, inputs, predictions, gamma, p, potential_type="harmonic", precomputed_potential=None):
+        """cell 6:82-131 -> (pde_loss, pde_residual, lambda_pde + mode, u)."""
+        u = self.get_complete_solution(inputs, predictions)
+        u_xx = d_dx(d_dx(u, inputs), inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        hu = -0.5 * u_xx + V * u + gamma * torch.abs(u) ** (p - 1) * u
+        mu = torch.mean(u * hu) / torch.mean(u ** 2)
+        r = hu - mu * u
+        return torch.mean(r ** 2), r, mu + self.mode, u
+
+    def riesz_loss(self, inputs, predictions, gamma, p, potential_type="harmonic", precomputed_potential=None):
+        """cell 6:133-183 -> (E, E + mode, u), E = (1/2 S u'^2 + S V u^2 + gamma/(p+1) S |u|^(p+1)) / S u^2 with
+        S = sum * dx, dx = inputs[1] - inputs[0]."""
+        u = self.get_complete_solution(inputs, predictions)
+        if not inputs.requires_grad:
+            inputs = inputs.clone().detach().requires_grad_(True)
+        u_x = d_dx(u, inputs)
+        dx = inputs[1] - inputs[0]
+        nf = torch.sum(u ** 2) * dx
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        e = (0.5 * torch.sum(u_x ** 2) * dx / nf + torch.sum(V * u ** 2) * dx / nf
+             + 0.5 * (2.0 * gamma / (p + 1)) * torch.sum(torch.abs(u) ** (p + 1)) * dx / nf)
+        return e, e + self.mode, u
+
+    def boundary_loss(self, boundary_points, boundary_values):
+        full = self.get_complete_solution(boundary_points, self.forward(boundary_points))
+        return torch.mean((full - boundary_values) ** 2)
+
+    def symmetry_loss(self, collocation_points, lb, ub):
+        """cell 6:193-214: on base + network."""
+        xr = -collocation_points
+        a = self.get_complete_solution(collocation_points, self.forward(collocation_points))
+        b = self.get_complete_solution(xr, self.forward(xr))
+        return torch.mean((a + b) ** 2) if self.mode % 2 == 1 else torch.mean((a - b) ** 2)
+
+
+def paper_train_terms(model, X, boundary_points, boundary_values, dx, gamma, p, lb, ub, potential_type="harmonic"):
+    """Loop body NBP/Gross_Pitaevskii_1D_Harmonic.ipynb cell 8:97-145: mode 0 minimises Riesz + pde, the others pde;
+    returns (total, physics, bc, norm, sym, lambda_value)."""
+    u_pred = model.forward(X)
+    bc = model.boundary_loss(boundary_points, boundary_values)
+    nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+    sym = model.symmetry_loss(X, lb, ub)
+    if model.mode == 0:
+        e, lam, _ = model.riesz_loss(X, u_pred, gamma, p, potential_type)
+        pde, _, _, _ = model.pde_loss(X, u_pred, gamma, p, potential_type)
+        phys = e + pde
+    else:
+        phys, _, lam, _ = model.pde_loss(X, u_pred, gamma, p, potential_type)
+    return phys + 10.0 * bc + 20.0 * nrm + 5.0 * sym, phys, bc, nrm, sym, lam
+
+
 # --------------------------------------------------------------------------------------
 # F-final: the paper's PL-PINN scripts (own the shipped .pkl fixtures)
 # --------------------------------------------------------------------------------------

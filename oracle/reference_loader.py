@@ -112,6 +112,16 @@ def load_root_notebook_class():
     return ns["GrossPitaevskiiPINN"]
 
 
+def load_paper_notebook_class(name="Gross_Pitaevskii_1D_Harmonic.ipynb", cell=6):
+    """`GrossPitaevskiiPINN` of Notebooks/Paper/Gross_Pitaevskii_1D_Harmonic.ipynb cell 6."""
+    from scipy.special import hermite
+    with open(os.path.join(REF_ROOT, "Notebooks", "Paper", name)) as fh:
+        nb = json.load(fh)
+    ns = dict(torch=torch, nn=nn, np=np, math=math, hermite=hermite, device=torch.device("cpu"))
+    exec("".join(nb["cells"][cell]["source"]), ns)
+    return ns["GrossPitaevskiiPINN"]
+
+
 def load_pickle(relpath_under_refine):
     import pickle
     with open(os.path.join(REFINE, relpath_under_refine), "rb") as fh:

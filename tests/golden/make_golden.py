@@ -92,6 +92,34 @@ def case_root(mode, p, gamma, layers, n_pts):
     return out
 
 
+# ------------------------------------------------------------------------------ F-paper (notebook)
+def case_paper(mode, p, gamma, layers, n_pts):
+    """NBP/Gross_Pitaevskii_1D_Harmonic.ipynb cell 6 with the loop body of cell 8:97-145."""
+    Cls = rl.load_paper_notebook_class()
+    lb, ub = -10.0, 10.0
+    Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
+    dx = float(Xn[1, 0] - Xn[0, 0])
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        bp = torch.tensor([[lb], [ub]], dtype=dt)
+        bv = torch.zeros((2, 1), dtype=dt)
+        u_pred = model.forward(X)
+        bc = model.boundary_loss(bp, bv)
+        nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
+        sym = model.symmetry_loss(X, lb, ub)
+        e, lam_e, _ = model.riesz_loss(X, u_pred, gamma, p, "harmonic")
+        pde, res, lam, full_u = model.pde_loss(X, u_pred, gamma, p, "harmonic")
+        phys = e + pde if mode == 0 else pde
+        total = phys + 10.0 * bc + 20.0 * nrm + 5.0 * sym
+        return dict(pde=_np(pde), riesz=_np(e), lam_riesz=_np(lam_e), bc=_np(bc), norm=_np(nrm), sym=_np(sym),
+                    total=_np(total), mu=_np(lam), u=_np(full_u)[:, 0], residual=_np(res)[:, 0], grads=_grads(model, total))
+
+    out = _both_dtypes(seeded(lambda: Cls(layers, mode=mode, gamma=gamma), init=xavier), run)
+    out.update(X=Xn, dx=dx, lb=lb, ub=ub, mode=mode, p=p, gamma=gamma, layers=np.array(layers))
+    return out
+
+
 # ------------------------------------------------------------------------------ F-final (pkl fixtures)
 def case_final_fixture(kind):
     """Protocol of SURVEY.md 8c-1: shipped weights, X = linspace(lb,ub,4000),
@@ -349,6 +377,8 @@ def main():
         "root_m0_p2": lambda: case_root(0, 2, 1.0, [1, 32, 32, 32, 1], 600),
         "root_m1_p3": lambda: case_root(1, 3, 1.0, [1, 64, 64, 64, 1], 1000),
         "root_m2_p3": lambda: case_root(2, 3, 1.0, [1, 100, 100, 100, 1], 700),
+        "paper_m0_g10_p3": lambda: case_paper(0, 3, 10.0, [1, 64, 64, 64, 1], 800),
+        "paper_m1_g20_p2": lambda: case_paper(1, 2, 20.0, [1, 48, 48, 48, 1], 600),
         "final_harmonic_fixture": lambda: case_final_fixture("harmonic"),
         "final_box_fixture": lambda: case_final_fixture("box"),
         "final_harmonic_g20_p3_m1": lambda: case_final_random(20.0, 3, 1, [1, 64, 64, 64, 1], 900),

@@ -18,7 +18,7 @@ GTOL = 2e-5
 
 
 def close(a, b, tol=TOL):
-    a, b = float(a), float(b)
+    a, b = float(a.detach().reshape(-1)[0]) if torch.is_tensor(a) else float(a), float(np.asarray(b).reshape(-1)[0])
     return abs(a - b) <= tol * max(abs(b), 1e-30)
 
 
@@ -42,6 +42,29 @@ def test_root(golden, name):
     _, res, _, full = model.pde_loss(int(g["p"]), X, model.forward(X), float(g["gamma"]))
     assert rel_err(full.detach().cpu().numpy().ravel(), g["f64.u"]) < TOL
     assert rel_err(res.detach().cpu().numpy().ravel(), g["f64.residual"]) < 5 * TOL
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
+
+
+@pytest.mark.parametrize("name", ["paper_m0_g10_p3", "paper_m1_g20_p2"])
+def test_paper_notebook(golden, name):
+    """gpe_b200.PaperGPE1D (NBP/Gross_Pitaevskii_1D_Harmonic.ipynb cell 6) with the loop body of cell 8:97-145."""
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.PaperGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    gamma, p = float(g["gamma"]), int(g["p"])
+    total, phys, bc, nrm, sym, lam = po.paper_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                          gamma, p, lb, ub)
+    e, lam_e, _ = model.riesz_loss(X, model.forward(X), gamma, p)
+    pde, res, mu, u = model.pde_loss(X, model.forward(X), gamma, p)
+    for key, val in dict(pde=pde, riesz=e, lam_riesz=lam_e, mu=mu, bc=bc, sym=sym, total=total).items():
+        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+    assert close(lam, g["f64.lam_riesz"] if int(g["mode"]) == 0 else g["f64.mu"], 2 * TOL)
+    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
+    assert rel_err(u.detach().cpu().numpy()[:, 0], g["f64.u"]) < TOL
+    assert rel_err(res.detach().cpu().numpy()[:, 0], g["f64.residual"]) < 5 * TOL
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 

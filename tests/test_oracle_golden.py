@@ -14,7 +14,7 @@ TOL = {"f32": 2e-4, "f64": 1e-9}
 
 
 def close(a, b, tol):
-    a, b = float(a), float(b)
+    a, b = float(a.detach().reshape(-1)[0]) if torch.is_tensor(a) else float(a), float(np.asarray(b).reshape(-1)[0])
     return abs(a - b) <= tol * max(abs(b), 1e-30)
 
 
@@ -32,6 +32,30 @@ def test_root(golden, name, tag):
                                                        float(g["gamma"]), int(g["p"]), lb, ub)
     for key, val in dict(pde=pde, bc=bc, norm=nrm, sym=sym, total=total, mu=mu).items():
         assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("name", ["paper_m0_g10_p3", "paper_m1_g20_p2"])
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_paper_notebook(golden, name, tag):
+    """NBP/Gross_Pitaevskii_1D_Harmonic.ipynb cell 6 (|u|^(p-1) u, mu + mode, normalised Riesz, full-solution symmetry)."""
+    g = golden(name)
+    dt = DT[tag]
+    model = load_weights(po.PaperGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"])), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], dtype=dt)
+    gamma, p = float(g["gamma"]), int(g["p"])
+    total, phys, bc, nrm, sym, lam = po.paper_train_terms(model, X, bp, torch.zeros((2, 1), dtype=dt), float(g["dx"]),
+                                                          gamma, p, lb, ub)
+    e, lam_e, _ = model.riesz_loss(X, model.forward(X), gamma, p)
+    pde, res, mu, u = model.pde_loss(X, model.forward(X), gamma, p)
+    want_lam = g[f"{tag}.lam_riesz"] if int(g["mode"]) == 0 else g[f"{tag}.mu"]
+    for key, val in dict(pde=pde, riesz=e, lam_riesz=lam_e, mu=mu, bc=bc, norm=nrm, sym=sym, total=total).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert close(lam, want_lam, TOL[tag])
+    assert rel_err(u.detach().numpy()[:, 0], g[f"{tag}.u"]) < TOL[tag]
+    assert rel_err(res.detach().numpy()[:, 0], g[f"{tag}.residual"]) < TOL[tag]
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
 
 
