@@ -114,8 +114,9 @@ def helmholtz_pointwise_mse(M: Moments, k2):
     return M.quad({F_LAP: 1.0, F_U: k2, F_Q: -1.0}) / M.n
 
 
-def riesz_energy(M: Moments, eta, reduction="mean"):
-    """1/2 (R|grad u|^2 + R V u^2 + eta/2 R u nl(u)), R = mean
-    (S/gross_pitaevskii_1D_Different_Optimizers.py:278-280) or sum (S/gross_pitaevskii_2D.py:146-149)."""
-    s = M.grad2 + M.P(F_U, F_VU) + 0.5 * eta * M.P(F_U, F_NL)
+def riesz_energy(M: Moments, eta, reduction="mean", nl_coef=0.5):
+    """1/2 (R|grad u|^2 + R V u^2 + nl_coef eta R u nl(u)), R = mean
+    (S/gross_pitaevskii_1D_Different_Optimizers.py:278-280) or sum (S/gross_pitaevskii_2D.py:146-149); nl_coef = 1/2
+    for u^4, 2/(p+1) for |u|^(p+1) (S/gross_pitaevskii_1D_Different_Optimizers_and_Nonlinearity_Powers.py:244)."""
+    s = M.grad2 + M.P(F_U, F_VU) + nl_coef * eta * M.P(F_U, F_NL)
     return 0.5 * (s / M.n if reduction == "mean" else s)

@@ -570,17 +570,21 @@ class OptGPE1D(_GPE1DBase):
 
     compute_potential = RootGPE1D.compute_potential
 
-    def _base(self, x, prev_prediction):
+    #: weight of prev_prediction(x) in the complete solution: self.beta here (:204-208), 1 in the later copies
+    _prev_weighted = True
+
+    def _base(self, x, prev_prediction, mode=None):
         """Base jets [N,3]: psi_n (const-H form, :89-111) or beta * prev_prediction(x) (:204-208), whose
         derivatives are taken the reference's way (autograd through the callable)."""
         if prev_prediction is None:
-            return hermite_base_jets(x, self.mode, const_h=True)
+            return hermite_base_jets(x, self.mode if mode is None else mode, const_h=True)
         with torch.enable_grad():
             xx = x.detach().clone().requires_grad_(True)
             p0 = prev_prediction(xx)
             p1 = torch.autograd.grad(p0, xx, torch.ones_like(p0), create_graph=True)[0]
             p2 = torch.autograd.grad(p1, xx, torch.ones_like(p1))[0]
-        return (self.beta * torch.cat([p0, p1, p2], dim=1)).detach().float().contiguous()
+        w = self.beta if self._prev_weighted else 1.0
+        return (w * torch.cat([p0, p1, p2], dim=1)).detach().float().contiguous()
 
     def get_complete_solution(self, x, perturbation, prev_prediction=None):
         """:175-213."""
@@ -590,13 +594,15 @@ class OptGPE1D(_GPE1DBase):
         u = self.get_complete_solution(boundary_points, self.forward(boundary_points), prev_prediction)
         return torch.mean((u - boundary_values) ** 2)
 
-    def _M(self, inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction):
+    def _M(self, inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, p=None, mode=None):
+        """Moments of one jet evaluation; nl(u) = u^3 (= |u^2| u, :341) or |u|^(p-1) u when p is given."""
         V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs.detach(), potential_type)
         scale = trace_scale(predictions)
         if scale is None:
             raise RuntimeError("gpe_b200: `predictions` must be (a scalar multiple of) model.forward(inputs)")
-        base = self._base(inputs, prev_prediction)
-        M = self._moments(inputs, base=base, V=_col(V), scale=scale * self.alpha, nl_kind=ops.NL_POW, nl_power=3)
+        base = self._base(inputs, prev_prediction, mode)
+        nl = dict(nl_kind=ops.NL_POW, nl_power=3) if p is None else dict(nl_kind=ops.NL_ABSPOW, nl_power=p)
+        M = self._moments(inputs, base=base, V=_col(V), scale=scale * self.alpha, **nl)
         return M, base, _col(V), scale * self.alpha
 
     def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None):
@@ -636,6 +642,108 @@ class OptGPE1D(_GPE1DBase):
         self.last_weighted_sum = sum(w * t for w, t in zip(weights, terms))
         total = data + pde / length + riesz / length
         return total, data, riesz, pde, norm
+
+
+class _OptAdditive(OptGPE1D):
+    """The two later copies of the F-opt class: ctor (layers, hbar, m, g, mode, prev_prediction=None), no alpha / beta,
+    u = psi_n + predictions or prev_prediction(x) + predictions (_Self_Adaptive.py:32-61,178-206;
+    _and_Nonlinearity_Powers.py:32-55,172-198)."""
+    _prev_weighted = False
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, mode=0, prev_prediction=None):
+        super().__init__(layers, hbar, m, g, mode)
+
+    def _five_terms(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, potential_type,
+                    precomputed_potential, prev_prediction, p=None):
+        """(data, riesz, pde, norm, sym) from one jet evaluation + one moment pass + the mirrored forward."""
+        pred = self.forward(collocation_points)
+        M, _, _, _ = self._M(collocation_points, pred, eta, potential_type, precomputed_potential, prev_prediction, p)
+        data = self.boundary_loss(boundary_points, boundary_values, prev_prediction)
+        riesz = L.riesz_energy(M, eta, "mean", 0.5 if p is None else 2.0 / (p + 1)).float()
+        pde = L.residual_mse(M, L.hamiltonian_weights(-1.0, eta), L.energy_mu(M, eta)).float()
+        norm = ((torch.sqrt(M.nn2) - 1.0) ** 2).float()
+        return data, riesz, pde, norm, self.symmetry_loss(collocation_points, lb, ub)
+
+
+class SelfAdaptiveGPE1D(_OptAdditive):
+    """S/gross_pitaevskii_1D_Different_Optimizers_Self_Adaptive.py:27-429: five learnable log-weights `log_alpha`
+    (an ordinary parameter next to the network's; its gradient comes from autograd on the returned terms)."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, mode=0, prev_prediction=None):
+        super().__init__(layers, hbar, m, g, mode, prev_prediction)
+        self.log_alpha = nn.Parameter(torch.zeros(5, dtype=torch.float32))
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights, potential_type,
+                   precomputed_potential=None, prev_prediction=None):
+        """:356-429 -> (total, data, riesz, pde, norm, sym, alpha)."""
+        data, riesz, pde, norm, sym = self._five_terms(collocation_points, boundary_points, boundary_values, eta, lb, ub,
+                                                       potential_type, precomputed_potential, prev_prediction)
+        alpha = torch.exp(self.log_alpha)
+        length = ub - lb
+        total = sum(alpha[i] * weights[i] * t for i, t in enumerate([data, riesz / length, pde / length, norm, sym]))
+        return total, data, riesz, pde, norm, sym, alpha
+
+
+class PowersGPE1D(_OptAdditive):
+    """S/gross_pitaevskii_1D_Different_Optimizers_and_Nonlinearity_Powers.py:27-407: |u|^(p-1) u, p an argument."""
+
+    def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, p=2):
+        """:200-248: 1/2 (mean u'^2 + mean V u^2 + 2 eta/(p+1) mean |u|^(p+1))."""
+        M = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, p)[0]
+        return L.riesz_energy(M, eta, "mean", 2.0 / (p + 1)).float()
+
+    def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None, p=2):
+        """:250-317 -> (pde_loss, pde_residual [N,1], lambda_pde)."""
+        M, base, V, scale = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, p)
+        wH = L.hamiltonian_weights(-1.0, eta)
+        mu = L.energy_mu(M, eta)
+        res, _ = self._full_fields(inputs, base, V, scale, -1.0, eta, _abs_pow(p), mu)
+        return L.residual_mse(M, wH, mu).float(), res, mu.float()
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights, potential_type,
+                   precomputed_potential=None, prev_prediction=None, p=2):
+        """:348-407 -> (weighted five-term sum, data, riesz, pde, norm)."""
+        data, riesz, pde, norm, sym = self._five_terms(collocation_points, boundary_points, boundary_values, eta, lb, ub,
+                                                       potential_type, precomputed_potential, prev_prediction, p)
+        length = ub - lb
+        total = sum(w * t for w, t in zip(weights, [data, riesz / length, pde / length, norm, sym]))
+        return total, data, riesz, pde, norm
+
+
+class ModesGPE1D(OptGPE1D):
+    """S/gross_pitaevskii_1D_Different_Modes.py:27-450: the mode is an argument of every loss method, the previous
+    solution enters without beta (:184-213), total = data + pde/len + riesz/len + norm (:448)."""
+    _prev_weighted = False
+
+    def get_complete_solution(self, x, perturbation, prev_prediction=None, mode=0):
+        return self._base(x, prev_prediction, mode)[:, :1] + self.alpha * perturbation
+
+    def boundary_loss(self, boundary_points, boundary_values, prev_prediction=None, mode=0):
+        u = self.get_complete_solution(boundary_points, self.forward(boundary_points), prev_prediction, mode)
+        return torch.mean((u - boundary_values) ** 2)
+
+    def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
+        M = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, None, mode)[0]
+        return L.riesz_energy(M, eta, "mean").float()
+
+    def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
+        M, base, V, scale = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, None, mode)
+        wH = L.hamiltonian_weights(-1.0, eta)
+        mu = L.energy_mu(M, eta)
+        res, _ = self._full_fields(inputs, base, V, scale, -1.0, eta, lambda u: torch.abs(u ** 2) * u, mu)
+        return L.residual_mse(M, wH, mu).float(), res, mu.float()
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights, potential_type,
+                   precomputed_potential=None, prev_prediction=None, mode=0):
+        """:383-450 -> (total, data, riesz, pde, norm)."""
+        pred = self.forward(collocation_points)
+        M = self._M(collocation_points, pred, eta, potential_type, precomputed_potential, prev_prediction, None, mode)[0]
+        data = self.boundary_loss(boundary_points, boundary_values, prev_prediction, mode)
+        riesz = L.riesz_energy(M, eta, "mean").float()
+        pde = L.residual_mse(M, L.hamiltonian_weights(-1.0, eta), L.energy_mu(M, eta)).float()
+        norm = ((torch.sqrt(M.nn2) - 1.0) ** 2).float()
+        length = ub - lb
+        return data + pde / length + riesz / length + norm, data, riesz, pde, norm
 
 
 class GPE2D(JetMLP):

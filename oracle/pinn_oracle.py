@@ -515,6 +515,7 @@ class OptGPE1D(nn.Module):
         sym = self.symmetry_loss(collocation_points, lb, ub)
         length = ub - lb
         terms = [data, riesz / length, pde / length, norm, sym]
+        self._terms, self._raw = terms, (data, riesz, pde, norm, sym)
         self.last_weighted_sum = sum(w * t for w, t in zip(weights, terms))
         total = data + pde / length + riesz / length
         return total, data, riesz, pde, norm
@@ -523,6 +524,110 @@ class OptGPE1D(nn.Module):
 # --------------------------------------------------------------------------------------
 # G2D: S/gross_pitaevskii_2D.py (BASELINE configs 4/5 family) -- keeps the [N]x[N,1] broadcast
 # --------------------------------------------------------------------------------------
+class _OptAdditive(OptGPE1D):
+    """Shared by the two later copies of the F-opt class: ctor (layers, hbar, m, g, mode, prev_prediction=None), no
+    alpha / beta, u = base + predictions with base = psi_n or prev_prediction(x)
+    (_Self_Adaptive.py:32-61,178-206; _and_Nonlinearity_Powers.py:32-55,172-198)."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, mode=0, prev_prediction=None):
+        super().__init__(layers, hbar, m, g, mode)
+
+    def get_complete_solution(self, x, perturbation, prev_prediction=None):
+        base = self.weighted_hermite(x, self.mode) if prev_prediction is None else prev_prediction(x)
+        return base + perturbation
+
+
+class SelfAdaptiveGPE1D(_OptAdditive):
+    """S/gross_pitaevskii_1D_Different_Optimizers_Self_Adaptive.py:27-429: five learnable log-weights."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, mode=0, prev_prediction=None):
+        super().__init__(layers, hbar, m, g, mode, prev_prediction)
+        self.log_alpha = nn.Parameter(torch.zeros(5, dtype=torch.float32))
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights,
+                   potential_type, precomputed_potential=None, prev_prediction=None):
+        """:356-429 -> (total, data, riesz, pde, norm, sym, alpha), total = sum_i exp(log_alpha_i) w_i term_i."""
+        OptGPE1D.total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights,
+                            potential_type, precomputed_potential, prev_prediction)
+        alpha = torch.exp(self.log_alpha)
+        total = sum(alpha[i] * weights[i] * t for i, t in enumerate(self._terms))
+        data, riesz, pde, norm, sym = self._raw
+        return total, data, riesz, pde, norm, sym, alpha
+
+
+class PowersGPE1D(_OptAdditive):
+    """S/gross_pitaevskii_1D_Different_Optimizers_and_Nonlinearity_Powers.py:27-407: nonlinearity |u|^(p-1) u."""
+
+    def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, p=2):
+        """:200-248."""
+        u = self.get_complete_solution(inputs, predictions, prev_prediction)
+        u_x = d_dx(u, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        return 0.5 * (torch.mean(u_x ** 2) + torch.mean(V * u ** 2) + 2 * eta / (p + 1) * torch.mean(torch.abs(u) ** (p + 1)))
+
+    def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None, p=2):
+        """:250-317."""
+        u = self.get_complete_solution(inputs, predictions, prev_prediction)
+        u_x = d_dx(u, inputs)
+        u_xx = d_dx(u_x, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        mu = torch.mean(u_x ** 2 + V * u ** 2 + eta * torch.abs(u) ** (p + 1)) / torch.mean(u ** 2)
+        r = -u_xx + V * u + eta * torch.abs(u) ** (p - 1) * u - mu * u
+        return torch.mean(r ** 2), r, mu
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights,
+                   potential_type, precomputed_potential=None, prev_prediction=None, p=2):
+        """:348-407 -> (weighted five-term sum, data, riesz, pde, norm)."""
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(collocation_points, potential_type)
+        data = self.boundary_loss(boundary_points, boundary_values, prev_prediction)
+        riesz = self.riesz_loss(self.forward(collocation_points), collocation_points, eta, potential_type, V, prev_prediction, p)
+        pde, _, _ = self.pde_loss(collocation_points, self.forward(collocation_points), eta, potential_type, V, prev_prediction, p)
+        norm = (torch.norm(self.forward(collocation_points), p=2) - 1) ** 2
+        sym = self.symmetry_loss(collocation_points, lb, ub)
+        length = ub - lb
+        total = sum(w * t for w, t in zip(weights, [data, riesz / length, pde / length, norm, sym]))
+        return total, data, riesz, pde, norm
+
+
+class ModesGPE1D(OptGPE1D):
+    """S/gross_pitaevskii_1D_Different_Modes.py:27-450: the mode is an argument of every loss method, the previous
+    solution enters without beta (:184-213), total = data + pde/len + riesz/len + norm (:448)."""
+
+    def get_complete_solution(self, x, perturbation, prev_prediction=None, mode=0):
+        base = self.weighted_hermite(x, mode) if prev_prediction is None else prev_prediction(x)
+        return base + self.alpha * perturbation
+
+    def boundary_loss(self, boundary_points, boundary_values, prev_prediction=None, mode=0):
+        u = self.get_complete_solution(boundary_points, self.forward(boundary_points), prev_prediction, mode)
+        return torch.mean((u - boundary_values) ** 2)
+
+    def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
+        u = self.get_complete_solution(inputs, predictions, prev_prediction, mode)
+        u_x = d_dx(u, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        return 0.5 * (torch.mean(u_x ** 2) + torch.mean(V * u ** 2) + 0.5 * eta * torch.mean(u ** 4))
+
+    def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
+        u = self.get_complete_solution(inputs, predictions, prev_prediction, mode)
+        u_x = d_dx(u, inputs)
+        u_xx = d_dx(u_x, inputs)
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(inputs, potential_type)
+        mu = torch.mean(u_x ** 2 + V * u ** 2 + eta * u ** 4) / torch.mean(u ** 2)
+        r = -u_xx + V * u + eta * torch.abs(u ** 2) * u - mu * u
+        return torch.mean(r ** 2), r, mu
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights,
+                   potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
+        """:383-450."""
+        V = precomputed_potential if precomputed_potential is not None else self.compute_potential(collocation_points, potential_type)
+        data = self.boundary_loss(boundary_points, boundary_values, prev_prediction, mode)
+        riesz = self.riesz_loss(self.forward(collocation_points), collocation_points, eta, potential_type, V, prev_prediction, mode)
+        pde, _, _ = self.pde_loss(collocation_points, self.forward(collocation_points), eta, potential_type, V, prev_prediction, mode)
+        norm = (torch.norm(self.forward(collocation_points), p=2) - 1) ** 2
+        length = ub - lb
+        return data + pde / length + riesz / length + norm, data, riesz, pde, norm
+
+
 class GPE2D(nn.Module):
     """S/gross_pitaevskii_2D.py:16-274.  `potential` extends compute_potential beyond the
     reference's Gaussian so the BASELINE harmonic / optical-lattice configs can be stated."""

@@ -371,6 +371,48 @@ def case_helmholtz_circle(layers, n_pts):
     return out
 
 
+def case_opt_variant(kind, mode, eta, layers, n_pts, p=2):
+    """The three later copies of the F-opt class:
+    self_adaptive  S/gross_pitaevskii_1D_Different_Optimizers_Self_Adaptive.py:27-429 (log_alpha weights),
+    powers         S/gross_pitaevskii_1D_Different_Optimizers_and_Nonlinearity_Powers.py:27-407 (|u|^(p-1) u),
+    modes          S/gross_pitaevskii_1D_Different_Modes.py:27-450 (mode as an argument, + norm in the total)."""
+    if kind == "self_adaptive":
+        Cls = rl.load_class_by_lines("gross_pitaevskii_1D_Different_Optimizers_Self_Adaptive.py", 27, 429)["GrossPitaevskiiPINN"]
+    elif kind == "powers":
+        Cls = rl.load_class_by_lines("gross_pitaevskii_1D_Different_Optimizers_and_Nonlinearity_Powers.py", 27, 407)["GrossPitaevskiiPINN"]
+    else:
+        Cls = rl.load_class_by_lines("gross_pitaevskii_1D_Different_Modes.py", 27, 450)["GrossPitaevskiiPINN"]
+    lb, ub = -10.0, 10.0
+    rng = np.random.default_rng(11)
+    Xn = np.sort(lb + (ub - lb) * rng.random((n_pts, 1)), axis=0)
+    weights = [50.0, 1.0, 2.0, 10.0, 25.0]
+    la = np.array([0.3, -0.2, 0.1, -0.4, 0.25], dtype=np.float32)
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        bp = torch.tensor([[lb], [ub]], dtype=dt)
+        bv = torch.zeros((2, 1), dtype=dt)
+        lbt, ubt = torch.tensor(lb, dtype=dt), torch.tensor(ub, dtype=dt)
+        extra = {"powers": dict(p=p), "modes": dict(mode=mode)}.get(kind, {})
+        if kind == "self_adaptive":
+            with torch.no_grad():
+                model.log_alpha.copy_(torch.tensor(la, dtype=dt))
+        ret = model.total_loss(X, bp, bv, eta, lbt, ubt, weights, "harmonic", **extra)
+        total, data, riesz, pde, norm = ret[:5]
+        _, _, mu = model.pde_loss(X, model.forward(X), eta, "harmonic", **extra)
+        out = dict(total=_np(total), data=_np(data), riesz=_np(riesz), pde=_np(pde), norm=_np(norm), mu=_np(mu),
+                   grads=_grads(model, total))
+        if kind == "self_adaptive":
+            out.update(sym=_np(ret[5]), alpha=_np(ret[6]))
+        return out
+
+    ctor = (lambda: Cls(layers, mode=mode)) if kind != "modes" else (lambda: Cls(layers, mode=0))
+    out = _both_dtypes(seeded(ctor, init=xavier), run)
+    out.update(X=Xn, lb=lb, ub=ub, mode=mode, eta=eta, p=p, weights=np.array(weights), layers=np.array(layers), kind=kind,
+               log_alpha=la)
+    return out
+
+
 def main():
     torch.set_num_threads(8)
     cases = {
@@ -398,6 +440,10 @@ def main():
         "perturb_b4_gm4_p3_m1": lambda: case_variant("perturb", 1, 4.0, -4.0, 3, 1000),
         "opt_m0_eta10": lambda: case_opt(0, 10.0, [1, 64, 64, 64, 1], 900),
         "opt_m1_eta50": lambda: case_opt(1, 50.0, [1, 128, 128, 128, 128, 1], 500),
+        "opt_selfadaptive_m0_eta20": lambda: case_opt_variant("self_adaptive", 0, 20.0, [1, 64, 64, 64, 1], 700),
+        "opt_powers_m1_eta30_p4": lambda: case_opt_variant("powers", 1, 30.0, [1, 64, 64, 64, 1], 600, p=4),
+        "opt_powers_m0_eta10_p2": lambda: case_opt_variant("powers", 0, 10.0, [1, 48, 48, 1], 500, p=2),
+        "opt_modes_m2_eta40": lambda: case_opt_variant("modes", 2, 40.0, [1, 64, 64, 64, 1], 600),
         "g2d_g100": lambda: case_g2d([2, 48, 48, 48, 1], 300, 40, 100.0),
         "g2d_g1_w128": lambda: case_g2d([2, 128, 128, 128, 128, 1], 160, 24, 1.0),
         "helmholtz_leaky": lambda: case_helmholtz([2, 40, 40, 40, 1], 300, 40, "leaky_relu"),

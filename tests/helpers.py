@@ -51,3 +51,20 @@ def variant_model_and_args(ns, g):
     if ptype:
         args = args + (ptype,)
     return load_weights(model, g), args
+
+
+OPT_VARIANT_GOLDENS = ["opt_selfadaptive_m0_eta20", "opt_powers_m1_eta30_p4", "opt_powers_m0_eta10_p2", "opt_modes_m2_eta40"]
+
+
+def opt_variant_model_and_kwargs(ns, g):
+    """(model, extra keyword arguments of its loss methods) of an F-opt variant golden (make_golden.case_opt_variant)."""
+    kind, layers, mode = str(g["kind"]), [int(v) for v in g["layers"]], int(g["mode"])
+    if kind == "self_adaptive":
+        model, extra = load_weights(ns.SelfAdaptiveGPE1D(layers, mode=mode), g), {}
+        with torch.no_grad():
+            model.log_alpha.copy_(torch.tensor(g["log_alpha"]))
+    elif kind == "powers":
+        model, extra = load_weights(ns.PowersGPE1D(layers, mode=mode), g), dict(p=int(g["p"]))
+    else:
+        model, extra = load_weights(ns.ModesGPE1D(layers, mode=0), g), dict(mode=mode)
+    return model, extra

@@ -10,7 +10,8 @@ import pytest
 import torch
 
 from oracle import pinn_oracle as po
-from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args
+from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args, \
+    OPT_VARIANT_GOLDENS, opt_variant_model_and_kwargs
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
@@ -136,6 +137,30 @@ def test_beta_sweep_variants(golden, name):
     assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
     assert abs(float(bc) - float(g["f64.bc"])) <= 2 * TOL * abs(float(g["f64.bc"])) + 1e-12
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
+
+
+@pytest.mark.parametrize("name", OPT_VARIANT_GOLDENS)
+def test_opt_variants(golden, name):
+    """gpe_b200.SelfAdaptiveGPE1D / PowersGPE1D / ModesGPE1D against the float64 runs of the real classes
+    (_Self_Adaptive.py, _and_Nonlinearity_Powers.py, _Different_Modes.py)."""
+    import gpe_b200
+    g = golden(name)
+    model, extra = opt_variant_model_and_kwargs(gpe_b200, g)
+    model = model.cuda()
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = torch.tensor(float(g["lb"]), device="cuda"), torch.tensor(float(g["ub"]), device="cuda")
+    bp = torch.stack([lb, ub]).view(2, 1)
+    eta = float(g["eta"])
+    ret = model.total_loss(X, bp, torch.zeros((2, 1), device="cuda"), eta, lb, ub, list(g["weights"]), "harmonic", **extra)
+    _, _, mu = model.pde_loss(X, model.forward(X), eta, "harmonic", **extra)
+    got = dict(total=ret[0], data=ret[1], riesz=ret[2], pde=ret[3], mu=mu)
+    if str(g["kind"]) == "self_adaptive":
+        got["sym"] = ret[5]
+        assert rel_err(ret[6].detach().cpu().numpy(), g["f64.alpha"]) < TOL
+    for key, val in got.items():
+        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+    assert abs(float(ret[4]) - float(g["f64.norm"])) <= 1e-4 * abs(float(g["f64.norm"])) + 1e-9
+    assert rel_err(flat(model_grads(model, ret[0])), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 @pytest.mark.parametrize("name", ["opt_m0_eta10", "opt_m1_eta50"])

@@ -7,7 +7,8 @@ import pytest
 import torch
 
 from oracle import pinn_oracle as po
-from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args
+from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args, \
+    OPT_VARIANT_GOLDENS, opt_variant_model_and_kwargs
 
 DT = {"f32": torch.float32, "f64": torch.float64}
 TOL = {"f32": 2e-4, "f64": 1e-9}
@@ -187,6 +188,29 @@ def test_beta_sweep_variants(golden, name, tag):
         assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
     if shipped:     # the value the reference logged while training these weights (an epoch before the saved state)
         assert abs(float(mu) - float(g["mu_logged"])) < 2e-3 * abs(float(g["mu_logged"]))
+
+
+@pytest.mark.parametrize("name", OPT_VARIANT_GOLDENS)
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_opt_variants(golden, name, tag):
+    """_Self_Adaptive.py, _and_Nonlinearity_Powers.py, _Different_Modes.py copies of the F-opt class."""
+    g = golden(name)
+    dt = DT[tag]
+    model, extra = opt_variant_model_and_kwargs(po, g)
+    model = model.to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    lb, ub = torch.tensor(float(g["lb"]), dtype=dt), torch.tensor(float(g["ub"]), dtype=dt)
+    bp = torch.stack([lb, ub]).view(2, 1)
+    eta = float(g["eta"])
+    ret = model.total_loss(X, bp, torch.zeros((2, 1), dtype=dt), eta, lb, ub, list(g["weights"]), "harmonic", **extra)
+    _, _, mu = model.pde_loss(X, model.forward(X), eta, "harmonic", **extra)
+    got = dict(total=ret[0], data=ret[1], riesz=ret[2], pde=ret[3], norm=ret[4], mu=mu)
+    if str(g["kind"]) == "self_adaptive":
+        got["sym"] = ret[5]
+        assert rel_err(ret[6].detach().numpy(), g[f"{tag}.alpha"]) < TOL[tag]
+    for key, val in got.items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, ret[0])), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
 
 
 def test_helmholtz_circle(golden):
