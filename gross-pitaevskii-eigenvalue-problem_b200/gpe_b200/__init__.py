@@ -5,8 +5,9 @@ from . import _lib, ops  # noqa: F401
 from . import distributed, graphs, losses, models  # noqa: F401
 from ._lib import version  # noqa: F401
 from .models import (FinalGPE1D, GPE2D, Helmholtz2D, ModesGPE1D, OptGPE1D, PaperGPE1D, PerturbGammaBetaGPE1D,  # noqa: F401
-                     PowersGPE1D, RootGPE1D, SelfAdaptiveGPE1D, ShiftedTanh, VaryPotentialGPE1D, patch)
+                     PowersGPE1D, ReLoBRaLoGPE2D, RootGPE1D, SelfAdaptiveGPE1D, ShiftedTanh, VaryPotentialGPE1D, patch)
 
 __all__ = ["ops", "losses", "models", "distributed", "graphs", "version", "RootGPE1D", "FinalGPE1D", "OptGPE1D", "GPE2D",
            "Helmholtz2D", "ShiftedTanh", "VaryPotentialGPE1D", "PerturbGammaBetaGPE1D",
-           "PaperGPE1D", "SelfAdaptiveGPE1D", "PowersGPE1D", "ModesGPE1D", "patch"]
+           "PaperGPE1D", "SelfAdaptiveGPE1D", "PowersGPE1D", "ModesGPE1D", "ReLoBRaLoGPE2D",
+           "patch"]

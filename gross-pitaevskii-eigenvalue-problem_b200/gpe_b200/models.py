@@ -819,6 +819,111 @@ class GPE2D(JetMLP):
         pde, _, _ = self.pde_loss(x, None)
         return data + pde + riesz
 
+    total_loss = loss            # S/gross_pitaevskii_2D_minimal.py:201-222: the same sum under another name
+
+
+class ReLoBRaLoGPE2D(JetMLP):
+    """`GrossPitaevskiiPINN(layers, hbar, m, g, alpha, temperature, rho)` of S/gross_pitaevskii_2D_ReLoBRaLo.py:13-341.
+    The file keeps 1-D formulas on [N,2] inputs: V = exp(-(x-a)^2) is [N,2], u_xx = grad(sum grad u) = Hessian.(1,1),
+    the residual is [N,2] with one scalar lambda.  Here: one FULL jet evaluation (u, grad u, u_xx, u_yy, u_xy) and one
+    moment pass per residual column (its "Laplacian" is u_cc + u_xy, its potential V[:,c]); the ReLoBRaLo weight
+    update (:294-335) stays the reference's host-side python."""
+    jet_mode = "full"
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, alpha=0.999, temperature=1.0, rho=0.9999):
+        super().__init__()
+        self.layers = layers
+        self.network = _sequential(layers, nn.Tanh)
+        self.g, self.hbar, self.m = g, hbar, m
+        self.alpha, self.temperature, self.rho = alpha, temperature, rho
+        self.call_count = 0
+        self.lambdas, self.last_losses, self.init_losses = [1.0] * 5, [1.0] * 5, [1.0] * 5
+
+    def forward(self, inputs):
+        return self._net(inputs)
+
+    def compute_potential(self, x, potential_type="gaussian", a=0.5, l=1.0):
+        """:94-126 (elementwise on whatever shape x has)."""
+        if potential_type == "gaussian":
+            return torch.exp(-(x - a) ** 2)
+        return torch.sin(torch.pi * (x - (a - l / 2)) / l)
+
+    def boundary_loss(self, boundary_points, boundary_values):
+        """:128-145."""
+        return torch.mean((self.forward(boundary_points) - boundary_values) ** 2)
+
+    def _M2(self, inputs):
+        """Moments of the two residual columns (cached per step like GPE2D._M)."""
+        u, g, h = self.jets(inputs, derivs=True)            # h = (u_xx, u_yy, u_xy)
+        key = ("M", id(inputs), inputs._version)
+        hit = self._jet_cache.get(key)
+        if hit is None or hit[0] is not inputs:
+            V = self.compute_potential(inputs.detach()).float()
+            Ms = []
+            for c in (0, 1):
+                m = ops.gram_moments(u, g, h[:, [c, 2]].contiguous(), None, V=V[:, c].contiguous(), d=2,
+                                     nl_kind=ops.NL_POW, nl_power=3, lap_cols=2)
+                Ms.append(L.Moments(gdist.all_reduce_sum(m, self.group)))
+            hit = (inputs, Ms, V)
+            self._jet_cache[key] = hit
+        return hit[1], hit[2]
+
+    @staticmethod
+    def _lambda(Ms, eta):
+        """mean over [N,2] of (u_c^2 + V_c u^2 + eta u^4) / mean u^2 (:207)."""
+        M0, M1 = Ms
+        return (M0.grad2 + M0.P(F_U, F_VU) + M1.P(F_U, F_VU) + 2.0 * eta * M0.P(F_U, F_NL)) / (2.0 * M0.P(F_U, F_U))
+
+    def riesz_loss(self, predictions, inputs, eta):
+        """:147-180 (means over the [N,2] tables)."""
+        (M0, M1), _ = self._M2(inputs)
+        n = M0.n
+        e = 0.5 * (M0.grad2 / (2.0 * n) + (M0.P(F_U, F_VU) + M1.P(F_U, F_VU)) / (2.0 * n) + 0.5 * eta * M0.P(F_U, F_NL) / n)
+        return e.float()
+
+    def pde_loss(self, inputs, predictions, eta):
+        """:182-230 -> (pde_loss, pde_residual [N,2], lambda_pde)."""
+        Ms, V = self._M2(inputs)
+        lam = self._lambda(Ms, eta)
+        wH = L.hamiltonian_weights(-1.0, eta)
+        mse = 0.5 * (L.residual_mse(Ms[0], wH, lam) + L.residual_mse(Ms[1], wH, lam))
+        u, g, h = self.jets(inputs)
+        uc = u.unsqueeze(1)
+        res = -(h[:, :2] + h[:, 2:3]) + V * uc + eta * torch.abs(uc ** 2) * uc - lam.float() * uc
+        return mse.float(), res, lam.float()
+
+    def symmetry_loss(self, collocation_points):
+        """:232-257: mirror y -> -y."""
+        return self._mirror_sym(collocation_points, [1.0, -1.0], [0.0, 0.0], 1)
+
+    def relobralo_weights(self, losses):
+        """:294-335: the weight update from the terms' host values (five .item() syncs, one torch.bernoulli draw)."""
+        vals = [t.item() for t in losses]
+        if self.call_count == 0:
+            self.lambdas, self.last_losses, self.init_losses = [1.0] * len(vals), list(vals), list(vals)
+        hat = [vals[i] / (self.last_losses[i] * self.temperature + 1e-8) for i in range(len(vals))]
+        hat = torch.softmax(torch.tensor(hat) - max(hat), dim=0).tolist()
+        hat0 = [vals[i] / (self.init_losses[i] * self.temperature + 1e-8) for i in range(len(vals))]
+        hat0 = torch.softmax(torch.tensor(hat0) - max(hat0), dim=0).tolist()
+        rho = torch.bernoulli(torch.tensor(self.rho))
+        alpha = self.alpha if self.call_count > 1 else (0.0 if self.call_count == 1 else 1.0)
+        self.lambdas = [float(rho * alpha * self.lambdas[i] + (1 - rho) * alpha * hat0[i] + (1 - alpha) * hat[i])
+                        for i in range(len(vals))]
+        self.last_losses = list(vals)
+        self.call_count += 1
+        return [lam * w for lam, w in zip(self.lambdas, [500.0, 1.0, 2.0, 100.0, 500])]
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta):
+        """:259-341 -> (total, data, riesz, pde, norm); one jet evaluation serves riesz, pde and norm."""
+        data = self.boundary_loss(boundary_points, boundary_values)
+        riesz = self.riesz_loss(None, collocation_points, eta)
+        pde, _, _ = self.pde_loss(collocation_points, None, eta)
+        norm = ((torch.sqrt(self._M2(collocation_points)[0][0].nn2) - 1.0) ** 2).float()
+        sym = self.symmetry_loss(collocation_points)
+        losses = [data, riesz, pde, norm, sym]
+        total = sum(w * t for w, t in zip(self.relobralo_weights(losses), losses))
+        return total, data, riesz, pde, norm
+
 
 class Helmholtz2D(JetMLP):
     """`HelmholtzPINN` of S/helmholtz_2D.py:19-132 (config 3).  activation='leaky_relu' is the

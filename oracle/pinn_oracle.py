@@ -687,6 +687,85 @@ class GPE2D(nn.Module):
         pde, _, _ = self.pde_loss(x, self.forward(x))
         return data + pde + riesz
 
+    total_loss = loss            # S/gross_pitaevskii_2D_minimal.py:201-222: the same sum under another name
+
+
+class ReLoBRaLoGPE2D(nn.Module):
+    """S/gross_pitaevskii_2D_ReLoBRaLo.py:13-341.  The file keeps the 1-D formulas on [N,2] inputs: V = exp(-(x-a)^2)
+    is [N,2] (:94-126), u_x = grad u [N,2], u_xx = grad(sum u_x) = Hessian . (1,1) [N,2] (:200-201), so the residual is
+    [N,2] with a shared scalar lambda; the mirror is y -> -y (:232-257), the norm term (||NN||_2 - 1)^2 (:285) and the
+    five terms are weighted by ReLoBRaLo's .item()-based softmax (:294-339)."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, alpha=0.999, temperature=1.0, rho=0.9999):
+        super().__init__()
+        self.layers = layers
+        self.network = sequential_mlp(layers, nn.Tanh)
+        self.g, self.hbar, self.m = g, hbar, m
+        self.alpha, self.temperature, self.rho = alpha, temperature, rho
+        self.call_count = 0
+        self.lambdas, self.last_losses, self.init_losses = [1.0] * 5, [1.0] * 5, [1.0] * 5
+
+    def forward(self, inputs):
+        return self.network(inputs)
+
+    def compute_potential(self, x, potential_type="gaussian", a=0.5, l=1.0):
+        if potential_type == "gaussian":
+            return torch.exp(-(x - a) ** 2)
+        return torch.sin(torch.pi * (x - (a - l / 2)) / l)
+
+    def boundary_loss(self, boundary_points, boundary_values):
+        return torch.mean((self.forward(boundary_points) - boundary_values) ** 2)
+
+    def riesz_loss(self, predictions, inputs, eta):
+        """:147-180, mean form."""
+        u = predictions
+        u_x = d_dx(u, inputs)
+        V = self.compute_potential(inputs)
+        return 0.5 * (torch.mean(u_x ** 2) + torch.mean(V * u ** 2) + 0.5 * eta * torch.mean(u ** 4))
+
+    def pde_loss(self, inputs, predictions, eta):
+        """:182-230 -> (pde_loss, pde_residual [N,2], lambda_pde)."""
+        u = predictions
+        u_x = d_dx(u, inputs)
+        u_xx = d_dx(u_x, inputs)
+        V = self.compute_potential(inputs)
+        lam = torch.mean(u_x ** 2 + V * u ** 2 + eta * u ** 4) / torch.mean(u ** 2)
+        r = -u_xx + V * u + eta * torch.abs(u ** 2) * u - lam * u
+        return torch.mean(r ** 2), r, lam
+
+    def symmetry_loss(self, collocation_points):
+        refl = collocation_points.clone()
+        refl[:, 1] = -refl[:, 1]
+        return torch.mean((self.forward(collocation_points) - self.forward(refl)) ** 2)
+
+    def relobralo_weights(self, losses):
+        """:294-335: the weight update from the terms' host values (one torch.bernoulli draw per call)."""
+        vals = [t.item() for t in losses]
+        if self.call_count == 0:
+            self.lambdas, self.last_losses, self.init_losses = [1.0] * len(vals), list(vals), list(vals)
+        hat = [vals[i] / (self.last_losses[i] * self.temperature + 1e-8) for i in range(len(vals))]
+        hat = torch.softmax(torch.tensor(hat) - max(hat), dim=0).tolist()
+        hat0 = [vals[i] / (self.init_losses[i] * self.temperature + 1e-8) for i in range(len(vals))]
+        hat0 = torch.softmax(torch.tensor(hat0) - max(hat0), dim=0).tolist()
+        rho = torch.bernoulli(torch.tensor(self.rho))
+        alpha = self.alpha if self.call_count > 1 else (0.0 if self.call_count == 1 else 1.0)
+        self.lambdas = [float(rho * alpha * self.lambdas[i] + (1 - rho) * alpha * hat0[i] + (1 - alpha) * hat[i])
+                        for i in range(len(vals))]
+        self.last_losses = list(vals)
+        self.call_count += 1
+        return [lam * w for lam, w in zip(self.lambdas, [500.0, 1.0, 2.0, 100.0, 500])]
+
+    def total_loss(self, collocation_points, boundary_points, boundary_values, eta):
+        """:259-341 -> (total, data, riesz, pde, norm)."""
+        data = self.boundary_loss(boundary_points, boundary_values)
+        riesz = self.riesz_loss(self.forward(collocation_points), collocation_points, eta)
+        pde, _, _ = self.pde_loss(collocation_points, self.forward(collocation_points), eta)
+        norm = (torch.norm(self.forward(collocation_points), p=2) - 1) ** 2
+        sym = self.symmetry_loss(collocation_points)
+        losses = [data, riesz, pde, norm, sym]
+        total = sum(w * t for w, t in zip(self.relobralo_weights(losses), losses))
+        return total, data, riesz, pde, norm
+
 
 def gpe2d_pointwise_terms(model, x, x_bc):
     """The *intended* (pointwise, all [N,1]) mathematics of S/gross_pitaevskii_2D.py:154-242:

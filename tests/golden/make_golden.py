@@ -314,6 +314,58 @@ def case_g2d(layers, n_pts, n_bc, g):
     return out
 
 
+def case_relobralo(layers, n_pts, n_bc, eta, calls=3):
+    """S/gross_pitaevskii_2D_ReLoBRaLo.py: total_loss called `calls` times on the same weights (the ReLoBRaLo state
+    evolves: call_count 0, 1, 2 take the three alpha branches of :322); torch.manual_seed(77) before the first call
+    fixes the bernoulli draws."""
+    mod = rl.load_script("gross_pitaevskii_2D_ReLoBRaLo.py")
+    mod.device = torch.device("cpu")
+    rng = np.random.default_rng(17)
+    Xn = rng.random((n_pts, 2)) * 4 - 2
+    Xb = rng.random((n_bc, 2)) * 4 - 2
+    Xb[: n_bc // 2, 0] = -2.0
+    Xb[n_bc // 2:, 1] = 2.0
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        xb = torch.tensor(Xb, dtype=dt)
+        bv = torch.zeros((n_bc, 1), dtype=dt)
+        torch.manual_seed(77)
+        out = {}
+        for c in range(calls):
+            total, data, riesz, pde, norm = model.total_loss(X, xb, bv, eta)
+            out[f"c{c}.total"], out[f"c{c}.lambdas"] = _np(total), np.array(model.lambdas)
+            if c == calls - 1:
+                out["grads"] = _grads(model, total)
+        pde, res, lam = model.pde_loss(X, model.forward(X), eta)
+        out.update(data=_np(data), riesz=_np(riesz), pde=_np(pde), norm=_np(norm), sym=_np(model.symmetry_loss(X)),
+                   mu=_np(lam), residual=_np(res))
+        return out
+
+    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers), init=xavier), run)
+    out.update(X=Xn, Xb=Xb, eta=eta, layers=np.array(layers), calls=calls)
+    return out
+
+
+def case_g2d_minimal(layers, n_pts, n_bc, g):
+    """S/gross_pitaevskii_2D_minimal.py: total_loss(x, x_bc, u_bc) (:201-222)."""
+    mod = rl.load_script("gross_pitaevskii_2D_minimal.py")
+    mod.device = torch.device("cpu")
+    rng = np.random.default_rng(19)
+    Xn = rng.random((n_pts, 2)) * np.pi
+    Xb = rng.random((n_bc, 2)) * np.pi
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        xb = torch.tensor(Xb, dtype=dt)
+        total = model.total_loss(X, xb, torch.zeros((n_bc, 1), dtype=dt))
+        return dict(total=_np(total), grads=_grads(model, total))
+
+    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers, g=g), init=xavier), run)
+    out.update(X=Xn, Xb=Xb, g=g, layers=np.array(layers))
+    return out
+
+
 # ------------------------------------------------------------------------------ Helmholtz
 def case_helmholtz(layers, n_pts, n_bc, act):
     mod = rl.load_script("helmholtz_2D.py")
@@ -446,6 +498,8 @@ def main():
         "opt_modes_m2_eta40": lambda: case_opt_variant("modes", 2, 40.0, [1, 64, 64, 64, 1], 600),
         "g2d_g100": lambda: case_g2d([2, 48, 48, 48, 1], 300, 40, 100.0),
         "g2d_g1_w128": lambda: case_g2d([2, 128, 128, 128, 128, 1], 160, 24, 1.0),
+        "g2d_relobralo_eta10": lambda: case_relobralo([2, 48, 48, 48, 1], 400, 40, 10.0),
+        "g2d_minimal_g50": lambda: case_g2d_minimal([2, 32, 32, 1], 200, 30, 50.0),
         "helmholtz_leaky": lambda: case_helmholtz([2, 40, 40, 40, 1], 300, 40, "leaky_relu"),
         "helmholtz_tanh": lambda: case_helmholtz([2, 100, 100, 100, 1], 200, 40, "tanh"),
         "helmholtz_circle": lambda: case_helmholtz_circle([2, 64, 64, 64, 1], 150),

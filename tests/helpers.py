@@ -3,6 +3,13 @@ import numpy as np
 import torch
 
 
+def scalar(v):
+    """float of a 0-dim / one-element tensor (with or without grad) or array."""
+    if torch.is_tensor(v):
+        return float(v.detach().reshape(-1)[0])
+    return float(np.asarray(v).reshape(-1)[0])
+
+
 def load_weights(model, g, prefix="w."):
     sd = {k[len(prefix):]: torch.tensor(v) for k, v in g.items() if k.startswith(prefix)}
     model.load_state_dict(sd)

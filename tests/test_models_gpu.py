@@ -10,7 +10,7 @@ import pytest
 import torch
 
 from oracle import pinn_oracle as po
-from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args, \
+from helpers import scalar, load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args, \
     OPT_VARIANT_GOLDENS, opt_variant_model_and_kwargs
 
 pytestmark = pytest.mark.gpu
@@ -19,7 +19,7 @@ GTOL = 2e-5
 
 
 def close(a, b, tol=TOL):
-    a, b = float(a.detach().reshape(-1)[0]) if torch.is_tensor(a) else float(a), float(np.asarray(b).reshape(-1)[0])
+    a, b = scalar(a), scalar(b)
     return abs(a - b) <= tol * max(abs(b), 1e-30)
 
 
@@ -271,6 +271,52 @@ def test_compat_g2d_and_helmholtz(golden):
     total = model.compute_loss(X, xb, ub, float(g["k"]))
     assert close(total, g["f64.total"], 2e-5)
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+
+
+def _relobralo_check(model, g, tol_scale=1.0):
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    bv = torch.zeros((xb.shape[0], 1), device="cuda")
+    eta = float(g["eta"])
+    torch.manual_seed(77)
+    for c in range(int(g["calls"])):
+        total, data, riesz, pde, norm = model.total_loss(X, xb, bv, eta)
+        assert close(total, g[f"f64.c{c}.total"], 2 * TOL * tol_scale), (c, float(total), float(g[f"f64.c{c}.total"]))
+        assert rel_err(np.array(model.lambdas), g[f"f64.c{c}.lambdas"]) < 2 * TOL * tol_scale, c
+    grads = model_grads(model, total)
+    _, res, lam = model.pde_loss(X, model.forward(X), eta)
+    for key, val in dict(data=data, riesz=riesz, pde=pde, sym=model.symmetry_loss(X), mu=lam).items():
+        assert close(val, g[f"f64.{key}"], 2 * TOL * tol_scale), (key, float(val), float(g[f"f64.{key}"]))
+    assert abs(float(norm) - float(g["f64.norm"])) <= 1e-4 * abs(float(g["f64.norm"])) + 1e-9
+    assert rel_err(res.detach().cpu().numpy(), g["f64.residual"]) < 5 * TOL * tol_scale
+    assert rel_err(flat(grads), flat(golden_grads(g, "f64.grads"))) < GTOL * tol_scale
+
+
+def test_relobralo_2d(golden):
+    """gpe_b200.ReLoBRaLoGPE2D (S/gross_pitaevskii_2D_ReLoBRaLo.py): FULL jets + one moment pass per residual column,
+    three calls of the ReLoBRaLo-weighted total, against the float64 run of the real class."""
+    import gpe_b200
+    g = golden("g2d_relobralo_eta10")
+    _relobralo_check(cuda_model(gpe_b200.ReLoBRaLoGPE2D, g, [int(v) for v in g["layers"]]), g)
+
+
+def test_compat_relobralo_2d(golden):
+    """The same file through patch(): its own loss code (Hessian.(1,1) by nested autograd.grad) on the jet node."""
+    from gpe_b200.models import patch
+    g = golden("g2d_relobralo_eta10")
+    _relobralo_check(patch(load_weights(po.ReLoBRaLoGPE2D([int(v) for v in g["layers"]]), g).cuda()), g, tol_scale=2.5)
+
+
+def test_g2d_minimal(golden):
+    """S/gross_pitaevskii_2D_minimal.py:201-222 total_loss on gpe_b200.GPE2D."""
+    import gpe_b200
+    g = golden("g2d_minimal_g50")
+    model = cuda_model(gpe_b200.GPE2D, g, [int(v) for v in g["layers"]], g=float(g["g"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    total = model.total_loss(X, xb, None)
+    assert close(total, g["f64.total"], 2 * TOL)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 def test_compat_helmholtz_circle(golden):

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import pinn_oracle as po
-from helpers import load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args, \
+from helpers import scalar, load_weights, golden_grads, flat, rel_err, model_grads, VARIANT_GOLDENS, variant_model_and_args, \
     OPT_VARIANT_GOLDENS, opt_variant_model_and_kwargs
 
 DT = {"f32": torch.float32, "f64": torch.float64}
@@ -15,7 +15,7 @@ TOL = {"f32": 2e-4, "f64": 1e-9}
 
 
 def close(a, b, tol):
-    a, b = float(a.detach().reshape(-1)[0]) if torch.is_tensor(a) else float(a), float(np.asarray(b).reshape(-1)[0])
+    a, b = scalar(a), scalar(b)
     return abs(a - b) <= tol * max(abs(b), 1e-30)
 
 
@@ -211,6 +211,43 @@ def test_opt_variants(golden, name, tag):
     for key, val in got.items():
         assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
     assert rel_err(flat(model_grads(model, ret[0])), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_relobralo_2d(golden, tag):
+    """S/gross_pitaevskii_2D_ReLoBRaLo.py: [N,2] residual with Hessian.(1,1), y-mirror, norm form and three calls of
+    the ReLoBRaLo-weighted total (call_count 0, 1, 2)."""
+    g = golden("g2d_relobralo_eta10")
+    dt = DT[tag]
+    model = load_weights(po.ReLoBRaLoGPE2D([int(v) for v in g["layers"]]), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=dt)
+    bv = torch.zeros((xb.shape[0], 1), dtype=dt)
+    eta = float(g["eta"])
+    torch.manual_seed(77)
+    for c in range(int(g["calls"])):
+        total, data, riesz, pde, norm = model.total_loss(X, xb, bv, eta)
+        assert close(total, g[f"{tag}.c{c}.total"], TOL[tag]), c
+        assert rel_err(np.array(model.lambdas), g[f"{tag}.c{c}.lambdas"]) < TOL[tag], c
+    grads = model_grads(model, total)
+    _, res, lam = model.pde_loss(X, model.forward(X), eta)
+    for key, val in dict(data=data, riesz=riesz, pde=pde, norm=norm, sym=model.symmetry_loss(X), mu=lam).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(res.detach().numpy(), g[f"{tag}.residual"]) < TOL[tag]
+    assert rel_err(flat(grads), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_g2d_minimal(golden, tag):
+    """S/gross_pitaevskii_2D_minimal.py:201-222 total_loss."""
+    g = golden("g2d_minimal_g50")
+    dt = DT[tag]
+    model = load_weights(po.GPE2D([int(v) for v in g["layers"]], g=float(g["g"])), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=dt)
+    total = model.total_loss(X, xb, None)
+    assert close(total, g[f"{tag}.total"], TOL[tag])
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
 
 
 def test_helmholtz_circle(golden):
