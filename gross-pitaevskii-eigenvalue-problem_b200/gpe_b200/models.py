@@ -405,12 +405,15 @@ class FinalGPE1D(_GPE1DBase):
     R/harmonic_pinn_simulation.py:52-217; `potential='box'` follows R/box_pinn_simulation.py:52-262,
     `potential='gravity_well'` R/gravity_well_pinn_simulation.py:53-256 (Airy base, V = x)."""
 
-    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, use_perturbation=True, potential="harmonic", L=1.0):
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, use_perturbation=True, potential="harmonic", L=1.0,
+                 enforce_boundary=None):
         super().__init__()
         self.layers = layers
         self.network = _sequential(layers, ShiftedTanh)
         self.hbar, self.m, self.mode, self.gamma = hbar, m, mode, gamma
         self.use_perturbation, self.potential, self.L = use_perturbation, potential, L
+        # R/plot_box_potential_at_ground_state.py:58-91,124-137: the factor as an option (off for its vanilla PINN)
+        self.enforce_boundary = (potential == "box") if enforce_boundary is None else enforce_boundary
 
     def weighted_hermite(self, x, n):
         return hermite_base_jets(x, n, const_h=False)[:, :1]
@@ -421,7 +424,7 @@ class FinalGPE1D(_GPE1DBase):
     @property
     def _has_factor(self):
         """forward() multiplies the network by sin(pi x) (R/box_pinn_simulation.py:119-130)."""
-        return self.potential == "box"
+        return bool(self.enforce_boundary)
 
     def forward(self, inputs):
         out = self._net(inputs)

@@ -244,13 +244,16 @@ class FinalGPE1D(nn.Module):
     given, its second derivative by np.gradient; V = x)."""
 
     def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, use_perturbation=True,
-                 potential="harmonic", L=1.0):
+                 potential="harmonic", L=1.0, enforce_boundary=None):
         super().__init__()
         self.layers = layers
         self.network = sequential_mlp(layers, ShiftedTanh)
         self.hbar, self.m, self.mode, self.gamma = hbar, m, mode, gamma
         self.use_perturbation = use_perturbation
         self.potential, self.L = potential, L
+        # R/plot_box_potential_at_ground_state.py:58-91,124-137 makes the sin(pi x) factor of the box forward an
+        # option (False for its vanilla PINN); None = the box script's behaviour (always on)
+        self.enforce_boundary = (potential == "box") if enforce_boundary is None else enforce_boundary
 
     def weighted_hermite(self, x, n):
         return hermite_state_torch(x, n)
@@ -272,7 +275,7 @@ class FinalGPE1D(nn.Module):
 
     def forward(self, inputs):
         out = self.network(inputs)
-        if self.potential == "box":                      # R/box_pinn_simulation.py:119-130
+        if self.enforce_boundary:                        # R/box_pinn_simulation.py:119-130
             out = out * torch.sin(torch.pi * inputs)
         return out
 

@@ -168,12 +168,16 @@ def case_final_fixture(kind):
     return out
 
 
-def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic"):
+def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=None):
+    """ctor_kw: the extra constructor options of R/plot_box_potential_at_ground_state.py:58-91 (kind='plot_box':
+    use_perturbation / enforce_boundary, its vanilla PINN has both off)."""
     script = {"harmonic": "final/refine/harmonic_pinn_simulation.py", "box": "final/refine/box_pinn_simulation.py",
-              "gravity_well": "final/refine/gravity_well_pinn_simulation.py"}[kind]
+              "gravity_well": "final/refine/gravity_well_pinn_simulation.py",
+              "plot_box": "final/refine/plot_box_potential_at_ground_state.py"}[kind]
     mod = rl.load_script(script)
     mod.device = torch.device("cpu")
-    lb, ub = {"harmonic": (-10.0, 10.0), "box": (0.0, 1.0), "gravity_well": (0.0, 35.0)}[kind]
+    ctor_kw = ctor_kw or {}
+    lb, ub = {"harmonic": (-10.0, 10.0), "box": (0.0, 1.0), "gravity_well": (0.0, 35.0), "plot_box": (0.0, 1.0)}[kind]
     Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
     if kind == "gravity_well":
         Xn = Xn.astype(np.float32).astype(np.float64)      # see case_final_fixture
@@ -187,13 +191,14 @@ def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic"):
         u_pred = pc * model.forward(X) / const
         bc = model.boundary_loss(bp, bv)
         nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
-        pde, mu = model.pde_loss(X, u_pred, gamma, p, kind)
+        pde, mu = model.pde_loss(X, u_pred, gamma, p, "box" if kind == "plot_box" else kind)
         total = pde + 10.0 * bc + 20.0 * nrm
         return dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), total=_np(total), mu=_np(mu), grads=_grads(model, total))
 
-    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, gamma=gamma), init=xavier), run)
+    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, gamma=gamma, **ctor_kw), init=xavier), run)
     out.update(X=Xn, dx=dx, lb=lb, ub=ub, mode=mode, p=p, gamma=gamma, const=const, perturb_const=pc,
-               layers=np.array(layers))
+               layers=np.array(layers), use_perturbation=ctor_kw.get("use_perturbation", True),
+               enforce_boundary=ctor_kw.get("enforce_boundary", kind == "box"))
     return out
 
 
@@ -478,6 +483,10 @@ def main():
         "final_harmonic_g20_p3_m1": lambda: case_final_random(20.0, 3, 1, [1, 64, 64, 64, 1], 900),
         "final_harmonic_g5_p4_m2": lambda: case_final_random(5.0, 4, 2, [1, 48, 48, 1], 500),
         "final_box_g10_p3_m0": lambda: case_final_random(10.0, 3, 0, [1, 64, 64, 64, 1], 800, kind="box"),
+        "final_box_vanilla_g10_p3_m0": lambda: case_final_random(
+            10.0, 3, 0, [1, 64, 64, 64, 1], 700, kind="plot_box", ctor_kw=dict(use_perturbation=False, enforce_boundary=False)),
+        "final_box_option_g5_p3_m1": lambda: case_final_random(
+            5.0, 3, 1, [1, 48, 48, 1], 500, kind="plot_box", ctor_kw=dict(use_perturbation=True, enforce_boundary=True)),
         "final_gravity_fixture": lambda: case_final_fixture("gravity_well"),
         "final_gravity_g10_p3_m1": lambda: case_final_random(10.0, 3, 1, [1, 64, 64, 64, 1], 1200, kind="gravity_well"),
         "vary_harmonic_b0.6_g5_p3_m1": lambda: case_variant("harmonic", 1, 0.6, 5.0, 3, 900),

@@ -70,12 +70,14 @@ def test_paper_notebook(golden, name):
 
 
 @pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
-                                       ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well")])
+                                       ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well"),
+                                       ("final_box_vanilla_g10_p3_m0", "box"), ("final_box_option_g5_p3_m1", "box")])
 def test_final_random(golden, name, kind):
     import gpe_b200
     g = golden(name)
+    opts = {k: bool(g[k]) for k in ("use_perturbation", "enforce_boundary") if k in g}   # plot_box_potential_at_ground_state.py
     model = cuda_model(gpe_b200.FinalGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
-                       potential=kind)
+                       potential=kind, **opts)
     X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
     lb, ub = float(g["lb"]), float(g["ub"])
     bp = torch.tensor([[lb], [ub]], device="cuda")

@@ -92,13 +92,15 @@ def test_final_fixture_mu_table(golden, kind):
 
 
 @pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
-                                       ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well")])
+                                       ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well"),
+                                       ("final_box_vanilla_g10_p3_m0", "box"), ("final_box_option_g5_p3_m1", "box")])
 @pytest.mark.parametrize("tag", ["f64", "f32"])
 def test_final_random(golden, name, kind, tag):
     g = golden(name)
     dt = DT[tag]
+    opts = {k: bool(g[k]) for k in ("use_perturbation", "enforce_boundary") if k in g}   # plot_box_potential_at_ground_state.py
     model = load_weights(po.FinalGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
-                                       potential=kind), g).to(dt)
+                                       potential=kind, **opts), g).to(dt)
     X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
     lb, ub = float(g["lb"]), float(g["ub"])
     bp = torch.tensor([[lb], [ub]], dtype=dt)
