@@ -168,7 +168,7 @@ def case_final_fixture(kind):
     return out
 
 
-def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=None):
+def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=None, shipped=None):
     """ctor_kw: the extra constructor options of R/plot_box_potential_at_ground_state.py:58-91 (kind='plot_box':
     use_perturbation / enforce_boundary, its vanilla PINN has both off)."""
     script = {"harmonic": "final/refine/harmonic_pinn_simulation.py", "box": "final/refine/box_pinn_simulation.py",
@@ -182,7 +182,13 @@ def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=No
     if kind == "gravity_well":
         Xn = Xn.astype(np.float32).astype(np.float64)      # see case_final_fixture
     dx = float(Xn[1, 0] - Xn[0, 0])
-    const, pc = 0.37, 0.01
+    const, pc, state = 0.37, 0.01, None
+    if shipped is not None:
+        # shipped = (pickle, dict key, normalisation constant): trained weights of a comparison_results_* file.  No
+        # script in the reference writes or reads these files; for the negative-gamma one the protocol
+        # u_pred = 0.01 model(X) (constants are None) reproduces mu(gamma=0) = 1, 3, 5 to 2e-4, which fixes it.
+        entry = rl.load_pickle(shipped[0])[shipped[1]][mode][gamma]
+        layers, state, const = entry["layers"], entry["state_dict"], shipped[2]
 
     def run(model, dt):
         X = torch.tensor(Xn, dtype=dt, requires_grad=True)
@@ -195,7 +201,15 @@ def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=No
         total = pde + 10.0 * bc + 20.0 * nrm
         return dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), total=_np(total), mu=_np(mu), grads=_grads(model, total))
 
-    out = _both_dtypes(seeded(lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, gamma=gamma, **ctor_kw), init=xavier), run)
+    seeded_build = seeded(lambda: mod.GrossPitaevskiiPINN(layers, mode=mode, gamma=gamma, **ctor_kw), init=xavier)
+
+    def build():
+        m = seeded_build()
+        if state is not None:
+            m.load_state_dict(state)
+        return m
+
+    out = _both_dtypes(build, run)
     out.update(X=Xn, dx=dx, lb=lb, ub=ub, mode=mode, p=p, gamma=gamma, const=const, perturb_const=pc,
                layers=np.array(layers), use_perturbation=ctor_kw.get("use_perturbation", True),
                enforce_boundary=ctor_kw.get("enforce_boundary", kind == "box"))
@@ -487,6 +501,9 @@ def main():
             10.0, 3, 0, [1, 64, 64, 64, 1], 700, kind="plot_box", ctor_kw=dict(use_perturbation=False, enforce_boundary=False)),
         "final_box_option_g5_p3_m1": lambda: case_final_random(
             5.0, 3, 1, [1, 48, 48, 1], 500, kind="plot_box", ctor_kw=dict(use_perturbation=True, enforce_boundary=True)),
+        "final_neg_gamma_shipped_m1_gm8": lambda: case_final_random(
+            -8, 3, 1, None, 4000, shipped=("comparison_results_neg_int_strength_p3_harmonic/curriculum_pinn_models_p3_harmonic.pkl",
+                                           "curriculum_state_dicts", 1.0)),
         "final_gravity_fixture": lambda: case_final_fixture("gravity_well"),
         "final_gravity_g10_p3_m1": lambda: case_final_random(10.0, 3, 1, [1, 64, 64, 64, 1], 1200, kind="gravity_well"),
         "vary_harmonic_b0.6_g5_p3_m1": lambda: case_variant("harmonic", 1, 0.6, 5.0, 3, 900),

@@ -71,7 +71,8 @@ def test_paper_notebook(golden, name):
 
 @pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
                                        ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well"),
-                                       ("final_box_vanilla_g10_p3_m0", "box"), ("final_box_option_g5_p3_m1", "box")])
+                                       ("final_box_vanilla_g10_p3_m0", "box"), ("final_box_option_g5_p3_m1", "box"),
+                                       ("final_neg_gamma_shipped_m1_gm8", "harmonic")])
 def test_final_random(golden, name, kind):
     import gpe_b200
     g = golden(name)
