@@ -12,6 +12,8 @@ What is here
                         reference file:line it follows.
 * `jet_oracle`       -- per-point value / gradient / Hessian of the MLP and the parameter
                         gradient of a weighted jet functional, by autograd in fp64.
+* `train_oracle`     -- the paper's curriculum driver (`train_gpe_model`, R/harmonic_pinn_simulation.py:220-431) on
+                        the oracle classes with torch's own scheduler, to check `gpe_b200.training`.
 * `reference_loader` -- imports the *real* reference classes from /root/reference (exists only
                         in the build container) to pin the restatement and to generate the
                         golden vectors under `tests/golden/` (script: tests/golden/make_golden.py).

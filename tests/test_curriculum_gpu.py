@@ -1,0 +1,113 @@
+"""gpe_b200.training.train_gpe_model (CUDA-graph curriculum driver) against the CPU restatement of the
+reference driver (oracle/train_oracle.py: R/harmonic_pinn_simulation.py:220-431 with torch's own
+CosineAnnealingWarmRestarts), and the reference's pickle bundle (8f-3)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import pinn_oracle as po
+from oracle import train_oracle
+from helpers import rel_err
+
+pytestmark = pytest.mark.gpu
+
+LAYERS, LB, UB, N = [1, 64, 64, 64, 1], -10.0, 10.0, 1000
+
+
+def _init_state(seed=5):
+    torch.manual_seed(seed)
+    m = po.FinalGPE1D(LAYERS, mode=0, gamma=0.0)
+    m.apply(po.xavier_bias001_)
+    return {k: v.clone() for k, v in m.state_dict().items()}
+
+
+def _X():
+    return np.linspace(LB, UB, N).reshape(-1, 1)
+
+
+def _max_rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b) / np.abs(b)))
+
+
+@pytest.mark.parametrize("use_graph", [True, False])
+def test_two_stage_curriculum_follows_the_reference_driver(use_graph):
+    """Two gamma stages x 30 epochs from the same weights: every epoch's loss and mu in the device rings follow the
+    float64 CPU driver.  The learning rate is a function of the loss through the scheduler call, so this also checks
+    the device-side restatement of CosineAnnealingWarmRestarts.step(loss).  lr = 1e-4: at 1e-3 this loop amplifies an
+    fp32-vs-fp64 difference x1.3 per epoch (tests/test_training_gpu.py) and 60 epochs say nothing."""
+    from gpe_b200 import training
+    init, X = _init_state(), _X()
+    args = dict(gamma_values=[0.0, 2.0], modes=[0], p=3, X_train=X, lb=LB, ub=UB, layers=LAYERS, epochs=30, tol=1e-12,
+                perturb_const=0.01, potential_type="harmonic", lr=1e-4)
+    ref = train_oracle.train_gpe_model(init_state={k: v.double() for k, v in init.items()}, **args)
+    got = training.train_gpe_model(verbose=False, init_state=init, use_graph=use_graph, check_every=7, keep_rings=True, **args)
+    assert abs(float(got[3][0]) - float(ref[3][0])) < 1e-5 * abs(float(ref[3][0]))          # normalisation constant
+    for gamma in (0.0, 2.0):
+        r = np.array(ref[2][0][gamma]["per_epoch"])
+        g = got[2][0][gamma]["per_epoch"]
+        assert g.shape == (3, 30) and got[4][0][gamma] == ref[4][0][gamma] == 30
+        assert _max_rel(g[0], r[:, 0]) < 2e-4, (gamma, g[0][-3:], r[-3:, 0])
+        assert _max_rel(g[1], r[:, 1]) < 1e-4
+        assert _max_rel(g[2], r[:, 2]) < 2e-3       # (sum u^2 dx - 1)^2 squares an fp32 difference
+        assert _max_rel(got[2][0][gamma]["loss"], ref[2][0][gamma]["loss"]) < 2e-4
+        assert len(got[2][0][gamma]["lambda"]) == len(ref[2][0][gamma]["lambda"]) == 1
+    assert _max_rel([m for _, m in got[1][0]], [m for _, m in ref[1][0]]) < 1e-4
+
+
+def test_device_side_early_stop_restores_the_reference_stop_state():
+    """tol chosen so the CPU driver leaves the loop at epoch e < epochs: the graph driver, which looks at the device
+    flag only every 6 epochs and so runs past e, must report e and end with the parameters of epoch e."""
+    from gpe_b200 import training
+    init, X = _init_state(9), _X()
+    args = dict(gamma_values=[0.0], modes=[0], p=3, X_train=X, lb=LB, ub=UB, layers=LAYERS, epochs=60,
+                perturb_const=0.01, potential_type="harmonic", lr=1e-4)
+    probe = train_oracle.train_gpe_model(init_state={k: v.double() for k, v in init.items()}, tol=1e-12, **args)
+    losses = np.array(probe[2][0][0.0]["per_epoch"])[:, 0]
+    cand = [e for e in range(15, 45) if losses[e] < losses[:e].min() * 0.999]      # a clear new minimum
+    assert cand, losses[:45]
+    e = cand[len(cand) // 2]
+    tol = float(0.5 * (losses[e] + losses[:e].min()))
+    ref = train_oracle.train_gpe_model(init_state={k: v.double() for k, v in init.items()}, tol=tol, **args)
+    got = training.train_gpe_model(verbose=False, init_state=init, tol=tol, check_every=6, **args)
+    assert ref[4][0][0.0] == e and got[4][0][0.0] == e
+    pr = torch.cat([q.detach().reshape(-1) for q in ref[0][0][0.0].parameters()])
+    pg = torch.cat([q.detach().reshape(-1).cpu().double() for q in got[0][0][0.0].parameters()])
+    assert float((pr - pg).norm() / pr.norm()) < 1e-5
+    assert len(got[2][0][0.0]["loss"]) == len(ref[2][0][0.0]["loss"]) == e // 10 + 1
+
+
+def test_pickle_bundle_round_trip_and_reference_fixture(tmp_path, golden):
+    """save_models writes the reference's bundle layout; load_models reads it back -- and reads a bundle built from the
+    reference's shipped weights (tests/golden/final_harmonic_fixture.npz), reproducing its mu_table."""
+    import pickle
+    import gpe_b200
+    from gpe_b200 import training
+    g = golden("final_harmonic_fixture")
+    bundle, consts = {}, {}
+    for mode in range(3):
+        sd = {k[len(f"m{mode}.w."):]: torch.tensor(v) for k, v in g.items() if k.startswith(f"m{mode}.w.")}
+        bundle[mode] = {0: dict(state_dict=sd, layers=[int(v) for v in g[f"m{mode}.layers"]], hbar=1.0, m=1.0, mode=mode, gamma=0)}
+        consts[mode] = torch.tensor(float(g[f"m{mode}.const"]))
+    with open(tmp_path / "ref.pkl", "wb") as fh:
+        pickle.dump(dict(models_state_dicts=bundle, mu_table={}, training_history={}, constant_history=consts,
+                         epochs_history={}), fh)
+    models, _, _, constants, _ = training.load_models("ref.pkl", str(tmp_path))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    for mode in range(3):
+        model = models[mode][0]
+        assert isinstance(model, gpe_b200.FinalGPE1D) and next(model.parameters()).is_cuda
+        _, mu = model.pde_loss(X, 0.01 * model.forward(X) / float(constants[mode]), 0.0, 3)
+        assert abs(float(mu) - float(g[f"m{mode}.mu_table"])) < 2e-5 * abs(float(g[f"m{mode}.mu_table"]))
+    path = training.save_models(models, {0: [(0, 1.0)]}, {0: {0: {"loss": [1.0], "constraint": [], "lambda": []}}}, constants,
+                                {0: {0: 5}}, "out.pkl", str(tmp_path))
+    with open(path, "rb") as fh:
+        data = pickle.load(fh)
+    assert sorted(data) == ["constant_history", "epochs_history", "models_state_dicts", "mu_table", "training_history"]
+    entry = data["models_state_dicts"][1][0]
+    assert sorted(entry) == ["gamma", "hbar", "layers", "m", "mode", "state_dict"] and entry["mode"] == 1
+    assert all(not v.is_cuda for v in entry["state_dict"].values())
+    assert list(entry["state_dict"]) == list(bundle[1][0]["state_dict"])
+    again = training.load_models("out.pkl", str(tmp_path))[0]
+    for a, b in zip(again[2][0].parameters(), models[2][0].parameters()):
+        assert torch.equal(a, b)

@@ -233,3 +233,22 @@ def test_shard_bounds_cover_ragged_sizes():
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             sizes = [hi - lo for lo, hi in spans]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_loss_as_epoch_learning_rate_matches_torch_scheduler():
+    """gpe_b200.training._loss_as_epoch_lr restates `CosineAnnealingWarmRestarts(T_0=200, T_mult=2, eta_min=1e-6)
+    .step(total_loss)` (R/harmonic_pinn_simulation.py:347-349,391) as tensor arithmetic: compare with the scheduler
+    itself, both branches (loss < T_0 and the restart branch loss >= T_0)."""
+    import warnings
+    from torch.optim.lr_scheduler import CosineAnnealingWarmRestarts
+    from gpe_b200.training import _loss_as_epoch_lr
+    base = 1e-3
+    opt = torch.optim.Adam([torch.nn.Parameter(torch.zeros(1))], lr=base)
+    sched = CosineAnnealingWarmRestarts(opt, T_0=200, T_mult=2, eta_min=1e-6)
+    for loss in [0.0, 1e-6, 0.37, 23.18, 150.0, 199.99, 200.0, 333.3, 599.9, 600.0, 1234.5, 9.9e4]:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            sched.step(torch.tensor(loss))
+        want = opt.param_groups[0]["lr"]
+        got = float(_loss_as_epoch_lr(torch.tensor(loss, dtype=torch.float64), base))
+        assert abs(got - want) <= 1e-9 * base + 1e-6 * abs(want), (loss, got, want)   # the scheduler works on the float32 tensor
