@@ -95,7 +95,7 @@ __global__ void finish_grads_kernel(const float* __restrict__ dWacc, int n_cta, 
 
 // ---------------------------------------------------------------- plan cache
 struct PlanKey {
-    int d, jet, wp, L, dev;
+    int d, jet, wp, L, dev, res;
 };
 struct PlanEntry {
     PlanKey k;
@@ -111,7 +111,12 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
     if (!desc) { set_error("null descriptor"); return -1; }
     if (desc->d != 1 && desc->d != 2) { set_error("d must be 1 or 2 (got %d)", desc->d); return -1; }
     if (desc->n_hidden < 1 || desc->n_hidden > kMaxLayers) { set_error("n_hidden must be in [1,%d]", kMaxLayers); return -1; }
-    if (desc->act < 0 || desc->act > 2) { set_error("unknown activation %d", desc->act); return -1; }
+    if (desc->act < 0 || desc->act > 3) { set_error("unknown activation %d", desc->act); return -1; }
+    const int res = desc->act == ACT_RESBLOCK_TANH;
+    if (res && !(desc->n_hidden & 1)) {
+        set_error("residual-block network: n_hidden must be 1 + 2 * blocks (got %d)", desc->n_hidden);
+        return -1;
+    }
     if (desc->jet < 0 || desc->jet > 3) { set_error("unknown jet kind %d", desc->jet); return -1; }
     const int wp = padded_width(desc->width);
     if (desc->width < 1 || !wp) { set_error("hidden width %d unsupported (1..256)", desc->width); return -1; }
@@ -121,17 +126,17 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
     std::lock_guard<std::mutex> lk(g_plan_mu);
     for (int i = 0; i < g_n_plans; ++i) {
         const PlanKey& k = g_plans[i].k;
-        if (k.d == desc->d && k.jet == desc->jet && k.wp == wp && k.L == desc->n_hidden && k.dev == dev) {
+        if (k.d == desc->d && k.jet == desc->jet && k.wp == wp && k.L == desc->n_hidden && k.dev == dev && k.res == res) {
             *out = g_plans[i].p;
             return 0;
         }
     }
     JetPlan p;
-    const int rc = wp == 64    ? plan_wp64(desc->d, desc->jet, desc->n_hidden, &p)
-                   : wp == 128 ? plan_wp128(desc->d, desc->jet, desc->n_hidden, &p)
-                               : plan_wp256(desc->d, desc->jet, desc->n_hidden, &p);
+    const int rc = wp == 64    ? plan_wp64(desc->d, desc->jet, desc->n_hidden, res, &p)
+                   : wp == 128 ? plan_wp128(desc->d, desc->jet, desc->n_hidden, res, &p)
+                               : plan_wp256(desc->d, desc->jet, desc->n_hidden, res, &p);
     if (rc) return rc;
-    if (g_n_plans < 64) g_plans[g_n_plans++] = PlanEntry{PlanKey{desc->d, desc->jet, wp, desc->n_hidden, dev}, p};
+    if (g_n_plans < 64) g_plans[g_n_plans++] = PlanEntry{PlanKey{desc->d, desc->jet, wp, desc->n_hidden, dev, res}, p};
     *out = p;
     return 0;
 }
@@ -167,7 +172,7 @@ WsLayout layout(const gpe_mlp_desc* desc, const JetPlan& p, int wp, long long n)
     w.wt_fwd = off; off = align_up(off + mat);
     w.w_bwd = off; off = align_up(off + mat);
     w.small = off; off = align_up(off + w.n_small * sizeof(float));
-    w.tc = tc_enabled() && tc_eligible(desc->d, desc->jet, desc->width, L);
+    w.tc = tc_enabled() && desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, L);
     w.wimg = off;
     if (w.tc) off = align_up(off + tc_wimg_bytes(L));
     w.total_fwd = off;
@@ -329,7 +334,7 @@ int gpe_stash_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* bytes) {
     const int rc = get_plan(desc, &p, &wp);
     if (rc) return rc;
     if (n < 0 || !bytes) { set_error("gpe_stash_bytes: bad arguments"); return -1; }
-    const bool tc = tc_enabled() && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
+    const bool tc = tc_enabled() && desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
     *bytes = (tc && n > 0) ? tc_resident_stash_bytes(desc->n_hidden, n) : 0;
     return 0;
 }

@@ -28,7 +28,14 @@ constexpr int kStages = 4;
 constexpr int kMaxLayers = 8;              // hidden layers
 constexpr int kPad = 4;                    // smem row padding (floats)
 
-enum Act { ACT_TANH = 0, ACT_SHIFTED_TANH = 1, ACT_LEAKY_RELU = 2 };
+// ACT_RESBLOCK_TANH: the residual network of R/box_to_gaussian_pinn_simulation.py:52-62,100-130 --
+// layer 0 ShiftedTanh, then blocks tanh(lin2(tanh(lin1(a))) + a): hidden layers 2k+1 / 2k+2 are lin1 / lin2 of block
+// k, all tanh, and the jets of a_{2k} are added to the pre-activation jets of layer 2k+2 (the skip is linear, so
+// every stream passes through it unchanged).
+enum Act { ACT_TANH = 0, ACT_SHIFTED_TANH = 1, ACT_LEAKY_RELU = 2, ACT_RESBLOCK_TANH = 3 };
+__host__ __device__ constexpr int layer_act(int act, int l) {
+    return act == ACT_RESBLOCK_TANH ? (l == 0 ? ACT_SHIFTED_TANH : ACT_TANH) : act;
+}
 enum Jet { JET_VALUE = 0, JET_DIAG = 1, JET_FULL = 2, JET_LAPLACIAN = 3 };
 
 // number of streams per point

@@ -24,7 +24,7 @@ struct JetPlan {          // resolved launch geometry for (d, jet, WP, L)
 
 // implemented once per padded width (jet_launch.cu compiled with -DGPE_WP=...)
 #define GPE_DECL_WP(WP)                                                                                          \
-    int plan_wp##WP(int d, int jet, int L, JetPlan* plan);                                                       \
+    int plan_wp##WP(int d, int jet, int L, bool res, JetPlan* plan);                                                     \
     int launch_fwd_wp##WP(int d, int jet, const MlpParams& P, const float* x, long long n, const XForm& xf,      \
                           float* u, float* g, float* h, int grid, int num_tiles, cudaStream_t s);                \
     int launch_bwd_wp##WP(int d, int jet, const MlpParams& P, const float* x, long long n, const XForm& xf,      \

@@ -21,14 +21,36 @@ struct TileCfg {
     static constexpr int PTS = TY * TP;    // points per CTA tile
     static constexpr int LDA = WP + kPad;
     static constexpr int STASH_F4 = TR * 2;  // float4 per thread per layer
-    __host__ __device__ static size_t smem_fwd(int L) {
-        return (size_t)M * LDA * 4 + (size_t)kStages * KC * WP * 4 + ((size_t)(D + L + 1) * WP + 4) * 4 + 2 * kStages * 8;
+    __host__ __device__ static size_t smem_fwd(int L, bool res = false) {
+        return (size_t)M * LDA * 4 + (size_t)kStages * KC * WP * 4 + ((size_t)(D + L + 1) * WP + 4) * 4 + 2 * kStages * 8 +
+               (res ? STASH_F4 * kConsumers * 16 : 0);
     }
-    __host__ __device__ static size_t smem_bwd(int L) {
-        return smem_fwd(L) + (size_t)M * LDA * 4 + ((size_t)(D + L + 1) * WP + 4) * 4;
+    __host__ __device__ static size_t smem_bwd(int L, bool res = false) {
+        return smem_fwd(L, false) + (size_t)M * LDA * 4 + ((size_t)(D + L + 1) * WP + 4) * 4 + (res ? STASH_F4 * kConsumers * 16 : 0);
     }
     __host__ __device__ static size_t stash_floats_per_cta(int L) { return (size_t)L * STASH_F4 * 4 * kConsumers; }
+    // residual nets (smem_*(L, true)): a thread-private copy of the tile -- the block input going forward, zbar of lin2
+    // going back
 };
+
+// thread-private, conflict-free [TR*2][kConsumers] float4 image of a thread's TR x 8 tile
+template <int TR>
+__device__ __forceinline__ void skip_save(float4* sk, const float (&v)[TR][8]) {
+#pragma unroll
+    for (int r = 0; r < TR; ++r) {
+        sk[(size_t)(2 * r) * kConsumers] = make_float4(v[r][0], v[r][1], v[r][2], v[r][3]);
+        sk[(size_t)(2 * r + 1) * kConsumers] = make_float4(v[r][4], v[r][5], v[r][6], v[r][7]);
+    }
+}
+template <int TR>
+__device__ __forceinline__ void skip_add(const float4* sk, float (&v)[TR][8]) {
+#pragma unroll
+    for (int r = 0; r < TR; ++r) {
+        const float4 a = sk[(size_t)(2 * r) * kConsumers], b = sk[(size_t)(2 * r + 1) * kConsumers];
+        v[r][0] += a.x, v[r][1] += a.y, v[r][2] += a.z, v[r][3] += a.w;
+        v[r][4] += b.x, v[r][5] += b.y, v[r][6] += b.z, v[r][7] += b.w;
+    }
+}
 
 __device__ __forceinline__ int col_of(int tx, int j, int WP) { return j < 4 ? 4 * tx + j : WP / 2 + 4 * tx + (j - 4); }
 
@@ -62,7 +84,7 @@ __device__ __forceinline__ void first_layer(float (&acc)[TP * R][8], const float
 // ------------------------------------------------------------------------------------------
 // forward: per point u, grad u, second derivatives
 // ------------------------------------------------------------------------------------------
-template <int D, int JET, int WP>
+template <int D, int JET, int WP, bool RES = false>
 __global__ void __launch_bounds__(kThreads)
 jet_fwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, float* __restrict__ out_u,
                float* __restrict__ out_g, float* __restrict__ out_h, int num_tiles) {
@@ -75,6 +97,7 @@ jet_fwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
     const int L = P.n_hidden;
     const int n_small = (D + L + 1) * WP + 4;
     uint64_t* bars = reinterpret_cast<uint64_t*>(small + n_small);
+    float4* skip = reinterpret_cast<float4*>(bars + 2 * kStages) + threadIdx.x;
 
     const int tid = threadIdx.x;
     WeightPipe<WP> pipe{stages, bars, bars + kStages, 0u};
@@ -108,6 +131,8 @@ jet_fwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
         float acc[TR][8];
         first_layer<D, JET, WP, TP, R>(acc, xin, W0t, bias, tx);
         for (int l = 0;; ++l) {
+            if (RES && !(l & 1) && l >= 2) skip_add<TR>(skip, acc);  // z_l += a_{l-2}
+            const int act_l = RES ? layer_act(ACT_RESBLOCK_TANH, l) : act;
             // activation jets, thread-local
 #pragma unroll
             for (int tp = 0; tp < TP; ++tp)
@@ -117,11 +142,12 @@ jet_fwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
 #pragma unroll
                     for (int s = 0; s < R; ++s) z[s] = acc[tp * R + s][j];
                     float st0;
-                    act_jet_fwd<D, JET>(z, act, st0);
+                    act_jet_fwd<D, JET>(z, act_l, st0);
 #pragma unroll
                     for (int s = 0; s < R; ++s) acc[tp * R + s][j] = z[s];
                 }
             if (l == L - 1) break;
+            if (RES && !(l & 1)) skip_save<TR>(skip, acc);  // block input
             consumer_sync();  // everybody finished reading As (previous layer / previous tile)
             store_tile<TR, WP>(As, row0, tx, acc);
             consumer_sync();
@@ -218,7 +244,7 @@ __device__ __forceinline__ void dw_gemm_accumulate(const float* __restrict__ Zb,
     }
 }
 
-template <int D, int JET, int WP>
+template <int D, int JET, int WP, bool RES = false>
 __global__ void __launch_bounds__(kThreads)
 jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, const float* __restrict__ u_bar,
                const float* __restrict__ g_bar, const float* __restrict__ h_bar, float* __restrict__ stash_all,
@@ -234,6 +260,7 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
     uint64_t* bars = reinterpret_cast<uint64_t*>(small + n_small);
     float* Zb = reinterpret_cast<float*>(bars + 2 * kStages);
     float* gacc = Zb + (size_t)C::M * LDA;  // same layout as `small`: dW0t[D][WP], db[L][WP], dwout[WP], dbout
+    float4* skip = reinterpret_cast<float4*>(gacc + n_small) + threadIdx.x;
 
     const int tid = threadIdx.x;
     WeightPipe<WP> pipe{stages, bars, bars + kStages, 0u};
@@ -278,6 +305,8 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
         // ---------------- forward recompute with stash ----------------
         first_layer<D, JET, WP, TP, R>(acc, xin, W0t, bias, tx);
         for (int l = 0;; ++l) {
+            if (RES && !(l & 1) && l >= 2) skip_add<TR>(skip, acc);  // z_l += a_{l-2}
+            const int act_l = RES ? layer_act(ACT_RESBLOCK_TANH, l) : act;
             float4* sl = stash + (size_t)l * C::STASH_F4 * kConsumers + tid;
 #pragma unroll
             for (int tp = 0; tp < TP; ++tp)
@@ -292,7 +321,7 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
                         for (int s = 0; s < R; ++s) z[s] = acc[tp * R + s][j];
 #pragma unroll
                         for (int s = 1; s < R; ++s) sv[s][jj] = z[s];
-                        act_jet_fwd<D, JET>(z, act, sv[0][jj]);
+                        act_jet_fwd<D, JET>(z, act_l, sv[0][jj]);
 #pragma unroll
                         for (int s = 0; s < R; ++s) acc[tp * R + s][j] = z[s];
                     }
@@ -301,6 +330,7 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
                         sl[(size_t)((tp * R + s) * 2 + hf) * kConsumers] = make_float4(sv[s][0], sv[s][1], sv[s][2], sv[s][3]);
                 }
             if (l == L - 1) break;
+            if (RES && !(l & 1)) skip_save<TR>(skip, acc);  // block input
             consumer_sync();
             store_tile<TR, WP>(As, row0, tx, acc);
             consumer_sync();
@@ -343,6 +373,8 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
         }
         // ---------------- hidden layers, top down ----------------
         for (int l = L - 1;; --l) {
+            if (RES && !(l & 1) && l < L - 1) skip_add<TR>(skip, acc);  // abar_l += zbar_{l+2} (the skip)
+            const int act_l = RES ? layer_act(ACT_RESBLOCK_TANH, l) : act;
             // zbar from abar (in place) using the stash of layer l
             const float4* sl = stash + (size_t)l * C::STASH_F4 * kConsumers + tid;
 #pragma unroll
@@ -361,11 +393,12 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
                             st[s] = jj == 0 ? sv[s].x : jj == 1 ? sv[s].y : jj == 2 ? sv[s].z : sv[s].w;
                             ab[s] = acc[tp * R + s][j];
                         }
-                        act_jet_bwd<D, JET>(st, ab, act);
+                        act_jet_bwd<D, JET>(st, ab, act_l);
 #pragma unroll
                         for (int s = 0; s < R; ++s) acc[tp * R + s][j] = ab[s];
                     }
                 }
+            if (RES && !(l & 1) && l >= 2) skip_save<TR>(skip, acc);  // zbar_l also flows to abar_{l-2}
             // bias gradient (+ first-layer weight gradient)
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -405,7 +438,7 @@ jet_bwd_kernel(MlpParams P, const float* __restrict__ x, long long n, XForm xf, 
                         float st[R], a[R];
 #pragma unroll
                         for (int s = 0; s < R; ++s) st[s] = jj == 0 ? sv[s].x : jj == 1 ? sv[s].y : jj == 2 ? sv[s].z : sv[s].w;
-                        act_jet_from_stash<D, JET>(st, a, act);
+                        act_jet_from_stash<D, JET>(st, a, RES ? layer_act(ACT_RESBLOCK_TANH, l - 1) : act);
 #pragma unroll
                         for (int s = 0; s < R; ++s) av[s][jj] = a[s];
                     }

@@ -10,7 +10,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgpe_b200.so")
 
-ACT_TANH, ACT_SHIFTED_TANH, ACT_LEAKY_RELU = 0, 1, 2
+ACT_TANH, ACT_SHIFTED_TANH, ACT_LEAKY_RELU, ACT_RESBLOCK_TANH = 0, 1, 2, 3
 JET_VALUE, JET_DIAG, JET_FULL, JET_LAPLACIAN = 0, 1, 2, 3
 MAX_LAYERS = 8
 NFEAT, NMOM, MOM_GRAD2, MOM_NN2, MOM_SYM2 = 7, 32, 28, 29, 30

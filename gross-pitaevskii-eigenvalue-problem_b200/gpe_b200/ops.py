@@ -22,7 +22,7 @@ from typing import Optional, Sequence
 import torch
 
 from . import _lib
-from ._lib import (ACT_LEAKY_RELU, ACT_SHIFTED_TANH, ACT_TANH, JET_DIAG, JET_FULL, JET_LAPLACIAN,  # noqa: F401
+from ._lib import (ACT_LEAKY_RELU, ACT_RESBLOCK_TANH, ACT_SHIFTED_TANH, ACT_TANH, JET_DIAG, JET_FULL, JET_LAPLACIAN,  # noqa: F401
                    JET_VALUE, NL_ABSPOW, NL_NONE, NL_POW, NMOM)
 
 PREC_FP32, PREC_TF32X3, PREC_AUTO = 0, 1, 2

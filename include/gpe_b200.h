@@ -37,7 +37,16 @@ extern "C" {
 
 typedef struct CUstream_st* gpe_stream_t; /* == cudaStream_t */
 
-enum { GPE_ACT_TANH = 0, GPE_ACT_SHIFTED_TANH = 1, GPE_ACT_LEAKY_RELU = 2 };
+enum {
+    GPE_ACT_TANH = 0,
+    GPE_ACT_SHIFTED_TANH = 1,
+    GPE_ACT_LEAKY_RELU = 2,
+    /* the residual network of Gross-Pitaevskii/src/final/refine/box_to_gaussian_pinn_simulation.py:52-62 (ResidualBlock)
+     * and :113-130 (build_network, use_residual=True): hidden layer 0 is Linear + ShiftedTanh; hidden layers 2k+1 and
+     * 2k+2 are lin1 and lin2 of block k, out = tanh(lin2(tanh(lin1(a))) + a).  n_hidden = 1 + 2*blocks; W[] / b[] list
+     * the Linear layers in module order.  d = 1, width <= 128, FP32 (FFMA) kernels. */
+    GPE_ACT_RESBLOCK_TANH = 3
+};
 /* which derivatives travel with the value */
 enum {
     GPE_JET_VALUE = 0,     /* u only                                   (boundary / mirror points)   */

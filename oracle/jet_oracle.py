@@ -8,7 +8,7 @@ independent check of the CUDA kernels' recurrences.
 """
 import torch
 
-ACT_TANH, ACT_SHIFTED_TANH, ACT_LEAKY_RELU = 0, 1, 2
+ACT_TANH, ACT_SHIFTED_TANH, ACT_LEAKY_RELU, ACT_RESBLOCK_TANH = 0, 1, 2, 3
 _EPS = 2.220446049250313e-16
 
 
@@ -24,6 +24,14 @@ def _act(z, act):
 
 def mlp(x, Ws, bs, act):
     """x [N,d]; Ws[i] [out,in] (PyTorch layout); returns [N,1]."""
+    if act == ACT_RESBLOCK_TANH:
+        # R/box_to_gaussian_pinn_simulation.py:52-62,113-130: Linear + ShiftedTanh, then blocks
+        # tanh(lin2(tanh(lin1(a))) + a) over consecutive (lin1, lin2) pairs, then the output Linear
+        a = _act(x @ Ws[0].t() + bs[0], ACT_SHIFTED_TANH)
+        for k in range(1, len(Ws) - 1, 2):
+            inner = torch.tanh(a @ Ws[k].t() + bs[k])
+            a = torch.tanh(inner @ Ws[k + 1].t() + bs[k + 1] + a)
+        return a @ Ws[-1].t() + bs[-1]
     a = x
     for i, (W, b) in enumerate(zip(Ws, bs)):
         a = a @ W.t() + b

@@ -353,6 +353,51 @@ def final_train_terms(model, X, boundary_points, boundary_values, dx, gamma, p, 
     return pde + 10.0 * bc + 20.0 * nrm, pde, bc, nrm, mu
 
 
+class ResidualBlock(nn.Module):
+    """R/box_to_gaussian_pinn_simulation.py:52-62."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.lin1 = nn.Linear(dim, dim)
+        self.lin2 = nn.Linear(dim, dim)
+
+    def forward(self, x):
+        return torch.tanh(self.lin2(torch.tanh(self.lin1(x))) + x)
+
+
+def residual_mlp(widths):
+    """R/box_to_gaussian_pinn_simulation.py:113-130: Linear + ShiftedTanh, len(widths) - 3 residual blocks, Linear."""
+    mods = [nn.Linear(widths[0], widths[1]), ShiftedTanh()]
+    mods += [ResidualBlock(widths[1]) for _ in range(len(widths) - 3)]
+    mods.append(nn.Linear(widths[1], widths[-1]))
+    return nn.Sequential(*mods)
+
+
+class BoxToGaussianGPE1D(FinalGPE1D):
+    """R/box_to_gaussian_pinn_simulation.py:65-247 `GrossPitaevskiiPINN(layers, hbar, m, mode, gamma, L, use_residual)`:
+    residual-block network, box-sine base differentiated by autograd (no analytic bundle, no sin(pi x) factor),
+    V = exp(-(x - 1/2)^2), Hu = -u'' + V u + gamma u**p."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, L=1.0, use_residual=True):
+        super().__init__(layers, hbar, m, mode, gamma, True, potential="box", L=L, enforce_boundary=False)
+        self.use_residual = use_residual
+        if use_residual:
+            self.network = residual_mlp(layers)
+
+    def compute_potential(self, x, potential_type="gaussian", **kw):
+        if potential_type != "gaussian":                 # :167-175
+            raise ValueError(f"Unknown potential type: {potential_type}")
+        return torch.exp(-(x - 0.5) ** 2)
+
+    def _jets(self, inputs, predictions):                # :182-200
+        u = self.get_complete_solution(inputs, predictions)
+        u_x = d_dx(u, inputs)
+        return u, u_x, d_dx(u_x, inputs)
+
+    def pde_loss(self, inputs, predictions, gamma, p, potential_type="gaussian", precomputed_potential=None):
+        return FinalGPE1D.pde_loss(self, inputs, predictions, gamma, p, potential_type, precomputed_potential)
+
+
 class VaryPotentialGPE1D(FinalGPE1D):
     """The beta-sweep classes `GrossPitaevskiiPINN(layers, hbar, m, mode, beta, [L], use_residual, use_perturbation)`
     (use_residual is stored and never read):

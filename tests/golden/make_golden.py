@@ -173,11 +173,13 @@ def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=No
     use_perturbation / enforce_boundary, its vanilla PINN has both off)."""
     script = {"harmonic": "final/refine/harmonic_pinn_simulation.py", "box": "final/refine/box_pinn_simulation.py",
               "gravity_well": "final/refine/gravity_well_pinn_simulation.py",
-              "plot_box": "final/refine/plot_box_potential_at_ground_state.py"}[kind]
+              "plot_box": "final/refine/plot_box_potential_at_ground_state.py",
+              "box_to_gaussian": "final/refine/box_to_gaussian_pinn_simulation.py"}[kind]
     mod = rl.load_script(script)
     mod.device = torch.device("cpu")
     ctor_kw = ctor_kw or {}
-    lb, ub = {"harmonic": (-10.0, 10.0), "box": (0.0, 1.0), "gravity_well": (0.0, 35.0), "plot_box": (0.0, 1.0)}[kind]
+    lb, ub = {"harmonic": (-10.0, 10.0), "box": (0.0, 1.0), "gravity_well": (0.0, 35.0), "plot_box": (0.0, 1.0),
+              "box_to_gaussian": (0.0, 1.0)}[kind]
     Xn = np.linspace(lb, ub, n_pts).reshape(-1, 1)
     if kind == "gravity_well":
         Xn = Xn.astype(np.float32).astype(np.float64)      # see case_final_fixture
@@ -197,7 +199,7 @@ def case_final_random(gamma, p, mode, layers, n_pts, kind="harmonic", ctor_kw=No
         u_pred = pc * model.forward(X) / const
         bc = model.boundary_loss(bp, bv)
         nrm = model.normalization_loss(model.get_complete_solution(X, u_pred), dx)
-        pde, mu = model.pde_loss(X, u_pred, gamma, p, "box" if kind == "plot_box" else kind)
+        pde, mu = model.pde_loss(X, u_pred, gamma, p, {"plot_box": "box", "box_to_gaussian": "gaussian"}.get(kind, kind))
         total = pde + 10.0 * bc + 20.0 * nrm
         return dict(pde=_np(pde), bc=_np(bc), norm=_np(nrm), total=_np(total), mu=_np(mu), grads=_grads(model, total))
 
@@ -504,6 +506,10 @@ def main():
         "final_neg_gamma_shipped_m1_gm8": lambda: case_final_random(
             -8, 3, 1, None, 4000, shipped=("comparison_results_neg_int_strength_p3_harmonic/curriculum_pinn_models_p3_harmonic.pkl",
                                            "curriculum_state_dicts", 1.0)),
+        "box_to_gaussian_res_g10_p3_m0": lambda: case_final_random(10.0, 3, 0, [1, 64, 64, 64, 1], 800, kind="box_to_gaussian"),
+        "box_to_gaussian_res_g4_p4_m2": lambda: case_final_random(4.0, 4, 2, [1, 48, 48, 48, 48, 1], 500, kind="box_to_gaussian"),
+        "box_to_gaussian_plain_g5_p3_m1": lambda: case_final_random(
+            5.0, 3, 1, [1, 64, 64, 64, 1], 600, kind="box_to_gaussian", ctor_kw=dict(use_residual=False)),
         "final_gravity_fixture": lambda: case_final_fixture("gravity_well"),
         "final_gravity_g10_p3_m1": lambda: case_final_random(10.0, 3, 1, [1, 64, 64, 64, 1], 1200, kind="gravity_well"),
         "vary_harmonic_b0.6_g5_p3_m1": lambda: case_variant("harmonic", 1, 0.6, 5.0, 3, 900),

@@ -76,6 +76,12 @@ CASES = [
     (1, 256, 2, 0, 1, 129),
     (2, 50, 5, 0, 0, 31),
     (1, 8, 2, 0, 1, 1),
+    # residual-block nets of R/box_to_gaussian_pinn_simulation.py (act 3; L = 1 + 2 * blocks)
+    (1, 64, 5, 3, 1, 4000),     # its own main: layers [1,64,64,64,1] -> two blocks
+    (1, 64, 3, 3, 1, 333),
+    (1, 100, 7, 3, 1, 1025),
+    (1, 128, 5, 3, 0, 2),       # value-only (the two boundary points)
+    (1, 32, 1, 3, 1, 65),       # no block at all: layers [1,32,1]
 ]
 
 
@@ -137,6 +143,14 @@ def test_empty_and_errors():
         ops.mlp_jet_fwd(torch.zeros((4, 1)), cW, cb, 0, ops.JET_DIAG)      # CPU tensor: no fallback
     with pytest.raises((ValueError, RuntimeError)):
         ops.mlp_jet_fwd(torch.zeros((4, 2), device="cuda"), cW, cb, 0, ops.JET_DIAG)
+    with pytest.raises(RuntimeError):       # residual blocks come in (lin1, lin2) pairs: n_hidden = 1 + 2 * blocks
+        Ws4, bs4 = make_net(1, 64, 4, seed=3, act=0)
+        ops.mlp_jet_fwd(torch.zeros((4, 1), device="cuda"), [w.cuda() for w in Ws4], [b.cuda() for b in bs4],
+                        ops.ACT_RESBLOCK_TANH, ops.JET_DIAG)
+    with pytest.raises(RuntimeError):       # ... and the reference's residual network is 1-D
+        Ws2, bs2 = make_net(2, 64, 3, seed=3, act=0)
+        ops.mlp_jet_fwd(torch.zeros((4, 2), device="cuda"), [w.cuda() for w in Ws2], [b.cuda() for b in bs2],
+                        ops.ACT_RESBLOCK_TANH, ops.JET_LAPLACIAN)
 
 
 # ---------------------------------------------------------------------------------------------

@@ -112,6 +112,28 @@ def test_final_random(golden, name, kind, tag):
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
 
 
+B2G_GOLDENS = ["box_to_gaussian_res_g10_p3_m0", "box_to_gaussian_res_g4_p4_m2", "box_to_gaussian_plain_g5_p3_m1"]
+
+
+@pytest.mark.parametrize("name", B2G_GOLDENS)
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_box_to_gaussian_residual_blocks(golden, name, tag):
+    """The ResidualBlock network of R/box_to_gaussian_pinn_simulation.py and its use_residual=False
+    twin, against the real class (state_dict keys network.{k}.lin1/lin2 load as they are)."""
+    g = golden(name)
+    dt = DT[tag]
+    model = load_weights(po.BoxToGaussianGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"]),
+                                               use_residual="_res_" in name), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], dtype=dt)
+    total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), dtype=dt), float(g["dx"]),
+                                                   float(g["gamma"]), int(g["p"]), float(g["perturb_const"]), float(g["const"]))
+    for key, val in dict(pde=pde, bc=bc, norm=nrm, total=total, mu=mu).items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
+
+
 @pytest.mark.parametrize("name", ["opt_m0_eta10", "opt_m1_eta50"])
 @pytest.mark.parametrize("tag", ["f64", "f32"])
 def test_opt(golden, name, tag):
