@@ -54,6 +54,28 @@ def _sequential(widths, act_factory):
     return nn.Sequential(*mods)
 
 
+class ResidualBlock(nn.Module):
+    """tanh(lin2(tanh(lin1(x))) + x) (R/box_to_gaussian_pinn_simulation.py:52-62).  Kept so the module tree and the
+    state_dict keys (`network.{k}.lin1.weight` ...) match; the kernels run the whole network as
+    ACT_RESBLOCK_TANH and never call this forward."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.lin1 = nn.Linear(dim, dim)
+        self.lin2 = nn.Linear(dim, dim)
+
+    def forward(self, x):  # only reached if someone calls the block directly
+        return torch.tanh(self.lin2(torch.tanh(self.lin1(x))) + x)
+
+
+def _residual_sequential(widths):
+    """R/box_to_gaussian_pinn_simulation.py:113-130: Linear + ShiftedTanh, len(widths) - 3 blocks, Linear."""
+    mods = [nn.Linear(widths[0], widths[1]), ShiftedTanh()]
+    mods += [ResidualBlock(widths[1]) for _ in range(len(widths) - 3)]
+    mods.append(nn.Linear(widths[1], widths[-1]))
+    return nn.Sequential(*mods)
+
+
 _ACT_OF = {nn.Tanh: ops.ACT_TANH, ShiftedTanh: ops.ACT_SHIFTED_TANH, nn.LeakyReLU: ops.ACT_LEAKY_RELU}
 
 
@@ -84,6 +106,10 @@ class JetMLP(nn.Module):
         return [m for m in self.modules() if isinstance(m, nn.Linear)]
 
     def _act_kind(self):
+        if any(type(m).__name__ == "ResidualBlock" for m in self.modules()):
+            # Linear + ShiftedTanh, residual blocks, Linear; modules() lists the Linears in the order
+            # (input, lin1, lin2, lin1, lin2, ..., output) the kernels expect
+            return ops.ACT_RESBLOCK_TANH
         for m in self.modules():
             if type(m) in _ACT_OF:
                 return _ACT_OF[type(m)]
@@ -478,6 +504,28 @@ class FinalGPE1D(_GPE1DBase):
 
     def normalization_loss(self, u, dx):
         return (gdist.all_reduce_sum(torch.sum(u ** 2), self.group) * dx - 1.0) ** 2
+
+
+class BoxToGaussianGPE1D(FinalGPE1D):
+    """`GrossPitaevskiiPINN(layers, hbar, m, mode, gamma, L, use_residual)` of
+    R/box_to_gaussian_pinn_simulation.py:65-247: the ResidualBlock network (use_residual=True, the default) or the
+    plain ShiftedTanh one, box-sine base, no sin(pi x) factor, V = exp(-(x - 1/2)^2) (:167-175),
+    pde_loss(inputs, predictions, gamma, p, potential_type="gaussian", precomputed_potential) -> (pde_loss, lambda_pde).
+    The reference differentiates the base through autograd; here its analytic jets feed the fused epilogue."""
+
+    def __init__(self, layers, hbar=1.0, m=1.0, mode=0, gamma=1.0, L=1.0, use_residual=True):
+        super().__init__(layers, hbar, m, mode, gamma, True, potential="box", L=L, enforce_boundary=False)
+        self.use_residual = use_residual
+        if use_residual:
+            self.network = _residual_sequential(layers)
+
+    def compute_potential(self, x, potential_type="gaussian", **kw):
+        if potential_type != "gaussian":
+            raise ValueError(f"Unknown potential type: {potential_type}")
+        return torch.exp(-(x - 0.5) ** 2)
+
+    def pde_loss(self, inputs, predictions, gamma, p, potential_type="gaussian", precomputed_potential=None):
+        return FinalGPE1D.pde_loss(self, inputs, predictions, gamma, p, potential_type, precomputed_potential)
 
 
 class VaryPotentialGPE1D(FinalGPE1D):

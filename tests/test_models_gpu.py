@@ -92,6 +92,44 @@ def test_final_random(golden, name, kind):
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
+B2G_GOLDENS = ["box_to_gaussian_res_g10_p3_m0", "box_to_gaussian_res_g4_p4_m2", "box_to_gaussian_plain_g5_p3_m1"]
+
+
+def _b2g_check(model, g, tol, gtol):
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp = torch.tensor([[lb], [ub]], device="cuda")
+    total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
+                                                   float(g["gamma"]), int(g["p"]), float(g["perturb_const"]), float(g["const"]))
+    for key, val in dict(pde=pde, total=total, mu=mu).items():
+        assert close(val, g[f"f64.{key}"], tol), (key, float(val), float(g[f"f64.{key}"]))
+    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
+    assert abs(float(bc) - float(g["f64.bc"])) <= tol * abs(float(g["f64.bc"])) + 1e-12
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < gtol
+
+
+@pytest.mark.parametrize("name", B2G_GOLDENS)
+def test_box_to_gaussian_residual_blocks(golden, name):
+    """the ResidualBlock network of R/box_to_gaussian_pinn_simulation.py through the fused path
+    (GPE_ACT_RESBLOCK_TANH kernels + moment epilogue), against the float64 run of the real class."""
+    import gpe_b200
+    g = golden(name)
+    model = cuda_model(gpe_b200.BoxToGaussianGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]),
+                       gamma=float(g["gamma"]), use_residual="_res_" in name)
+    assert ("network.2.lin1.weight" in model.state_dict()) == ("_res_" in name)
+    _b2g_check(model, g, 2 * TOL, GTOL)
+
+
+def test_compat_box_to_gaussian_residual_blocks(golden):
+    """... and through the compat path: the oracle's (= reference's) class with only forward() rerouted; its own
+    nested autograd.grad calls, which also differentiate the torch box-sine base, run on the kernel's jets."""
+    from gpe_b200.models import patch
+    g = golden("box_to_gaussian_res_g10_p3_m0")
+    model = patch(load_weights(po.BoxToGaussianGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]),
+                                                     gamma=float(g["gamma"])), g).cuda())
+    _b2g_check(model, g, 2e-5, 5e-5)
+
+
 @pytest.mark.parametrize("kind", ["harmonic", "box", "gravity_well"])
 def test_final_fixture_mu_table(golden, kind):
     """Shipped trained weights: the fused path must reproduce the pickled mu_table (SURVEY 8c-1);
