@@ -1016,6 +1016,71 @@ class Helmholtz2D(JetMLP):
         return self.loss_pde(x_f, k) + self.loss_data(x_u, u_true)
 
 
+class LearnableKHelmholtz2D(JetMLP):
+    """`PINN(layers, ub, lb)` of Notebooks/Helmholtz/Helmholtz_learnable_k_and_bc.ipynb cell 3 (SURVEY #18, 8f-4): LeakyReLU
+    MLP in `layers` (state_dict keys `layers.{2i}.weight`), min-max input scaling folded into the first layer, learnable
+    wave number `k` and boundary weight `adaptive_bc_scale` as ordinary parameters.  pde_loss (:129-162) keeps the
+    notebook's shapes: `u_xx + u_yy` is [N] and `predictions` [N,1], so the residual is the [N,N] matrix
+    lap_j - k^2 u_i and its mean square is <lap^2> - 2 k^2 <lap><u> + k^4 <u^2> -- three entries of the moment vector;
+    k.grad comes from autograd on that fp64 scalar expression, the network gradient from the reverse kernel."""
+
+    def __init__(self, layers, ub, lb):
+        super().__init__()
+        self.layers = nn.ModuleList()
+        self.input_ub, self.input_lb = [float(v) for v in ub], [float(v) for v in lb]
+        self.adaptive_bc_scale = nn.Parameter(torch.tensor(10.0))
+        self.k = nn.Parameter(torch.tensor(float(np.pi)))
+        for i in range(len(layers) - 1):
+            self.layers.append(nn.Linear(layers[i], layers[i + 1]))
+            if i < len(layers) - 2:
+                self.layers.append(nn.LeakyReLU())
+        self.activation = nn.LeakyReLU()
+        self.init_weights()
+
+    @property
+    def ub(self):
+        return torch.tensor(self.input_ub, dtype=torch.float32, device=self.k.device)
+
+    @property
+    def lb(self):
+        return torch.tensor(self.input_lb, dtype=torch.float32, device=self.k.device)
+
+    def init_weights(self):
+        for m in self.layers:
+            if isinstance(m, nn.Linear):
+                nn.init.xavier_normal_(m.weight)
+
+    def forward(self, x):
+        return self._net(x)
+
+    def loss_BC(self, x_bc, y_bc):
+        """:84-103."""
+        return self.adaptive_bc_scale * torch.mean((self.forward(x_bc) - y_bc) ** 2)
+
+    def _check_predictions(self, predictions):
+        if predictions is not None and trace_scale(predictions) != 1.0:
+            raise RuntimeError("gpe_b200: `predictions` must be model.forward(inputs) (use models.patch for anything else)")
+
+    def riesz_loss(self, predictions, inputs):
+        """:105-127: sum |grad u|^2."""
+        self._check_predictions(predictions)
+        return self._moments(inputs, derivs=True).grad2.float()
+
+    def pde_loss(self, inputs, predictions):
+        """:129-162."""
+        self._check_predictions(predictions)
+        M = self._moments(inputs, derivs=True)
+        k2 = self.k.double() ** 2
+        mse = M.mean(F_LAP, F_LAP) - 2.0 * k2 * M.mean(F_LAP) * M.mean(F_U) + k2 * k2 * M.mean(F_U, F_U)
+        return mse.float()
+
+    def loss(self, x_bc, y_bc, x_to_train_f):
+        """:164-192 (the boundary term carries the scale twice)."""
+        loss_u = self.adaptive_bc_scale * self.loss_BC(x_bc, y_bc)
+        predictions = self.forward(x_to_train_f)
+        return loss_u + self.pde_loss(x_to_train_f, predictions) + self.riesz_loss(predictions, x_to_train_f)
+
+
 def patch(model, jet_mode="full", precision=ops.PREC_AUTO, input_lb=None, input_ub=None):
     """Compat path: reroute `model.forward` of a reference-style module -- a plain
     tanh / ShiftedTanh / LeakyReLU MLP held in `network` (nn.Sequential) or `linears` (ModuleList) --

@@ -939,3 +939,52 @@ def param_grads(model, scalar):
     ps = list(model.parameters())
     gs = torch.autograd.grad(scalar, ps, allow_unused=True)
     return [torch.zeros_like(p) if g is None else g for p, g in zip(ps, gs)]
+
+
+class LearnableKHelmholtz2D(nn.Module):
+    """`PINN(layers, ub, lb)` of Notebooks/Helmholtz/Helmholtz_learnable_k_and_bc.ipynb cell 3 (SURVEY #18, 8f-4):
+    LeakyReLU MLP held in `layers` (Linear / LeakyReLU alternating), min-max input scaling (:68-73), learnable wave
+    number `k` and boundary weight `adaptive_bc_scale` (:35-36).  The notebook checkpoints its Linear layers (:76-80),
+    which changes memory, not numbers.  pde_loss (:129-162): `u_xx + u_yy` is [N], `predictions` [N,1], so the residual
+    is the [N,N] matrix lap_j - k^2 u_i; loss (:164-192) multiplies the boundary term by the scale a second time."""
+
+    def __init__(self, layers, ub, lb):
+        super().__init__()
+        self.layers = nn.ModuleList()
+        self.ub = torch.tensor(ub, dtype=torch.float32)
+        self.lb = torch.tensor(lb, dtype=torch.float32)
+        self.adaptive_bc_scale = nn.Parameter(torch.tensor(10.0))
+        self.k = nn.Parameter(torch.tensor(np.pi, dtype=torch.float32))
+        for i in range(len(layers) - 1):
+            self.layers.append(nn.Linear(layers[i], layers[i + 1]))
+            if i < len(layers) - 2:
+                self.layers.append(nn.LeakyReLU())
+        self.activation = nn.LeakyReLU()
+        for m in self.layers:
+            if isinstance(m, nn.Linear):
+                nn.init.xavier_normal_(m.weight)
+
+    def forward(self, x):
+        lb, ub = self.lb.view(1, -1).to(x.device), self.ub.view(1, -1).to(x.device)
+        x = (x - lb) / (ub - lb)
+        for layer in self.layers:
+            x = layer(x)
+        return x
+
+    def loss_BC(self, x_bc, y_bc):
+        return self.adaptive_bc_scale * torch.mean((self.forward(x_bc) - y_bc) ** 2)
+
+    def riesz_loss(self, predictions, inputs):
+        g = torch.autograd.grad(predictions, inputs, torch.ones_like(predictions), create_graph=True, retain_graph=True)[0]
+        return torch.sum(g ** 2)
+
+    def pde_loss(self, inputs, predictions):
+        u_x = torch.autograd.grad(predictions, inputs, torch.ones_like(predictions), create_graph=True)[0]
+        u_xx = torch.autograd.grad(u_x[:, 0], inputs, torch.ones_like(u_x[:, 0]), create_graph=True)[0][:, 0]
+        u_yy = torch.autograd.grad(u_x[:, 1], inputs, torch.ones_like(u_x[:, 1]), create_graph=True)[0][:, 1]
+        return torch.mean((u_xx + u_yy - self.k ** 2 * predictions) ** 2)
+
+    def loss(self, x_bc, y_bc, x_to_train_f):
+        loss_u = self.adaptive_bc_scale * self.loss_BC(x_bc, y_bc)
+        predictions = self.forward(x_to_train_f)
+        return loss_u + self.pde_loss(x_to_train_f, predictions) + self.riesz_loss(predictions, x_to_train_f)

@@ -122,6 +122,16 @@ def load_paper_notebook_class(name="Gross_Pitaevskii_1D_Harmonic.ipynb", cell=6)
     return ns["GrossPitaevskiiPINN"]
 
 
+def load_learnable_k_notebook_class():
+    """`PINN` of Notebooks/Helmholtz/Helmholtz_learnable_k_and_bc.ipynb cell 3."""
+    from torch.utils.checkpoint import checkpoint
+    with open(os.path.join(REF_ROOT, "Notebooks", "Helmholtz", "Helmholtz_learnable_k_and_bc.ipynb")) as fh:
+        nb = json.load(fh)
+    ns = dict(torch=torch, nn=nn, np=np, math=math, checkpoint=checkpoint, device=torch.device("cpu"))
+    exec("".join(nb["cells"][3]["source"]), ns)
+    return ns["PINN"]
+
+
 def load_pickle(relpath_under_refine):
     import pickle
     with open(os.path.join(REFINE, relpath_under_refine), "rb") as fh:

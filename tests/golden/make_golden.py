@@ -420,6 +420,42 @@ def case_helmholtz(layers, n_pts, n_bc, act):
     return out
 
 
+def case_helmholtz_learnable_k(layers, n_pts, n_bc):
+    """Notebooks/Helmholtz/Helmholtz_learnable_k_and_bc.ipynb cell 3 `PINN(layers, ub, lb)`: every term of loss() and the
+    gradient w.r.t. the network, k and adaptive_bc_scale."""
+    Cls = rl.load_learnable_k_notebook_class()
+    lb, ub = [-1.0, -1.0], [1.0, 1.0]
+    rng = np.random.default_rng(31)
+    Xn = rng.random((n_pts, 2)) * 2 - 1
+    Xb = rng.random((n_bc, 2)) * 2 - 1
+    Xb[: n_bc // 2, 0] = -1.0
+    Xb[n_bc // 2:, 1] = 1.0
+    yb = np.sin(np.pi * Xb[:, [0]]) * np.cos(np.pi * Xb[:, [1]])
+
+    def build():
+        torch.manual_seed(1234)
+        m = Cls(layers, ub, lb)
+        with torch.no_grad():                       # biases off zero, k and the scale off their initial values
+            for mod in m.layers:
+                if isinstance(mod, torch.nn.Linear):
+                    mod.bias.uniform_(-0.2, 0.2)
+            m.k.fill_(2.5)
+            m.adaptive_bc_scale.fill_(7.0)
+        return m
+
+    def run(model, dt):
+        X = torch.tensor(Xn, dtype=dt, requires_grad=True)
+        xb, y = torch.tensor(Xb, dtype=dt), torch.tensor(yb, dtype=dt)
+        pred = model.forward(X)
+        pde, riesz, bc = model.pde_loss(X, pred), model.riesz_loss(pred, X), model.loss_BC(xb, y)
+        total = model.loss(xb, y, X)
+        return dict(pde=_np(pde), riesz=_np(riesz), bc=_np(bc), total=_np(total), grads=_grads(model, total))
+
+    out = _both_dtypes(build, run)
+    out.update(X=Xn, Xb=Xb, yb=yb, lb=np.array(lb), ub=np.array(ub), layers=np.array(layers))
+    return out
+
+
 def case_helmholtz_circle(layers, n_pts):
     """S/helmholtz_2D_circle.py: scaled forward (:69-106), its autograd columns as loss_PDE takes them (:131-140)
     and loss_PDE itself (:112-172).  The reference's forward casts to float32 (:97), so there is no float64 run of
@@ -535,6 +571,7 @@ def main():
         "helmholtz_leaky": lambda: case_helmholtz([2, 40, 40, 40, 1], 300, 40, "leaky_relu"),
         "helmholtz_tanh": lambda: case_helmholtz([2, 100, 100, 100, 1], 200, 40, "tanh"),
         "helmholtz_circle": lambda: case_helmholtz_circle([2, 64, 64, 64, 1], 150),
+        "helmholtz_learnable_k": lambda: case_helmholtz_learnable_k([2, 64, 64, 64, 1], 300, 40),
     }
     only = sys.argv[1:]
     for name, fn in cases.items():

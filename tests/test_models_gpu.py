@@ -386,6 +386,40 @@ def test_compat_helmholtz_circle(golden):
     assert rel_err(flat(model_grads(model, got)), want_g) < 5e-5
 
 
+def test_helmholtz_learnable_k(golden):
+    """gpe_b200.LearnableKHelmholtz2D (notebook #18): loss terms, and the gradient w.r.t. adaptive_bc_scale, k and the
+    network, against the float64 run of the real class."""
+    import gpe_b200
+    g = golden("helmholtz_learnable_k")
+    model = cuda_model(gpe_b200.LearnableKHelmholtz2D, g, [int(v) for v in g["layers"]], list(g["ub"]), list(g["lb"]))
+    assert [n for n, _ in model.named_parameters()][:3] == ["adaptive_bc_scale", "k", "layers.0.weight"]
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    yb = torch.tensor(g["yb"], dtype=torch.float32, device="cuda")
+    pred = model.forward(X)
+    terms = dict(pde=model.pde_loss(X, pred), riesz=model.riesz_loss(pred, X), bc=model.loss_BC(xb, yb), total=model.loss(xb, yb, X))
+    for key, val in terms.items():
+        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+    grads, ref = model_grads(model, terms["total"]), golden_grads(g, "f64.grads")
+    assert rel_err(flat(grads), flat(ref)) < GTOL
+    for i in (0, 1):                                   # the two scalar parameters on their own
+        assert abs(float(grads[i]) - float(ref[i])) <= GTOL * abs(float(ref[i])), (i, float(grads[i]), float(ref[i]))
+
+
+def test_compat_helmholtz_learnable_k(golden):
+    """... and the oracle's (= notebook's) class with only forward() rerouted (input scaling folded by patch)."""
+    from gpe_b200.models import patch
+    g = golden("helmholtz_learnable_k")
+    model = load_weights(po.LearnableKHelmholtz2D([int(v) for v in g["layers"]], list(g["ub"]), list(g["lb"])), g).cuda()
+    model = patch(model, input_lb=list(g["lb"]), input_ub=list(g["ub"]))
+    X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
+    yb = torch.tensor(g["yb"], dtype=torch.float32, device="cuda")
+    total = model.loss(xb, yb, X)
+    assert close(total, g["f64.total"], 2e-5)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+
+
 def test_helmholtz2d_input_scaling():
     """gpe_b200.Helmholtz2D(lb=, ub=): fused loss_pde with the scaling folded into (W_0, b_0); gradients reach the
     unscaled leaves.  Against the fp64 oracle with the scaling applied as the reference writes it."""

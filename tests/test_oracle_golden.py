@@ -308,3 +308,19 @@ def test_nn_moment_identity(golden):
     b = (k ** 2 * u - k ** 2 * torch.sin(np.pi * xg[:, [0]]) * torch.sin(np.pi * xg[:, [1]]))[:, 0]
     fact = (lap ** 2).mean() + 2 * lap.mean() * b.mean() + (b ** 2).mean()
     assert abs(float(fact) - ref) < 1e-11 * abs(ref)
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_helmholtz_learnable_k(golden, tag):
+    """Notebooks/Helmholtz/Helmholtz_learnable_k_and_bc.ipynb cell 3 (SURVEY #18): terms of loss() and the gradient
+    w.r.t. (adaptive_bc_scale, k, network), against the real class."""
+    g = golden("helmholtz_learnable_k")
+    dt = DT[tag]
+    model = load_weights(po.LearnableKHelmholtz2D([int(v) for v in g["layers"]], list(g["ub"]), list(g["lb"])), g).to(dt)
+    X = torch.tensor(g["X"], dtype=dt, requires_grad=True)
+    xb, yb = torch.tensor(g["Xb"], dtype=dt), torch.tensor(g["yb"], dtype=dt)
+    pred = model.forward(X)
+    terms = dict(pde=model.pde_loss(X, pred), riesz=model.riesz_loss(pred, X), bc=model.loss_BC(xb, yb), total=model.loss(xb, yb, X))
+    for key, val in terms.items():
+        assert close(val, g[f"{tag}.{key}"], TOL[tag]), key
+    assert rel_err(flat(model_grads(model, terms["total"])), flat(golden_grads(g, f"{tag}.grads"))) < TOL[tag]
