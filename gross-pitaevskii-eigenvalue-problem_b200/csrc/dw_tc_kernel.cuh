@@ -77,9 +77,9 @@ __host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n1) {
 
 // stash / zb: [layer][block][kBlkFloats]; stash_ls / lstride = floats per layer of the stash / the zbar chunk buffer.  stash[l-1] = st_l, zb[l-1] = zbar_l (l = 1..L-1).
 // small: the packed small parameters (W0t[D][128] | b[L][128] | ...), small_acc: their gradient, same layout.
-template <int D>
+template <int D, int ACT = -1>
 __global__ void __launch_bounds__(kDwThreads, 1)
-dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __restrict__ x, long long n, long long stash_ls, long long lstride,
+dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __restrict__ x, long long n, long long stash_ls, long long lstride,
              const float* __restrict__ stash, const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc,
              int num_blocks, int n1_cta, int pf_dist) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
@@ -94,6 +94,7 @@ dw_tc_kernel(int L, int act, const float* __restrict__ small, const float* __res
     uint32_t* tbase_s = reinterpret_cast<uint32_t*>(acc_free + 2);
     float* xbuf = reinterpret_cast<float*>(smem + (size_t)kDwStages * kDwStageBytes + 256);   // [stage][8 points x D]
     float* w0s = xbuf + kDwStages * 16;                                                         // W0t[D][128] | b0[128]
+    const int act = ACT >= 0 ? ACT : act_rt;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const DwClass cls = dw_class((int)blockIdx.x, (int)gridDim.x, L, n1_cta);
     const int l = cls.layer;

@@ -23,8 +23,8 @@ int tc_pack_wimg(const PtrArray& W, int L, int Wd, int transpose, float* wimg, c
 
 static int tc_interleave();
 
-template <int D, bool STASH>
-static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
+template <int D, bool STASH, int ACT>
+static int fwd_tc_act(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
     static int sms = 0;
     if (!sms) {
         int dev = 0;
@@ -32,15 +32,26 @@ static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u,
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
     const size_t smem = tcp::tc_smem_bytes(D, P.n_hidden);
-    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, STASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, STASH, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { set_error("tc fwd smem attr (%zu B): %s", smem, cudaGetErrorString(e)); return -3; }
     const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
     long long clusters = sms / 2;
     if (pairs < clusters) clusters = pairs;
-    tcp::jet_fwd_tc_kernel<D, STASH><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (long long)((n + 7) / 8) * tcp::kBlkFloats, STASH ? (int)((n + 7) / 8) : 0, (int)pairs);
+    tcp::jet_fwd_tc_kernel<D, STASH, ACT><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (long long)((n + 7) / 8) * tcp::kBlkFloats, STASH ? (int)((n + 7) / 8) : 0, (int)pairs);
     e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("jet_fwd_tc_kernel launch: %s (grid %lld, smem %zu)", cudaGetErrorString(e), 2 * clusters, smem); return -4; }
     return 0;
+}
+
+// tanh (every BASELINE config) gets kernels with the activation fixed at compile time (GPE_TC_ACT_GENERIC=1: A/B knob)
+static bool tc_act_generic() {
+    static int v = -1;
+    if (v < 0) { const char* ev = getenv("GPE_TC_ACT_GENERIC"); v = (ev && ev[0] == '1') ? 1 : 0; }
+    return v == 1;
+}
+template <int D, bool STASH>
+static int fwd_tc(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
+    return (P.act == ACT_TANH && !tc_act_generic()) ? fwd_tc_act<D, STASH, ACT_TANH>(P, x, n, u, g, h, stash, s) : fwd_tc_act<D, STASH, -1>(P, x, n, u, g, h, stash, s);
 }
 
 // optional per-kernel timing of the tensor-path backward (bench.py roofline): events on the launch stream
@@ -95,14 +106,14 @@ static int tc_sms() {
     return sms;
 }
 
-template <int D>
-static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
+template <int D, int ACT>
+static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
                   const float* hb, float* stash, const float* resident, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
     const int sms = tc_sms(), L = Pf.n_hidden;
     const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes();
-    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::jet_rev_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::dw_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dw);
+    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::jet_rev_tc_kernel<D, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::dw_tc_kernel<D, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dw);
     if (e != cudaSuccess) { set_error("tc bwd smem attr: %s", cudaGetErrorString(e)); return -3; }
     static int rev_pf = -1;   // GPE_REV_PF: L2 prefetch distance of the reverse sweep, in (tile, layer) steps
     if (rev_pf < 0) { const char* ev = getenv("GPE_REV_PF"); rev_pf = ev ? atoi(ev) : 1; if (rev_pf < 1) rev_pf = 1; }
@@ -119,11 +130,11 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         const float* st = resident ? resident + (size_t)(c0 / tcp::kDwPts) * tcp::kBlkFloats : stash;
         if (!resident) {
             TcScope t(0, s);
-            tcp::jet_fwd_tc_kernel<D, true><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, stash_ls, nblk8, (int)pairs);
+            tcp::jet_fwd_tc_kernel<D, true, ACT><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, stash_ls, nblk8, (int)pairs);
         }
         {
             TcScope t(1, s);
-            tcp::jet_rev_tc_kernel<D><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
+            tcp::jet_rev_tc_kernel<D, ACT><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
                 Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, st, zb, small_acc, stash_ls, nblk8, (int)pairs, rev_pf);
         }
         const long long blocks = nblk8;
@@ -137,12 +148,19 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
         if (pf_env < 0) { const char* ev = getenv("GPE_DW_PF"); pf_env = ev ? atoi(ev) : tcp::kDwPf; }
         {
             TcScope t(2, s);
-            tcp::dw_tc_kernel<D><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, Pf.small, xc, nc, stash_ls, (long long)nblk8 * tcp::kBlkFloats, st, zb, dWacc, small_acc, nblk8, n0, pf_env);
+            tcp::dw_tc_kernel<D, ACT><<<grid, tcp::kDwThreads, smem_dw, s>>>(L, Pf.act, Pf.small, xc, nc, stash_ls, (long long)nblk8 * tcp::kBlkFloats, st, zb, dWacc, small_acc, nblk8, n0, pf_env);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("tensor-path backward launch: %s", cudaGetErrorString(e)); return -4; }
     }
     return 0;
+}
+
+template <int D>
+static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
+                  const float* hb, float* stash, const float* resident, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
+    return (Pf.act == ACT_TANH && !tc_act_generic()) ? bwd_tc_act<D, ACT_TANH>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s)
+                              : bwd_tc_act<D, -1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s);
 }
 
 // chunk of points processed per (stash forward, reverse sweep, dW contraction) round

@@ -133,7 +133,9 @@ __device__ __forceinline__ size_t slot_off(long long p, int g, int tq) {
 // image blocks stash[l-1][point / 8] (what the reverse sweep and the dW contraction read back; nblk8 = blocks of this
 // launch, stash_ls = floats per layer of the stash array -- larger than nblk8 * 4096 when the stash of ALL points is resident).
 // Layer 0 is recomputed from x by both consumers.
-template <int D, bool STASH>
+// ACT >= 0 fixes the activation at compile time (the tanh nets of every BASELINE config: no runtime activation branches in
+// the epilogue); ACT = -1 reads it from P.act.
+template <int D, bool STASH, int ACT = -1>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* __restrict__ out_u, float* __restrict__ out_g,
                   float* __restrict__ out_h, float* __restrict__ stash, long long stash_ls, int nblk8, int num_pairs) {
@@ -181,7 +183,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
     const float* bias = small + D * 128;
     const float* wout = small + (D + L) * 128;
     const float bout = small[(D + L + 1) * 128];
-    const int act = P.act;
+    const int act = ACT >= 0 ? ACT : P.act;
 
     if (w < kEpiWarps) {
         const int q = w & 3, sub = w >> 2, pl = lane >> 2, tq = lane & 3;
@@ -351,7 +353,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
 // Also accumulates the output-layer gradient (dwout, dbout) and the input-layer gradient (dW_0, db_0: 3 x 128 numbers,
 // summed in registers over the tiles of the CTA) into small_acc (layout of `small`).
 // ------------------------------------------------------------------------------------------
-template <int D>
+template <int D, int ACT = -1>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const float* __restrict__ u_bar,
                   const float* __restrict__ g_bar, const float* __restrict__ h_bar, const float* __restrict__ stash,
@@ -401,7 +403,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     const float* W0t = small;
     const float* bias = small + D * 128;
     const float* wout = small + (D + L) * 128;
-    const int act = P.act;
+    const int act = ACT >= 0 ? ACT : P.act;
 
     if (w < kEpiWarps) {
         const int q = w & 3, sub = w >> 2, pl = lane >> 2, tq = lane & 3;
