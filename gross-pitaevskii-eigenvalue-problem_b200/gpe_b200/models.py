@@ -21,6 +21,7 @@ Reference classes mirrored (paths under /root/reference):
 There is no CPU path: tensors must live on a CUDA device.
 """
 import math
+import weakref
 
 import numpy as np
 import torch
@@ -268,19 +269,31 @@ def box_base_jets(x, n, length):
     return torch.stack([c * s, c * k * co, -c * k * k * s], dim=1).float().contiguous()
 
 
+_AIRY_CACHE = {}   # (id(x), n) -> (weakref to x, x._version, jets): the Airy base of a fixed training grid is computed once
+
+
 def airy_base_jets(x, n):
     """[N,3] = (psi, psi', psi'') of the gravity-well base psi_n = Ai(x + alpha_n) / sqrt(sum(Ai^2) dx), exactly as
     R/gravity_well_pinn_simulation.py:135-160 builds it: scipy on the host in fp64, dx = x[1] - x[0] of the grid it is
     given, psi'' = np.gradient(psi', dx) (a finite difference, not the Airy equation), cast to float32.  The host
     round trip is the reference's own; it is O(N) and outside the timed kernels."""
+    hit = _AIRY_CACHE.get((id(x), n))
+    if hit is not None and hit[0]() is x and hit[1] == x._version:
+        return hit[2]          # same grid tensor as the last call (every epoch of a training loop): no host round trip
     from scipy.special import ai_zeros, airy
     xn = x.detach().reshape(-1).cpu().numpy()
     ai_val, aip_val, _, _ = airy(xn + ai_zeros(n + 1)[0][n])
     dx = xn[1] - xn[0] if len(xn) > 1 else 0.01
     nf = np.sqrt(np.sum(ai_val ** 2) * dx)
     d2 = np.gradient(aip_val / nf, dx) if len(xn) > 1 else np.zeros_like(aip_val)
-    out = np.stack([ai_val / nf, aip_val / nf, d2], axis=1).astype(np.float32)
-    return torch.from_numpy(out).to(x.device).contiguous()
+    out = torch.from_numpy(np.stack([ai_val / nf, aip_val / nf, d2], axis=1).astype(np.float32)).to(x.device).contiguous()
+    if len(_AIRY_CACHE) >= 16:
+        _AIRY_CACHE.clear()
+    try:
+        _AIRY_CACHE[(id(x), n)] = (weakref.ref(x), x._version, out)
+    except TypeError:
+        pass
+    return out
 
 
 class _GPE1DBase(JetMLP):
