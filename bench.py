@@ -330,8 +330,8 @@ def run_b200(args):
             kname = max(tc_ms, key=tc_ms.get)
             kms = tc_ms[kname]
             alg = {"stash_forward": f_contr, "reverse_sweep": f_contr, "dw_contraction": f_contr}[kname]
-            sym = {"stash_forward": "tcp::jet_fwd_tc_kernel<2,true>", "reverse_sweep": "tcp::jet_rev_tc_kernel<2>",
-                   "dw_contraction": "tcp::dw_tc_kernel<2>"}[kname]
+            sym = {"stash_forward": "tcp::jet_fwd_tc_kernel<2,true,ACT_TANH>", "reverse_sweep": "tcp::jet_rev_tc_kernel<2,ACT_TANH>",
+                   "dw_contraction": "tcp::dw_tc_kernel<2,ACT_TANH>"}[kname]
             bf16 = measured.get("bf16_tflops_sustained") or 1400.0
             achieved = alg * n / (kms * 1e-3) / 1e12
             # image blocks of 2 KB per point and hidden matrix l = 1..L-1: st_l written by the stash forward, read by the
