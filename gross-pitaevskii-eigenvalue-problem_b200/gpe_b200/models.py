@@ -21,7 +21,6 @@ Reference classes mirrored (paths under /root/reference):
 There is no CPU path: tensors must live on a CUDA device.
 """
 import math
-import weakref
 
 import numpy as np
 import torch
@@ -269,31 +268,88 @@ def box_base_jets(x, n, length):
     return torch.stack([c * s, c * k * co, -c * k * k * s], dim=1).float().contiguous()
 
 
-_AIRY_CACHE = {}   # (id(x), n) -> (weakref to x, x._version, jets): the Airy base of a fixed training grid is computed once
+# zeros of Ai (scipy.special.ai_zeros(16)[0]; DLMF table 9.9.1): alpha_n of the gravity-well ground / excited states
+_AI_ZEROS = (-2.3381074104597674, -4.08794944413097, -5.520559828095515, -6.786708090071912, -7.944133587112781,
+             -9.022650853340979, -10.040174341558087, -11.008524303733262, -11.936015563236262, -12.828776752865757,
+             -13.691489035210719, -14.527829951775335, -15.340755135977998, -16.13268515694577, -16.905633997429945,
+             -17.66130010569706)
+# scipy.special.airy(alpha_n)[0]: the float64 rounding residue of Ai at its tabulated zero.  It matters in one place: the
+# reference normalises the base on whatever points it is given, also on the two boundary points [lb, ub] of
+# boundary_loss (R/gravity_well_pinn_simulation.py:97-118 with dx = ub - lb), where Ai(ub + alpha) ~ 1e-60 and the value at
+# lb is this residue, so psi(lb) = sign(residue) / sqrt(ub - lb): the sign of a rounding error is part of its loss.
+_AI_AT_ZEROS = (-4.448110018624294e-16, -1.3353056000148618e-16, 3.1911491397354094e-14, 1.389199660200717e-13,
+                7.647131910089514e-12, -7.458343836354678e-16, -5.107371492894162e-15, -1.2862277747527667e-15,
+                5.991676314917106e-16, -1.662546322182675e-15, 7.172138647917394e-16, -2.4496873381868524e-15,
+                -1.997851055358401e-15, -3.0731540192105915e-15, -3.7750957790817223e-16, 2.743854279781097e-15)
+_AI0, _AIP0 = 0.355028053887817239, -0.258819403792806798   # Ai(0) = 3^(-2/3)/Gamma(2/3), Ai'(0) = -3^(-1/3)/Gamma(1/3)
+_AI_XPOS, _AI_XNEG = 5.5, 7.0
+
+
+def airy_ai(x):
+    """(Ai(x), Ai'(x)) in float64 ON THE DEVICE of x -- what `scipy.special.airy` gives the reference on the host
+    (R/gravity_well_pinn_simulation.py:97-118,135-160).  Maclaurin series on [-7, 5.5], the exponentially decaying
+    expansion above, the oscillatory one below (DLMF 9.4.1, 9.7.5-6, 9.7.9-10); within 2e-8 of scipy relative to the local
+    amplitude on [-60, 40] (4e-12 for x < 0), i.e. below float32 resolution, which is what the reference casts to."""
+    x = x.double()
+    xs = x.clamp(min=-_AI_XNEG - 0.5, max=_AI_XPOS + 0.5)
+    x3 = xs * xs * xs
+    a, b, c, d = torch.ones_like(xs), xs.clone(), xs * xs / 2.0, torch.ones_like(xs)
+    f, g, fp, gp = a.clone(), b.clone(), c.clone(), d.clone()
+    for k in range(1, 90):
+        a = a * x3 / ((3 * k - 1) * (3 * k))
+        b = b * x3 / ((3 * k) * (3 * k + 1))
+        c = c * x3 / ((3 * k) * (3 * k + 2))
+        d = d * x3 / ((3 * k - 2) * (3 * k))
+        f, g, fp, gp = f + a, g + b, fp + c, gp + d
+    ai_s, aip_s = _AI0 * f + _AIP0 * g, _AI0 * fp + _AIP0 * gp
+    xl = x.clamp(min=_AI_XPOS)
+    xn = (-x).clamp(min=_AI_XNEG)
+    z, zn = (2.0 / 3.0) * xl * torch.sqrt(xl), (2.0 / 3.0) * xn * torch.sqrt(xn)
+    l14, n14 = torch.sqrt(torch.sqrt(xl)), torch.sqrt(torch.sqrt(xn))
+    e = torch.exp(-z) / (2.0 * math.sqrt(math.pi))
+    cs, sn = torch.cos(zn - math.pi / 4), torch.sin(zn - math.pi / 4)
+    u, zi, zni = 1.0, torch.ones_like(xl), torch.ones_like(xn)
+    s_u, s_v = torch.ones_like(xl), torch.ones_like(xl)
+    Pu, Qu, Pv, Qv = torch.ones_like(xn), torch.zeros_like(xn), torch.ones_like(xn), torch.zeros_like(xn)
+    for k in range(1, 16):
+        u = u * (6 * k - 5) * (6 * k - 3) * (6 * k - 1) / (216.0 * k * (2 * k - 1))
+        v = -(6 * k + 1) / (6 * k - 1) * u
+        zi, zni = zi / z, zni / zn
+        s_u, s_v = s_u + (-1.0) ** k * u * zi, s_v + (-1.0) ** k * v * zi
+        sg = -1.0 if (k // 2) % 2 else 1.0
+        if k % 2 == 0:
+            Pu, Pv = Pu + sg * u * zni, Pv + sg * v * zni
+        else:
+            Qu, Qv = Qu + sg * u * zni, Qv + sg * v * zni
+    ai_p, aip_p = e / l14 * s_u, -e * l14 * s_v
+    ai_n = (cs * Pu + sn * Qu) / (math.sqrt(math.pi) * n14)
+    aip_n = (sn * Pv - cs * Qv) * n14 / math.sqrt(math.pi)
+    big, neg = x > _AI_XPOS, x < -_AI_XNEG
+    return torch.where(big, ai_p, torch.where(neg, ai_n, ai_s)), torch.where(big, aip_p, torch.where(neg, aip_n, aip_s))
 
 
 def airy_base_jets(x, n):
-    """[N,3] = (psi, psi', psi'') of the gravity-well base psi_n = Ai(x + alpha_n) / sqrt(sum(Ai^2) dx), exactly as
-    R/gravity_well_pinn_simulation.py:135-160 builds it: scipy on the host in fp64, dx = x[1] - x[0] of the grid it is
-    given, psi'' = np.gradient(psi', dx) (a finite difference, not the Airy equation), cast to float32.  The host
-    round trip is the reference's own; it is O(N) and outside the timed kernels."""
-    hit = _AIRY_CACHE.get((id(x), n))
-    if hit is not None and hit[0]() is x and hit[1] == x._version:
-        return hit[2]          # same grid tensor as the last call (every epoch of a training loop): no host round trip
-    from scipy.special import ai_zeros, airy
-    xn = x.detach().reshape(-1).cpu().numpy()
-    ai_val, aip_val, _, _ = airy(xn + ai_zeros(n + 1)[0][n])
-    dx = xn[1] - xn[0] if len(xn) > 1 else 0.01
-    nf = np.sqrt(np.sum(ai_val ** 2) * dx)
-    d2 = np.gradient(aip_val / nf, dx) if len(xn) > 1 else np.zeros_like(aip_val)
-    out = torch.from_numpy(np.stack([ai_val / nf, aip_val / nf, d2], axis=1).astype(np.float32)).to(x.device).contiguous()
-    if len(_AIRY_CACHE) >= 16:
-        _AIRY_CACHE.clear()
-    try:
-        _AIRY_CACHE[(id(x), n)] = (weakref.ref(x), x._version, out)
-    except TypeError:
-        pass
-    return out
+    """[N,3] = (psi, psi', psi'') of the gravity-well base psi_n = Ai(x + alpha_n) / sqrt(sum(Ai^2) dx), as
+    R/gravity_well_pinn_simulation.py:135-160 builds it -- dx = x[1] - x[0] of the (float32) grid it is given,
+    psi'' = np.gradient(psi', dx) (a finite difference, not the Airy equation), float64 arithmetic, cast to float32 -- but
+    on the device: the reference's scipy/numpy host round trip per call is gone."""
+    if n >= len(_AI_ZEROS):
+        raise ValueError(f"gravity-well mode {n}: Airy zeros are tabulated for modes 0..{len(_AI_ZEROS) - 1}")
+    xf = x.detach().reshape(-1).float()
+    arg = xf.double() + _AI_ZEROS[n]
+    ai, aip = airy_ai(arg)
+    ai = torch.where(arg == _AI_ZEROS[n], torch.full_like(ai, _AI_AT_ZEROS[n]), ai)
+    if xf.numel() > 1:
+        dx = (xf[1] - xf[0]).double()                    # float32 difference, as numpy forms it from the float32 grid
+        nf = torch.sqrt(torch.sum(ai * ai) * dx)
+        p1 = aip / nf
+        d2 = torch.empty_like(p1)                        # np.gradient: central differences, one-sided at the two ends
+        d2[1:-1] = (p1[2:] - p1[:-2]) / (2.0 * dx)
+        d2[0], d2[-1] = (p1[1] - p1[0]) / dx, (p1[-1] - p1[-2]) / dx
+    else:
+        nf = torch.sqrt(torch.sum(ai * ai) * 0.01)
+        p1, d2 = aip / nf, torch.zeros_like(aip)
+    return torch.stack([ai / nf, p1, d2], dim=1).float().contiguous()
 
 
 class _GPE1DBase(JetMLP):

@@ -252,3 +252,31 @@ def test_loss_as_epoch_learning_rate_matches_torch_scheduler():
         want = opt.param_groups[0]["lr"]
         got = float(_loss_as_epoch_lr(torch.tensor(loss, dtype=torch.float64), base))
         assert abs(got - want) <= 1e-9 * base + 1e-6 * abs(want), (loss, got, want)   # the scheduler works on the float32 tensor
+
+
+def test_airy_base_on_device_matches_the_scipy_construction():
+    """gpe_b200.models.airy_base_jets (pure torch, runs where x lives) against the reference's host construction
+    (R/gravity_well_pinn_simulation.py:135-160: scipy airy + ai_zeros, np.gradient), for every tabulated mode, on the
+    training grid and on the two boundary points (where psi(lb) is the sign of scipy's rounding residue at the zero)."""
+    from scipy.special import ai_zeros, airy
+    from gpe_b200.models import airy_ai, airy_base_jets
+    xs = torch.linspace(-60.0, 40.0, 50001, dtype=torch.float64)
+    ai, aip = airy_ai(xs)
+    ra, rap = airy(xs.numpy())[:2]
+    amp = np.where(xs.numpy() < 0, np.maximum(np.abs(xs.numpy()), 1.0) ** -0.25 / np.sqrt(np.pi), np.abs(ra))
+    ampp = np.where(xs.numpy() < 0, np.maximum(np.abs(xs.numpy()), 1.0) ** 0.25 / np.sqrt(np.pi), np.abs(rap))
+    assert (np.abs(ai.numpy() - ra) / amp).max() < 5e-8 and (np.abs(aip.numpy() - rap) / ampp).max() < 5e-8
+    for n in range(16):
+        for npts in (4000, 1200, 2):
+            x = torch.tensor(np.linspace(0, 35, npts).reshape(-1, 1), dtype=torch.float32)
+            got = airy_base_jets(x, n).numpy()
+            xn = x.reshape(-1).numpy()
+            a, ap = airy(xn + ai_zeros(n + 1)[0][n])[:2]
+            dx = xn[1] - xn[0]
+            nf = np.sqrt(np.sum(a ** 2) * dx)
+            ref = np.stack([a / nf, ap / nf, np.gradient(ap / nf, dx)], 1).astype(np.float32)
+            cols = 1 if npts == 2 else 3          # airy_solution (value only) is all the two-point case feeds
+            err = np.abs(got - ref)[:, :cols].max(0) / np.abs(ref)[:, :cols].max(0)
+            assert err.max() < 2e-7, (n, npts, err)
+    with pytest.raises(ValueError):
+        airy_base_jets(torch.zeros(4, 1), 16)
