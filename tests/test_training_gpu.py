@@ -59,6 +59,42 @@ def test_adam_trajectory_root_1d():
     assert rel_err(hist["gpu"][:, 0], hist["ref"][:, 0]) < 1e-4, (hist["gpu"][-1], hist["ref"][-1])
 
 
+def test_adam_trajectory_box_to_gaussian_residual_blocks():
+    """The loop body of R/box_to_gaussian_pinn_simulation.py:347-378 (perturbation scaling, 10 bc + 20 norm + pde, clip 1.0,
+    Adam, CosineAnnealingWarmRestarts) on the ResidualBlock network [1,64,64,64,1], 4000-point grid of its main: the
+    B200 class (GPE_ACT_RESBLOCK_TANH kernels) against the float64 oracle, 15 steps."""
+    import gpe_b200
+    layers, lb, ub, n, gamma, p, pc = [1, 64, 64, 64, 1], 0.0, 1.0, 4000, 10.0, 3, 0.01
+    ref = _xavier(po.BoxToGaussianGPE1D(layers, mode=1, gamma=gamma), 5).double()
+    gpu = gpe_b200.BoxToGaussianGPE1D(layers, mode=1, gamma=gamma)
+    gpu.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    gpu = gpu.cuda()
+    X64 = torch.linspace(lb, ub, n, dtype=torch.float64).view(-1, 1)
+    dx = float(X64[1] - X64[0])
+    bp64 = torch.tensor([[lb], [ub]], dtype=torch.float64)
+    const = float(ref(X64).max())
+    hist = {}
+    for name, model, X, bp in (("ref", ref, X64.clone().requires_grad_(True), bp64),
+                               ("gpu", gpu, X64.float().cuda().requires_grad_(True), bp64.float().cuda())):
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+        sched = torch.optim.lr_scheduler.CosineAnnealingWarmRestarts(opt, T_0=200, T_mult=2, eta_min=1e-6)
+        out = []
+        for _ in range(15):
+            opt.zero_grad()
+            total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros_like(bp), dx, gamma, p, pc, const)
+            total.backward()
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+            opt.step()
+            sched.step()
+            out.append((float(total), float(mu)))
+        hist[name] = np.array(out)
+    assert np.all(np.isfinite(hist["gpu"]))
+    assert rel_err(hist["gpu"][:, 1], hist["ref"][:, 1]) < 1e-4, (hist["gpu"][-1], hist["ref"][-1])
+    assert rel_err(hist["gpu"][:, 0], hist["ref"][:, 0]) < 1e-4, (hist["gpu"][-1], hist["ref"][-1])
+    for a, b in zip(gpu.parameters(), ref.parameters()):
+        assert rel_err(a.detach().cpu(), b.detach()) < 1e-4
+
+
 def test_adam_trajectory_gpe2d():
     """Config-4 network [2,128x4,1], 3000 points, pointwise semantics, 20 Adam steps."""
     import gpe_b200
