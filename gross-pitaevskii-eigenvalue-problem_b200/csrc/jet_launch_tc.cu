@@ -90,21 +90,23 @@ struct TcScope {
     }
 };
 
-static int tc_interleave() {   // GPE_TC_INTERLEAVE=1: see TcParams::interleave
+static int tc_env_mode(const char* name, int dflt);
+static int tc_interleave() {
     static int v = -1;
-    if (v < 0) { const char* ev = getenv("GPE_TC_INTERLEAVE"); v = (ev && ev[0] == '1') ? 1 : 0; }
+    if (v < 0) v = tc_env_mode("GPE_TC_INTERLEAVE", 0);
     return v;
 }
 
-// Forward / stash-forward kernel: the hi*hi MMAs of a 32-column chunk are issued right after its correction MMAs, so only
-// 12 MMAs (not 24) trail the last chunk and the epilogue warps wait less on the accumulator barrier: forward 10.95 -> 9.82 ms
-// per 4M points.  More accumulator roundings land at full magnitude: jets 0.3-1.2e-6 -> 0.6-2.8e-6, gradients 1.0-1.6e-6 ->
-// 1.3-2.2e-6 against the fp64 oracle (bound 1e-5).  GPE_TC_INTERLEAVE_FWD=0 restores corrections-first in the forward too;
-// the reverse sweep keeps corrections-first (GPE_TC_INTERLEAVE=1 interleaves everywhere).
+// MMA issue order (TcParams::interleave).  Forward / stash-forward kernel: GPE_TC_INTERLEAVE_FWD = 0 | 1, default 1;
+// reverse sweep: GPE_TC_INTERLEAVE = 0 | 1, default 0 (a non-zero value also sets the forward's unless that is given).
+static int tc_env_mode(const char* name, int dflt) {
+    const char* ev = getenv(name);
+    return (ev && ev[0] >= '0' && ev[0] <= '1') ? ev[0] - '0' : dflt;
+}
 static int tc_interleave_fwd() {
     static int v = -1;
-    if (v < 0) { const char* ev = getenv("GPE_TC_INTERLEAVE_FWD"); v = (ev && ev[0] == '0') ? 0 : 1; }
-    return v | tc_interleave();
+    if (v < 0) { const int r = tc_interleave(); v = tc_env_mode("GPE_TC_INTERLEAVE_FWD", 1) | r; }
+    return v;
 }
 
 static int tc_sms() {

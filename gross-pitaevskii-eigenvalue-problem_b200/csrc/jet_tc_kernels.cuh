@@ -44,8 +44,14 @@ struct TcParams {
     int act;
     const float* wimg;     // [L-1][cta 2][hi,lo][kImgFloats]
     const float* small;    // W0t[D][128], b[L][128], wout[128], bout[4]   (same pack as the FFMA path)
-    int interleave;        // 1: issue the hi*hi MMAs of a chunk right after its correction MMAs (shorter exposed tail,
-                           //    more accumulator roundings at full magnitude); 0: all corrections first (default)
+    int interleave;        // order of the 16 hi*hi MMAs of a layer relative to its 32 correction MMAs (the accumulator is rounded
+                           // toward zero after every MMA, so what lands late lands on a large accumulator):
+                           //   0: all corrections first, hi*hi last -- 24 MMAs trail the last chunk, fewest roundings at size;
+                           //   1: hi*hi of a chunk right after its corrections -- 12 MMAs trail and the tensor work is spread
+                           //      evenly under the epilogue of the next chunk; most roundings at size.
+                           // (Tried: corrections of chunks 0..2, then hi*hi of chunks 0..2 under the epilogue of chunk 3, then chunk
+                           // 3 -- also 12 trailing MMAs and fewer late roundings, but 20 MMAs do not fit under one chunk's epilogue:
+                           // forward 11.0 ms per 4M points against 11.7 (order 0) and 9.7 (order 1).)
 };
 
 constexpr int kDw0Stride = 12;   // floats per (row, feature) of the input-layer accumulator: 8 point slots, conflict-free banks
@@ -320,7 +326,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                         mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
                     }
-                    if (P.interleave) {
+                    if (P.interleave == 1) {
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk) {
                             const int j = 4 * c + kk;
@@ -330,7 +336,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                 }
                 // ... and the 16 hi*hi products last: the accumulator is rounded toward zero after every MMA, so
                 // the 32 correction MMAs land while it is ~2^-11 of its final size and only 16 roundings count
-                if (!P.interleave) {
+                if (P.interleave != 1) {
 #pragma unroll 4
                     for (int j = 0; j < 16; ++j)
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
@@ -604,7 +610,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                         mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, bhi, idesc, j > 0 ? 1u : 0u);
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, blo, idesc, 1u);
                     }
-                    if (P.interleave) {
+                    if (P.interleave == 1) {
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk) {
                             const int j = 4 * c + kk;
@@ -614,7 +620,7 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                 }
                 // ... and the 16 hi*hi products last: the accumulator is rounded toward zero after every MMA, so
                 // the 32 correction MMAs land while it is ~2^-11 of its final size and only 16 roundings count
-                if (!P.interleave) {
+                if (P.interleave != 1) {
 #pragma unroll 4
                     for (int j = 0; j < 16; ++j)
                         mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, smem_desc(bhi0 + j * 256, 128, 4096), idesc, 1u);
