@@ -61,8 +61,11 @@ __global__ void pack_weights_kernel(PtrArray W, PtrArray B, int D, int L, int Wd
 }
 
 // sum the per-CTA hidden-layer accumulators and scatter everything into PyTorch-shaped grads
-__global__ void finish_grads_kernel(const float* __restrict__ dWacc, int n_cta, const float* __restrict__ small_acc,
-                                    int D, int L, int Wd, int WP, MutPtrArray dW, MutPtrArray dB) {
+// dWacc: per-CTA fp32 accumulators of the FFMA path (n_cta of them), or -- acc64 != nullptr -- the single fp64
+// accumulator of the tensor path (the dW contraction adds every CTA's partial sums into it with fp64 atomics, so the
+// sum over CTAs and launches carries no fp32 rounding)
+__global__ void finish_grads_kernel(const float* __restrict__ dWacc, const double* __restrict__ acc64, int n_cta,
+                                    const float* __restrict__ small_acc, int D, int L, int Wd, int WP, MutPtrArray dW, MutPtrArray dB) {
     const long long n_hidden_el = (long long)(L - 1) * Wd * Wd;
     const long long n_rest = (long long)Wd * D + (long long)L * Wd + Wd + 1;
     const size_t cta_stride = (size_t)(L - 1) * WP * WP;
@@ -72,9 +75,13 @@ __global__ void finish_grads_kernel(const float* __restrict__ dWacc, int n_cta, 
             const int l = (int)(idx / ((long long)Wd * Wd));
             const int rem = (int)(idx % ((long long)Wd * Wd));
             const int o = rem / Wd, i = rem % Wd;
-            const float* src = dWacc + (size_t)l * WP * WP + (size_t)o * WP + i;
+            const size_t at = (size_t)l * WP * WP + (size_t)o * WP + i;
             double s = 0.0;
-            for (int c = 0; c < n_cta; ++c) s += (double)src[(size_t)c * cta_stride];
+            if (acc64) {
+                if (n_cta > 0) s = acc64[at];
+            } else {
+                for (int c = 0; c < n_cta; ++c) s += (double)dWacc[at + (size_t)c * cta_stride];
+            }
             dW.p[l + 1][(size_t)o * Wd + i] = (float)s;
         } else {
             long long j = idx - n_hidden_el;
@@ -179,7 +186,7 @@ WsLayout layout(const gpe_mlp_desc* desc, const JetPlan& p, int wp, long long n)
     w.small_acc = off; off = align_up(off + w.n_small * sizeof(float));
     w.wimg_rev = w.zb = 0;
     if (w.tc) {   // tensor path: one global accumulator, chunked stash of forward jets and of their adjoints
-        w.dWacc = off; off = align_up(off + mat);
+        w.dWacc = off; off = align_up(off + 2 * mat);   // fp64
         w.wimg_rev = off; off = align_up(off + tc_wimg_bytes(L));
         w.stash = off; off = align_up(off + tc_stash_bytes(L, n));
         w.zb = off; off = align_up(off + tc_zb_bytes(L, n));
@@ -364,7 +371,7 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     const int L = desc->n_hidden;
     const size_t mat = (size_t)(L - 1) * wp * wp * sizeof(float);
     if (mat) {
-        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (w.tc ? (size_t)1 : (size_t)w.grid_bwd) * mat, s);
+        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (w.tc ? (size_t)2 : (size_t)w.grid_bwd) * mat, s);
         if (e != cudaSuccess) { set_error("memset: %s", cudaGetErrorString(e)); return -4; }
     }
     MlpParams P{L, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd), reinterpret_cast<float*>(base + w.w_bwd),
@@ -383,7 +390,7 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
         }
         rc = launch_bwd_tc(desc->d, L, desc->act, wimg_f, wimg_r, P.small, x, n, u_bar, g_bar, h_bar,
                            reinterpret_cast<float*>(base + w.stash), resident, reinterpret_cast<float*>(base + w.zb),
-                           reinterpret_cast<float*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc), s);
+                           reinterpret_cast<double*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc), s);
         if (rc) return rc;
     } else if (n > 0) {
         if (resident) { set_error("this descriptor has no stash (gpe_stash_bytes = 0): use gpe_mlp_jet_bwd"); return -1; }
@@ -404,8 +411,9 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     }
     const long long total = (long long)(L - 1) * desc->width * desc->width + (long long)desc->width * (desc->d + L + 1) + 1;
     const int blocks = (int)((total + 255) / 256);
-    finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc), n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0,
-                                               reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
+    finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc),
+                                               w.tc ? reinterpret_cast<double*>(base + w.dWacc) : nullptr,
+                                               n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0, reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
     return check_launch("finish_grads_kernel");
 }
 

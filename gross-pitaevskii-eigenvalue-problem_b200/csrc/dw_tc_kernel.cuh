@@ -80,7 +80,7 @@ __host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n1) {
 template <int D, int ACT = -1>
 __global__ void __launch_bounds__(kDwThreads, 1)
 dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __restrict__ x, long long n, long long stash_ls, long long lstride,
-             const float* __restrict__ stash, const float* __restrict__ zb, float* __restrict__ dWacc, float* __restrict__ small_acc,
+             const float* __restrict__ stash, const float* __restrict__ zb, double* __restrict__ dWacc, float* __restrict__ small_acc,
              int num_blocks, int n1_cta, int pf_dist) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
     using tc::tmem_wait_st; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit;
@@ -227,12 +227,13 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
             }
         }
         if (groups >= 1) drain(groups - 1);
-        // ---- register accumulators -> global (vector RED, one per 4 elements and CTA) ----
+        // ---- register accumulators -> the global fp64 accumulator (one RED per element and CTA): the sum over the ~50 CTAs
+        // of a layer and the 64 launches of a 16M-point step is exact to fp64, only the per-CTA partial sums are fp32 ----
         if (items > 0) {
             const int o = 32 * q + lane;
-            float* dst = dWacc + ((size_t)(l - 1) * 128 + o) * 128 + 32 * grp;
+            double* dst = dWacc + ((size_t)(l - 1) * 128 + o) * 128 + 32 * grp;
 #pragma unroll
-            for (int c = 0; c < 32; c += 4) red_add_v4(dst + c, acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
+            for (int c = 0; c < 32; ++c) atomicAdd(dst + c, (double)acc[c]);
             atomicAdd(&small_acc[(D + l) * 128 + o], bsum);
         }
     } else if (w == kDwConvWarps) {

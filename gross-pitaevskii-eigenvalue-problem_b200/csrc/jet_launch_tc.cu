@@ -121,7 +121,7 @@ static int tc_sms() {
 
 template <int D, int ACT>
 static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
-                  const float* hb, float* stash, const float* resident, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
+                  const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
     const int sms = tc_sms(), L = Pf.n_hidden;
     const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes();
     cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -171,7 +171,7 @@ static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const fl
 
 template <int D>
 static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
-                  const float* hb, float* stash, const float* resident, float* zb, float* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
+                  const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
     return (Pf.act == ACT_TANH && !tc_act_generic()) ? bwd_tc_act<D, ACT_TANH>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s)
                               : bwd_tc_act<D, -1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s);
 }
@@ -188,7 +188,7 @@ size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd
 
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, const float* resident, float* zb,
-                  float* dWacc, float* small_acc, cudaStream_t s) {
+                  double* dWacc, float* small_acc, cudaStream_t s) {
     tcp::TcParams Pf{L, act, wimg_fwd, small, tc_interleave_fwd()}, Pr{L, act, wimg_rev, small, tc_interleave()};
     const long long chunk = tc_bwd_chunk(n);
     return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s)
