@@ -181,11 +181,13 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
                 for (int j = 0; j < 2; ++j) {
                     const int r = tid + kDwConvWarps * 32 * j;
                     const float4 sv = *reinterpret_cast<const float4*>(AH + 16 * r);
-                    const float st[4] = {sv.x, sv.y, sv.z, sv.w};
-                    float a[4] = {0.f, 0.f, 0.f, 0.f};
-                    act_jet_from_stash<D, JET_LAPLACIAN>(st, a, act);
+                    const float sv4[4] = {sv.x, sv.y, sv.z, sv.w};
+                    float st[D + 2], a[D + 2];
+#pragma unroll
+                    for (int s = 0; s < D + 2; ++s) st[s] = sv4[s];
+                    tc_act_from_stash<D, ACT>(st, a, act);
                     uint4 h, lw;
-                    split4(make_float4(a[0], a[1], a[2], a[3]), h, lw);
+                    split4(make_float4(a[0], a[1], a[2], D == 2 ? a[D + 1] : 0.f), h, lw);
                     *reinterpret_cast<uint4*>(AH + 16 * r) = h;
                     *reinterpret_cast<uint4*>(AL + 16 * r) = lw;
                 }
@@ -200,17 +202,18 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     const int fj = f + 64 * j;
-                    float z[4] = {w0s[D * 128 + fj], 0.f, 0.f, 0.f};
+                    float z[D + 2];
+                    z[0] = w0s[D * 128 + fj];
+                    z[D + 1] = 0.f;
 #pragma unroll
                     for (int k = 0; k < D; ++k) {
                         const float wk = w0s[k * 128 + fj];
                         z[0] = fmaf(wk, xv[k], z[0]);
                         z[1 + k] = wk;
                     }
-                    float st0;
-                    act_jet_fwd<D, JET_LAPLACIAN>(z, act, st0);
+                    tc_act_fwd<D, ACT>(z, act);
                     uint4 h, lw;
-                    split4(make_float4(z[0], z[1], z[2], z[3]), h, lw);
+                    split4(make_float4(z[0], z[1], z[2], D == 2 ? z[D + 1] : 0.f), h, lw);
                     *reinterpret_cast<uint4*>(AH + blk_off(fj, pp)) = h;
                     *reinterpret_cast<uint4*>(AL + blk_off(fj, pp)) = lw;
                 }

@@ -2,6 +2,7 @@
 #include "jet_host.h"
 #include <cstdlib>
 #include <mutex>
+#include <utility>
 #include <vector>
 #include "jet_tc_kernels.cuh"
 
@@ -23,17 +24,41 @@ int tc_pack_wimg(const PtrArray& W, int L, int Wd, int transpose, float* wimg, c
 
 static int tc_interleave();
 
+// Per-device facts, looked up once per device (several devices may be driven from one process).
+constexpr int kMaxDev = 64;
+static int cur_dev() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev < 0 || dev >= kMaxDev ? 0 : dev;
+}
+static int tc_sms() {
+    static int sms[kMaxDev] = {};
+    const int dev = cur_dev();
+    if (!sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    return sms[dev];
+}
+// cudaFuncAttributeMaxDynamicSharedMemorySize is set once per (kernel, device): the largest footprint any eligible network
+// needs (kTcMaxMat resident matrices), so the launches themselves carry no attribute call.
+static std::mutex g_attr_mu;
+static std::vector<std::pair<const void*, int>> g_attr_done;   // (kernel, device) pairs already configured
+template <typename K>
+static int ensure_smem(K kernel, size_t smem, const char* what) {
+    const std::pair<const void*, int> key(reinterpret_cast<const void*>(kernel), cur_dev());
+    std::lock_guard<std::mutex> lk(g_attr_mu);
+    for (const auto& k : g_attr_done)
+        if (k == key) return 0;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { set_error("%s: shared-memory attribute (%zu B): %s", what, smem, cudaGetErrorString(e)); return -3; }
+    g_attr_done.push_back(key);
+    return 0;
+}
+
 template <int D, bool STASH, int ACT>
 static int fwd_tc_act(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    }
+    const int sms = tc_sms();
     const size_t smem = tcp::tc_smem_bytes(D, P.n_hidden);
-    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, STASH, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) { set_error("tc fwd smem attr (%zu B): %s", smem, cudaGetErrorString(e)); return -3; }
+    if (int rc = ensure_smem(tcp::jet_fwd_tc_kernel<D, STASH, ACT>, tcp::tc_smem_bytes(D, tcp::kTcMaxMat + 1), "jet_fwd_tc_kernel")) return rc;
+    cudaError_t e;
     const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
     long long clusters = sms / 2;
     if (pairs < clusters) clusters = pairs;
@@ -109,25 +134,16 @@ static int tc_interleave_fwd() {
     return v;
 }
 
-static int tc_sms() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    }
-    return sms;
-}
-
 template <int D, int ACT>
 static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
                   const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
     const int sms = tc_sms(), L = Pf.n_hidden;
     const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes();
-    cudaError_t e = cudaFuncSetAttribute(tcp::jet_fwd_tc_kernel<D, true, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::jet_rev_tc_kernel<D, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tcp::dw_tc_kernel<D, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dw);
-    if (e != cudaSuccess) { set_error("tc bwd smem attr: %s", cudaGetErrorString(e)); return -3; }
+    const size_t smem_max = tcp::tc_smem_bytes(D, tcp::kTcMaxMat + 1);
+    if (int rc = ensure_smem(tcp::jet_fwd_tc_kernel<D, true, ACT>, smem_max, "jet_fwd_tc_kernel")) return rc;
+    if (int rc = ensure_smem(tcp::jet_rev_tc_kernel<D, ACT>, smem_max, "jet_rev_tc_kernel")) return rc;
+    if (int rc = ensure_smem(tcp::dw_tc_kernel<D, ACT>, smem_dw, "dw_tc_kernel")) return rc;
+    cudaError_t e;
     static int rev_pf = -1;   // GPE_REV_PF: L2 prefetch distance of the reverse sweep, in (tile, layer) steps
     if (rev_pf < 0) { const char* ev = getenv("GPE_REV_PF"); rev_pf = ev ? atoi(ev) : 1; if (rev_pf < 1) rev_pf = 1; }
     for (long long c0 = 0; c0 < n; c0 += chunk) {

@@ -67,10 +67,84 @@ __host__ __device__ __forceinline__ uint32_t img_off128(int r, int c) {
     return (uint32_t)((r >> 3) * 4096 + (c >> 2) * 128 + (r & 7) * 16 + (c & 3) * 4);
 }
 
-__device__ __forceinline__ uint32_t tf32_hi(float v) {
-    uint32_t h;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
-    return h;
+// RN (ties away) to tf32: what `cvt.rna.tf32.f32` computes -- ptxas emulates that instruction on sm_100a with four
+// instructions (add, inf test, select, mask; measured in the round-1 SASS: 20 of the 82 instructions per (point, feature)
+// of the forward epilogue); the add + mask below is the same rounding for every finite value below 2^127.
+__device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
+
+// tanh for the tensor-path epilogues: 1 - 2 / (1 + e^{2x}), one MUFU.EX2 + one MUFU.RCP, branch free, exact limits at
+// +-inf.  Absolute error <= 2e-7 (two units in the last place of 1), i.e. the rounding class of the fp32 sums the
+// activations feed; tanhf costs ~17 instructions with two predicated paths.
+__device__ __forceinline__ float tanh_tc(float x) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.8853900817779268f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.f));
+    return fmaf(-2.f, r, 1.f);
+}
+
+// Activation jets of the tensor-path kernels (JET_LAPLACIAN streams: value, D first derivatives, trace).  ACT fixed at
+// compile time for tanh / ShiftedTanh (no runtime branches); ACT = -1 takes the generic code of jet_common.cuh.
+// z: pre-activation jets in, post-activation jets out; returns the value the reverse sweep needs (tanh(z0)).
+template <int D, int ACT>
+__device__ __forceinline__ float tc_act_fwd(float (&z)[D + 2], int act) {
+    if (ACT == ACT_TANH || ACT == ACT_SHIFTED_TANH) {
+        const float t = tanh_tc(z[0]);
+        const float s1 = fmaf(-t, t, 1.f);
+        const float s2 = (-2.f * t) * s1;
+        float q = z[1] * z[1];
+        if (D == 2) q = fmaf(z[2], z[2], q);
+        z[1 + D] = fmaf(s1, z[1 + D], s2 * q);
+#pragma unroll
+        for (int i = 0; i < D; ++i) z[1 + i] *= s1;
+        z[0] = ACT == ACT_SHIFTED_TANH ? t + 1.f : t;
+        return t;
+    } else {
+        float st0;
+        act_jet_fwd<D, JET_LAPLACIAN>(z, act, st0);
+        return st0;
+    }
+}
+// stash {t, z1.., ztrace} -> post-activation jets
+template <int D, int ACT>
+__device__ __forceinline__ void tc_act_from_stash(const float (&st)[D + 2], float (&a)[D + 2], int act) {
+    if (ACT == ACT_TANH || ACT == ACT_SHIFTED_TANH) {
+        const float t = st[0];
+        const float s1 = fmaf(-t, t, 1.f);
+        const float s2 = (-2.f * t) * s1;
+        float q = st[1] * st[1];
+        if (D == 2) q = fmaf(st[2], st[2], q);
+        a[0] = ACT == ACT_SHIFTED_TANH ? t + 1.f : t;
+#pragma unroll
+        for (int i = 0; i < D; ++i) a[1 + i] = s1 * st[1 + i];
+        a[1 + D] = fmaf(s1, st[1 + D], s2 * q);
+    } else {
+        act_jet_from_stash<D, JET_LAPLACIAN>(st, a, act);
+    }
+}
+// reverse of the activation jets: ab (adjoint of the post-activation jets) -> adjoint of the pre-activation jets, in place
+template <int D, int ACT>
+__device__ __forceinline__ void tc_act_bwd(const float (&st)[D + 2], float (&ab)[D + 2], int act) {
+    if (ACT == ACT_TANH || ACT == ACT_SHIFTED_TANH) {
+        const float t = st[0];
+        const float s1 = fmaf(-t, t, 1.f);
+        const float s2 = (-2.f * t) * s1;
+        const float s3 = (-2.f * s1) * fmaf(-3.f * t, t, 1.f);
+        const float a2b = ab[1 + D];
+        const float c2 = (2.f * s2) * a2b;
+        float z0b = s1 * ab[0];
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            const float z1 = st[1 + i];
+            q = fmaf(z1, z1, q);
+            z0b = fmaf(s2 * z1, ab[1 + i], z0b);
+            ab[1 + i] = fmaf(s1, ab[1 + i], c2 * z1);
+        }
+        ab[0] = fmaf(fmaf(s3, q, s2 * st[1 + D]), a2b, z0b);
+        ab[1 + D] = s1 * a2b;
+    } else {
+        act_jet_bwd<D, JET_LAPLACIAN>(st, ab, act);
+    }
 }
 
 // hidden weight images for the tensor path.  transpose = 0: B[n = out][k = in] (forward);
@@ -192,9 +266,27 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
     const int act = ACT >= 0 ? ACT : P.act;
 
     if (w < kEpiWarps) {
+        // Three code paths per tile -- input layer (from x, no accumulator), middle layers, last hidden layer (output dot
+        // product, nothing handed on) -- so none of them carries the others' predicated-off instructions.
         const int q = w & 3, sub = w >> 2, pl = lane >> 2, tq = lane & 3;
         const uint32_t lane_lo = tb + ((uint32_t)(32 * q) << 16), lane_hi = lane_lo + (16u << 16);
-        uint32_t dcnt[2] = {0u, 0u};
+        const int fb = kCw * sub + 2 * tq;                 // this thread's feature pair inside every 32-column chunk
+        uint32_t dc0 = 0u, dc1 = 0u;                       // completed phases of d_full[0] / d_full[1]
+        // split the four stream slots of features (f, f + 1) and hand the chunk to the MMA thread
+        auto hand_over = [&](int c, const float (&a)[2][R]) {
+            uint32_t LoHi[4], HiHi[4], LoLo[4], HiLo[4];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) put_slots<R>(a[e], 0, e, LoHi, HiHi, LoLo, HiLo);
+            const uint32_t col = (uint32_t)(32 * c + kCw * sub);
+            IO::st(lane_lo + kColAHi + col, LoHi);
+            IO::st(lane_hi + kColAHi + col, HiHi);
+            IO::st(lane_lo + kColALo + col, LoLo);
+            IO::st(lane_hi + kColALo + col, HiLo);
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
+        };
         for (int it = 0;; ++it) {
             const long long T = cluster_id + (long long)it * num_clusters;
             if (T >= num_pairs) break;
@@ -202,85 +294,82 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
             const bool valid = p < n;
             float xin[D];
 #pragma unroll
-            for (int i = 0; i < D; ++i) xin[i] = valid ? x[p * D + i] : 0.f;
+            for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
+            // whole image blocks are written: the tail rows (x = 0) stay finite
+            float* sp = stash + slot_off(p, sub, tq);
+            const bool do_stash = STASH && (p >> 3) < nblk8;
+            // ---- input layer: z0 = W_0 x + b_0, dz0/dx_k = W_0[:,k], no second derivatives ----
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                const int f = 32 * c + fb;
+                const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
+                float2 w2[D];
+#pragma unroll
+                for (int k = 0; k < D; ++k) w2[k] = *reinterpret_cast<const float2*>(W0t + k * 128 + f);
+                float a[2][R];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    float z0 = e ? b2.y : b2.x;
+#pragma unroll
+                    for (int k = 0; k < D; ++k) {
+                        const float wk = e ? w2[k].y : w2[k].x;
+                        z0 = fmaf(wk, xin[k], z0);
+                        a[e][1 + k] = wk;
+                    }
+                    a[e][0] = z0;
+                    a[e][1 + D] = 0.f;
+                    tc_act_fwd<D, ACT>(a[e], act);
+                }
+                hand_over(c, a);
+            }
+            // ---- hidden layers 1 .. L-1 ----
             float o[R];
 #pragma unroll
             for (int s = 0; s < R; ++s) o[s] = 0.f;
-            for (int l = 0; l < L; ++l) {
-                const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
-                if (l > 0) {
-                    mbar_wait(&d_full[l & 1], dcnt[l & 1] & 1u);
-                    ++dcnt[l & 1];
-                    tc_fence_after();
-                }
-                const float* bl = bias + l * 128;
 #pragma unroll 1
+            for (int l = 1; l < L; ++l) {
+                const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
+                if (l & 1) { mbar_wait(&d_full[1], dc1 & 1u); ++dc1; } else { mbar_wait(&d_full[0], dc0 & 1u); ++dc0; }
+                tc_fence_after();
+                const float* bl = bias + l * 128;
+                const bool last = l == L - 1;
+                float* spl = sp + (size_t)(l - 1) * stash_ls;
+                uint32_t nLo[4], nHi[4];
+                IO::ld(lane_lo + dcol + kCw * sub, nLo);
+                IO::ld(lane_hi + dcol + kCw * sub, nHi);
+#pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    const int col0 = 32 * c + kCw * sub;   // every warp owns kCw columns of every 32-column chunk
-                    uint32_t LoHi[4 * kNI], HiHi[4 * kNI], LoLo[4 * kNI], HiLo[4 * kNI];
-                    if (l > 0) {
-                        IO::ld(lane_lo + dcol + col0, LoHi);
-                        IO::ld(lane_hi + dcol + col0, HiHi);
-                        tmem_wait_ld();
+                    const int f = 32 * c + fb;
+                    tmem_wait_ld();
+                    uint32_t LoHi[4], HiHi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                    if (c < 3) {   // the next chunk's accumulator columns travel while this chunk is computed
+                        IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                        IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
                     }
+                    const float2 b2 = *reinterpret_cast<const float2*>(bl + f);
+                    float a[2][R], sv8[8];
 #pragma unroll
-                    for (int i = 0; i < kNI; ++i) {
-                        float sv[2][R];
+                    for (int e = 0; e < 2; ++e) {
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int f = col0 + 8 * i + 2 * tq + e;
-                            float z[R];
-                            if (l == 0) {
-                                float z0 = bl[f];
+                        for (int s = 0; s < R; ++s) a[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
+                        a[e][0] += e ? b2.y : b2.x;
 #pragma unroll
-                                for (int k = 0; k < D; ++k) {
-                                    const float wk = W0t[k * 128 + f];
-                                    z0 = fmaf(wk, xin[k], z0);
-                                    z[1 + k] = wk;
-                                }
-                                z[0] = z0;
-                                z[1 + D] = 0.f;
-                            } else {
-#pragma unroll
-                                for (int s = 0; s < R; ++s) {
-                                    const int r = 4 * i + 2 * (s & 1) + e;
-                                    z[s] = __uint_as_float(s < 2 ? LoHi[r] : HiHi[r]);
-                                }
-                                z[0] += bl[f];
-                            }
-#pragma unroll
-                            for (int s = 1; s < R; ++s) sv[e][s] = z[s];
-                            act_jet_fwd<D, JET_LAPLACIAN>(z, act, sv[e][0]);
-                            if (l < L - 1) {
-                                put_slots<R>(z, i, e, LoHi, HiHi, LoLo, HiLo);
-                            } else {
-                                const float wo = wout[f];
-#pragma unroll
-                                for (int s = 0; s < R; ++s) o[s] = fmaf(wo, z[s], o[s]);
-                            }
-                        }
-                        if (STASH && l > 0 && (p >> 3) < nblk8) {   // whole blocks are written: the tail rows (x = 0) stay finite
-                            float sv8[8];
-#pragma unroll
-                            for (int e = 0; e < 2; ++e)
-#pragma unroll
-                                for (int s = 0; s < 4; ++s) sv8[4 * e + s] = s < R ? sv[e][s] : 0.f;
-                            stg_v8(stash + (size_t)(l - 1) * stash_ls + slot_off(p, (col0 >> 3) + i, tq), sv8);
-                        }
+                        for (int s = 1; s < 4; ++s) sv8[4 * e + s] = s < R ? a[e][s] : 0.f;
+                        sv8[4 * e] = tc_act_fwd<D, ACT>(a[e], act);
                     }
-                    if (l < L - 1) {
-                        IO::st(lane_lo + kColAHi + col0, LoHi);
-                        IO::st(lane_hi + kColAHi + col0, HiHi);
-                        IO::st(lane_lo + kColALo + col0, LoLo);
-                        IO::st(lane_hi + kColALo + col0, HiLo);
-                        tmem_wait_st();
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
+                    if (do_stash) stg_v8(spl + (size_t)c * 1024, sv8);
+                    if (!last) {
+                        hand_over(c, a);
+                    } else {
+                        const float2 wo = *reinterpret_cast<const float2*>(wout + f);
+#pragma unroll
+                        for (int s = 0; s < R; ++s) o[s] = fmaf(wo.y, a[1][s], fmaf(wo.x, a[0][s], o[s]));
                     }
                 }
             }
-            // output layer: reduce over the 4 lanes of a point, then over the two warps of the quadrant
+            // output layer: reduce over the 4 lanes of a point, then over the warps of the quadrant
 #pragma unroll
             for (int s = 0; s < R; ++s) {
                 o[s] += __shfl_xor_sync(0xffffffffu, o[s], 1);
@@ -412,15 +501,46 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
     const int act = ACT >= 0 ? ACT : P.act;
 
     if (w < kEpiWarps) {
+        // Three code paths per tile: last hidden layer (adjoint from the output layer, no accumulator), middle layers,
+        // input layer (forward jets recomputed from x, gradient summed in shared memory, nothing handed on).
         const int q = w & 3, sub = w >> 2, pl = lane >> 2, tq = lane & 3;
         const uint32_t lane_lo = tb + ((uint32_t)(32 * q) << 16), lane_hi = lane_lo + (16u << 16);
-        uint32_t dcnt[2] = {0u, 0u};
-        float dwout_acc[4][2 * kNI];
+        const int fb = kCw * sub + 2 * tq;                 // this thread's feature pair inside every 32-column chunk
+        uint32_t dc0 = 0u, dc1 = 0u;
+        float dwout_acc[4][2];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) dwout_acc[a][0] = dwout_acc[a][1] = 0.f;
+        float dbout_acc = 0.f;
+        float dw0_acc[4][2][D + 1];   // input-layer gradient of this thread's 8 features: dW_0[f][k], db_0[f]
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
-            for (int b = 0; b < 2 * kNI; ++b) dwout_acc[a][b] = 0.f;
-        float dbout_acc = 0.f;
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int k = 0; k <= D; ++k) dw0_acc[a][e][k] = 0.f;
+        const size_t lstride = (size_t)nblk8 * 4096;   // zbar chunk buffer: floats per layer
+        auto hand_over = [&](int c, const float (&a)[2][R]) {
+            uint32_t LoHi[4], HiHi[4], LoLo[4], HiLo[4];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) put_slots<R>(a[e], 0, e, LoHi, HiHi, LoLo, HiLo);
+            const uint32_t col = (uint32_t)(32 * c + kCw * sub);
+            IO::st(lane_lo + kColAHi + col, LoHi);
+            IO::st(lane_hi + kColAHi + col, HiHi);
+            IO::st(lane_lo + kColALo + col, LoLo);
+            IO::st(lane_hi + kColALo + col, HiLo);
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
+        };
+        auto store_zbar = [&](float* dst, const float (&ab)[2][R]) {
+            float zv8[8];
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int s = 0; s < 4; ++s) zv8[4 * e + s] = s < R ? ab[e][s] : 0.f;
+            stg_v8(dst, zv8);
+        };
         for (int it = 0;; ++it) {
             const long long T = cluster_id + (long long)it * num_clusters;
             if (T >= num_pairs) break;
@@ -428,13 +548,12 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
             const bool valid = p < n;
             float xin[D], adj[R];
 #pragma unroll
-            for (int i = 0; i < D; ++i) xin[i] = valid ? x[p * D + i] : 0.f;
-            adj[0] = (valid && u_bar) ? u_bar[p] : 0.f;
+            for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
+            adj[0] = (valid && u_bar) ? __ldg(u_bar + p) : 0.f;
 #pragma unroll
-            for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? g_bar[p * D + i] : 0.f;
-            adj[1 + D] = (valid && h_bar) ? h_bar[p] : 0.f;
+            for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? __ldg(g_bar + p * D + i) : 0.f;
+            adj[1 + D] = (valid && h_bar) ? __ldg(h_bar + p) : 0.f;
             if (sub == 0 && tq == 0) dbout_acc += adj[0];
-            const size_t lstride = (size_t)nblk8 * 4096;   // zbar chunk buffer: floats per layer
             // L2 bulk prefetch of the stash images one layer ahead of their use (4 image blocks = 64 KB contiguous per
             // tile and layer).  Not further ahead: at ~4.5 TB/s the whole L2 turns over in ~25 us.
             auto prefetch_stash = [&](int l, long long Tt) {
@@ -442,128 +561,143 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
                 if (Tt < num_pairs && bn < nblk8)
                     tc::prefetch_l2_bulk(stash + (size_t)(l - 1) * stash_ls + (size_t)bn * 4096, (uint32_t)(nblk8 - bn < 4 ? nblk8 - bn : 4) * 16384u);
             };
-            const bool in_blk = (p >> 3) < nblk8;
-            // stashed forward jets of (layer l, chunk c) for this thread: one 32-byte slot per 8-column group.  Loaded one
-            // chunk ahead (and across the layer boundary) so the load latency hides behind the previous chunk.
-            const float* sbase = stash + slot_off(in_blk ? p : 0, sub, tq);
-            auto load_stash = [&](int l, int c, float (&dst)[kNI][8]) {
-                const float* sp = sbase + (size_t)(l - 1) * stash_ls + (size_t)(4 * c) * 256;
-#pragma unroll
-                for (int i = 0; i < kNI; ++i) ldg_v8(sp + (size_t)i * 256, dst[i]);
-            };
-            if (tid == 0 && it == 0)   // the first tile's images that the rolling prefetch below does not cover
-                for (int j = 0; j < pf_dist && j < L - 1; ++j) prefetch_stash(L - 1 - j, T);
-            float cur[kNI][8];
-            if (L > 1) load_stash(L - 1, 0, cur);
-            for (int l = L - 1; l >= 0; --l) {
-                const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
-                if (tid == 0 && l >= 1) {   // the stash image consumed pf_dist (tile, layer) steps from now
+            auto rolling_prefetch = [&](int l) {   // the stash image consumed pf_dist (tile, layer) steps from now
+                if (tid == 0) {
                     const int tgt = (L - 1 - l) + pf_dist;
                     prefetch_stash(L - 1 - tgt % (L - 1), T + (long long)(tgt / (L - 1)) * num_clusters);
                 }
-                if (l < L - 1) {
-                    mbar_wait(&d_full[l & 1], dcnt[l & 1] & 1u);
-                    ++dcnt[l & 1];
-                    tc_fence_after();
+            };
+            const bool in_blk = (p >> 3) < nblk8;   // whole blocks are read and written; rows of points >= n carry zero adjoints
+            // stashed forward jets of (layer l, chunk c) for this thread: one 32-byte slot per 8-column group.  Loaded one
+            // chunk ahead (and across the layer boundary) so the load latency hides behind the previous chunk.
+            const float* sbase = stash + slot_off(in_blk ? p : 0, sub, tq);
+            float* zbase = zb + slot_off(in_blk ? p : 0, sub, tq);
+            auto load_stash = [&](int l, int c, float (&dst)[8]) { ldg_v8(sbase + (size_t)(l - 1) * stash_ls + (size_t)c * 1024, dst); };
+            if (tid == 0 && it == 0)   // the first tile's images that the rolling prefetch below does not cover
+                for (int j = 0; j < pf_dist && j < L - 1; ++j) prefetch_stash(L - 1 - j, T);
+            float cur[8];
+            load_stash(L - 1, 0, cur);
+            // ---- last hidden layer l = L-1: abar = adj * wout; output-layer gradient ----
+            rolling_prefetch(L - 1);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int f = 32 * c + fb;
+                float nxt[8];
+                if (c < 3) load_stash(L - 1, c + 1, nxt);
+                else if (L > 2) load_stash(L - 2, 0, nxt);
+                const float2 wo = *reinterpret_cast<const float2*>(wout + f);
+                float ab[2][R];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    float st[R], a[R];
+#pragma unroll
+                    for (int s = 0; s < R; ++s) st[s] = cur[4 * e + s];
+                    tc_act_from_stash<D, ACT>(st, a, act);
+                    float dw = dwout_acc[c][e];
+#pragma unroll
+                    for (int s = 0; s < R; ++s) {
+                        dw = fmaf(adj[s], a[s], dw);
+                        ab[e][s] = adj[s] * (e ? wo.y : wo.x);
+                    }
+                    dwout_acc[c][e] = dw;
+                    tc_act_bwd<D, ACT>(st, ab[e], act);
                 }
-                const float* bl = bias + l * 128;
+                if (in_blk) store_zbar(zbase + (size_t)(L - 2) * lstride + (size_t)c * 1024, ab);
+                hand_over(c, ab);
+#pragma unroll
+                for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
+            }
+            // ---- middle layers l = L-2 .. 1 ----
+#pragma unroll 1
+            for (int l = L - 2; l >= 1; --l) {
+                rolling_prefetch(l);
+                const uint32_t dcol = kColD0 + 128u * (uint32_t)(l & 1);
+                if (l & 1) { mbar_wait(&d_full[1], dc1 & 1u); ++dc1; } else { mbar_wait(&d_full[0], dc0 & 1u); ++dc0; }
+                tc_fence_after();
+                uint32_t nLo[4], nHi[4];
+                IO::ld(lane_lo + dcol + kCw * sub, nLo);
+                IO::ld(lane_hi + dcol + kCw * sub, nHi);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    const int col0 = 32 * c + kCw * sub;
-                    float nxt[kNI][8];
+                    float nxt[8];
+                    if (c < 3) load_stash(l, c + 1, nxt);
+                    else if (l > 1) load_stash(l - 1, 0, nxt);
+                    tmem_wait_ld();
+                    uint32_t LoHi[4], HiHi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
                     if (c < 3) {
-                        if (l > 0) load_stash(l, c + 1, nxt);
-                    } else if (l > 1) {
-                        load_stash(l - 1, 0, nxt);
+                        IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                        IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
                     }
-                    uint32_t LoHi[4 * kNI], HiHi[4 * kNI], LoLo[4 * kNI], HiLo[4 * kNI];
-                    if (l < L - 1) {
-                        IO::ld(lane_lo + dcol + col0, LoHi);
-                        IO::ld(lane_hi + dcol + col0, HiHi);
-                        tmem_wait_ld();
-                    }
+                    float ab[2][R];
 #pragma unroll
-                    for (int i = 0; i < kNI; ++i) {
-                        const int f0 = col0 + 8 * i + 2 * tq;
-                        float zbv[R][2];
+                    for (int e = 0; e < 2; ++e) {
+                        float st[R];
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int f = f0 + e;
-                            float st[R], ab[R];
-                            if (l > 0) {
-#pragma unroll
-                                for (int s = 0; s < R; ++s) st[s] = cur[i][4 * e + s];
-                            } else {
-                                float zz[R];
-                                float z0 = bl[f];
-#pragma unroll
-                                for (int k = 0; k < D; ++k) {
-                                    const float wk = W0t[k * 128 + f];
-                                    z0 = fmaf(wk, xin[k], z0);
-                                    zz[1 + k] = wk;
-                                }
-                                zz[0] = z0;
-                                zz[1 + D] = 0.f;
-#pragma unroll
-                                for (int s = 1; s < R; ++s) st[s] = zz[s];
-                                act_jet_fwd<D, JET_LAPLACIAN>(zz, act, st[0]);
-                            }
-                            if (l < L - 1) {
-#pragma unroll
-                                for (int s = 0; s < R; ++s) {
-                                    const int r = 4 * i + 2 * (s & 1) + e;
-                                    ab[s] = __uint_as_float(s < 2 ? LoHi[r] : HiHi[r]);
-                                }
-                            } else {
-                                float a[R];
-                                act_jet_from_stash<D, JET_LAPLACIAN>(st, a, act);
-                                const float wo = wout[f];
-                                float dw = dwout_acc[c][2 * i + e];
-#pragma unroll
-                                for (int s = 0; s < R; ++s) {
-                                    dw = fmaf(adj[s], a[s], dw);
-                                    ab[s] = adj[s] * wo;
-                                }
-                                dwout_acc[c][2 * i + e] = dw;
-                            }
-                            act_jet_bwd<D, JET_LAPLACIAN>(st, ab, act);
-#pragma unroll
-                            for (int s = 0; s < R; ++s) zbv[s][e] = ab[s];
-                            if (l > 0) put_slots<R>(ab, i, e, LoHi, HiHi, LoLo, HiLo);
+                        for (int s = 0; s < R; ++s) {
+                            st[s] = cur[4 * e + s];
+                            ab[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
                         }
-                        if (l == 0) {
-                            // input layer: dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val -- shared-memory
-                            // accumulator (the 4 warps of a feature group share an address: red.shared)
+                        tc_act_bwd<D, ACT>(st, ab[e], act);
+                    }
+                    if (in_blk) store_zbar(zbase + (size_t)(l - 1) * lstride + (size_t)c * 1024, ab);
+                    hand_over(c, ab);
 #pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                float* dq = dw0s + (size_t)(f0 + e) * kDw0Stride + pl;   // slot of this lane's point: no bank conflicts
+                    for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
+                }
+            }
+            // ---- input layer l = 0: forward jets from x; dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val ----
+            {
+                mbar_wait(&d_full[0], dc0 & 1u);
+                ++dc0;
+                tc_fence_after();
+                uint32_t nLo[4], nHi[4];
+                IO::ld(lane_lo + kColD0 + kCw * sub, nLo);
+                IO::ld(lane_hi + kColD0 + kCw * sub, nHi);
 #pragma unroll
-                                for (int k = 0; k < D; ++k) atomicAdd(dq + k * 128 * kDw0Stride, fmaf(zbv[0][e], xin[k], zbv[1 + k][e]));
-                                atomicAdd(dq + D * 128 * kDw0Stride, zbv[0][e]);
-                            }
-                        } else if (in_blk) {   // whole blocks are written; rows of points >= n carry zero adjoints
-                            float zv8[8];
+                for (int c = 0; c < 4; ++c) {
+                    const int f = 32 * c + fb;
+                    tmem_wait_ld();
+                    uint32_t LoHi[4], HiHi[4];
 #pragma unroll
-                            for (int e = 0; e < 2; ++e)
+                    for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                    if (c < 3) {
+                        IO::ld(lane_lo + kColD0 + 32 * (c + 1) + kCw * sub, nLo);
+                        IO::ld(lane_hi + kColD0 + 32 * (c + 1) + kCw * sub, nHi);
+                    }
+                    const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
+                    float2 w2[D];
 #pragma unroll
-                                for (int s = 0; s < 4; ++s) zv8[4 * e + s] = s < R ? zbv[s][e] : 0.f;
-                            stg_v8(zb + (size_t)(l - 1) * lstride + slot_off(p, (col0 >> 3) + i, tq), zv8);
+                    for (int k = 0; k < D; ++k) w2[k] = *reinterpret_cast<const float2*>(W0t + k * 128 + f);
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float st[R], ab[R];
+                        float z0 = e ? b2.y : b2.x;
+#pragma unroll
+                        for (int k = 0; k < D; ++k) {
+                            const float wk = e ? w2[k].y : w2[k].x;
+                            z0 = fmaf(wk, xin[k], z0);
+                            st[1 + k] = wk;
                         }
-                    }
-                    if (l > 0) {
-                        IO::st(lane_lo + kColAHi + col0, LoHi);
-                        IO::st(lane_hi + kColAHi + col0, HiHi);
-                        IO::st(lane_lo + kColALo + col0, LoLo);
-                        IO::st(lane_hi + kColALo + col0, HiLo);
-                        tmem_wait_st();
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive_cluster(&a_ready[c], 0);
-                    }
+                        st[1 + D] = 0.f;
+                        if (ACT == ACT_TANH || ACT == ACT_SHIFTED_TANH) {
+                            st[0] = tanh_tc(z0);
+                        } else {
+                            float zz[R];
 #pragma unroll
-                    for (int i = 0; i < kNI; ++i)
+                            for (int s = 1; s < R; ++s) zz[s] = st[s];
+                            zz[0] = z0;
+                            act_jet_fwd<D, JET_LAPLACIAN>(zz, act, st[0]);
+                        }
 #pragma unroll
-                        for (int s = 0; s < 8; ++s) cur[i][s] = nxt[i][s];
+                        for (int s = 0; s < R; ++s) ab[s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
+                        tc_act_bwd<D, ACT>(st, ab, act);
+                        // register accumulators over the tiles of this thread (shared-memory float atomics are CAS loops)
+#pragma unroll
+                        for (int k = 0; k < D; ++k) dw0_acc[c][e][k] += fmaf(ab[0], xin[k], ab[1 + k]);
+                        dw0_acc[c][e][D] += ab[0];
+                    }
                 }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");   // all D reads of this tile done
@@ -572,18 +706,31 @@ jet_rev_tc_kernel(TcParams P, const float* __restrict__ x, long long n, const fl
 #pragma unroll
         for (int c = 0; c < 4; ++c)
 #pragma unroll
-            for (int j = 0; j < 2 * kNI; ++j) {
+            for (int j = 0; j < 2; ++j) {
                 float v = dwout_acc[c][j];
                 v += __shfl_xor_sync(0xffffffffu, v, 4);
                 v += __shfl_xor_sync(0xffffffffu, v, 8);
                 v += __shfl_xor_sync(0xffffffffu, v, 16);
-                if (pl == 0) atomicAdd(&small_acc[(D + L) * 128 + 32 * c + kCw * sub + 8 * (j >> 1) + 2 * tq + (j & 1)], v);
+                if (pl == 0) atomicAdd(&small_acc[(D + L) * 128 + 32 * c + fb + j], v);
             }
-        // input-layer gradient: sum the 8 point slots, one atomic per element and CTA (rows 0..D-1: dW_0^T, row D: b_0)
+        // input-layer gradient: sum over the 8 points of the warp, then over the 4 quadrant warps of a feature group through
+        // shared memory (slot q), one global atomic per element and CTA (rows 0..D-1: dW_0^T, row D: b_0)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int k = 0; k <= D; ++k) {
+                    float v = dw0_acc[c][e][k];
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    if (pl == 0) dw0s[(size_t)(k * 128 + 32 * c + fb + e) * kDw0Stride + q] = v;
+                }
         asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
         for (int i = tid; i < (D + 1) * 128; i += kEpiWarps * 32) {
             const float* dq = dw0s + (size_t)i * kDw0Stride;
-            atomicAdd(&small_acc[i], ((dq[0] + dq[1]) + (dq[2] + dq[3])) + ((dq[4] + dq[5]) + (dq[6] + dq[7])));
+            atomicAdd(&small_acc[i], (dq[0] + dq[1]) + (dq[2] + dq[3]));
         }
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 4);
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 8);

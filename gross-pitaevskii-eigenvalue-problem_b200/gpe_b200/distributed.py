@@ -40,6 +40,29 @@ def all_reduce_sum(x: torch.Tensor, group=None) -> torch.Tensor:
     return _AllReduceSum.apply(x, group)
 
 
+class _ReplicatedTerm(torch.autograd.Function):
+    """Identity whose backward divides by the number of ranks."""
+
+    @staticmethod
+    def forward(ctx, t, world):
+        ctx.world = world
+        return t.view_as(t)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g / ctx.world, None
+
+
+def replicated_term(t: torch.Tensor, group=None) -> torch.Tensor:
+    """Mark a loss term that EVERY rank evaluates on the same (replicated) points -- the boundary / data terms, whose
+    2..500 points are not worth sharding.  `all_reduce_gradients` SUMs the ranks' gradients, so a replicated term would
+    enter the parameter gradient `world` times while the loss value counts it once; dividing its backward by `world`
+    keeps loss and gradient consistent (what an L-BFGS line search needs).  Value unchanged; no-op on one rank."""
+    if not is_active(group) or not t.requires_grad:
+        return t
+    return _ReplicatedTerm.apply(t, float(dist.get_world_size(group)))
+
+
 def shard_bounds(n: int, rank: int, world: int):
     """Contiguous block [lo, hi) of rank `rank`; block sizes differ by at most one point."""
     base, rem = divmod(n, world)

@@ -78,6 +78,17 @@ def _residual_sequential(widths):
 
 _ACT_OF = {nn.Tanh: ops.ACT_TANH, ShiftedTanh: ops.ACT_SHIFTED_TANH, nn.LeakyReLU: ops.ACT_LEAKY_RELU}
 
+#: Bumped whenever parameters may have changed behind autograd's back -- a CUDA-graph replay steps them on the device
+#: without touching `Tensor._version` (graphs.GraphedStep bumps it on every replay) -- so cached jets are never reused
+#: across such a change.  In-place edits through `.data` are invisible too: call `invalidate_caches()` after them.
+_generation = [0]
+
+
+def invalidate_caches():
+    """Drop every model's cached jets / moments (parameters were changed in a way autograd cannot see)."""
+    _generation[0] += 1
+
+
 
 class JetMLP(nn.Module):
     """Shared machinery: parameter views, the jet cache and the differentiable jet call."""
@@ -86,7 +97,9 @@ class JetMLP(nn.Module):
     #: 'full' (adds u_xy; needed when reference-style nested autograd.grad code runs on top)
     jet_mode = "laplacian"
     precision = ops.PREC_AUTO
-    #: optional torch.distributed process group (None = default group if initialised)
+    #: optional torch.distributed process group (None = default group if initialised).  Collocation points are sharded
+    #: (every rank passes its own block); boundary / data points are REPLICATED (every rank passes the same few points):
+    #: those terms go through `gdist.replicated_term`, so the SUM all-reduce of the gradients counts them once.
     group = None
     #: optional min-max feature scaling x -> (x - lb) / (ub - lb) in front of the first layer
     #: (S/helmholtz_2D_circle.py:89-94); sequences of length d, folded into (W_0, b_0) per call
@@ -132,13 +145,17 @@ class JetMLP(nn.Module):
         derivs = x.requires_grad if derivs is None else derivs
         kind = self._jet_kind(x.shape[1], derivs)
         lins = self._linears()
-        pver = tuple(p._version for lin in lins for p in (lin.weight, lin.bias))
+        pver = (_generation[0],) + tuple(p._version for lin in lins for p in (lin.weight, lin.bias))
         cache = self.__dict__.setdefault("_jet_cache", {})
         if cache.get("pver") != pver:          # parameters stepped: drop the previous step's graphs
             cache.clear()
             cache["pver"] = pver
-        key = (id(x), x._version, kind, xform, torch.is_grad_enabled())
-        hit = cache.get(key)
+        # Only results that belong to a live autograd graph are shared between the loss methods of one step (their
+        # backward hook drops them).  Without grad there is no such lifetime to tie the entry to, and the parameters can
+        # change unseen (graph replays, `.data` edits): evaluate afresh.
+        use_cache = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for lin in lins for p in (lin.weight, lin.bias)))
+        key = (id(x), x._version, kind, xform, True)
+        hit = cache.get(key) if use_cache else None
         if hit is not None and hit[0] is x:
             return hit[1]
         xin = x if x.is_contiguous() and x.dtype == torch.float32 else x.contiguous().float()
@@ -146,6 +163,8 @@ class JetMLP(nn.Module):
         if self.input_lb is not None:
             Ws[0], bs[0] = self._first_layer_folded(Ws[0], bs[0])
         out = ops.mlp_jets(xin, Ws, bs, self._act_kind(), kind, xform, self.precision)
+        if not use_cache:
+            return out
         cache[key] = (x, out)
 
         def _invalidate(_grad, cache=cache, key=key):
@@ -395,8 +414,8 @@ class RootGPE1D(_GPE1DBase):
         self.hbar, self.m, self.mode, self.gamma, self.power = hbar, m, mode, gamma, power
 
     def weighted_hermite(self, x, n):
-        """NBroot cell 6:41-48 (H_n constant for autograd), computed on the device."""
-        return hermite_base_jets(x, n, const_h=True)[:, :1]
+        """NBroot cell 6:41-48 (H_n constant for autograd), computed on the device; same shape as x."""
+        return hermite_base_jets(x, n, const_h=True)[:, 0].reshape(x.shape)
 
     def forward(self, inputs):
         """NBroot cell 6:50-54."""
@@ -435,7 +454,7 @@ class RootGPE1D(_GPE1DBase):
     def boundary_loss(self, boundary_points, boundary_values):
         """NBroot cell 6:129-135."""
         full = self.get_complete_solution(boundary_points, self.forward(boundary_points), self.mode)
-        return torch.mean((full - boundary_values) ** 2)
+        return gdist.replicated_term(torch.mean((full - boundary_values) ** 2), self.group)
 
     def symmetry_loss(self, collocation_points, lb, ub):
         """NBroot cell 6:137-155: network output only, mirror about 0, parity from the mode."""
@@ -487,7 +506,7 @@ class PaperGPE1D(RootGPE1D):
 
     def boundary_loss(self, boundary_points, boundary_values):
         full = self.get_complete_solution(boundary_points, self.forward(boundary_points))
-        return torch.mean((full - boundary_values) ** 2)
+        return gdist.replicated_term(torch.mean((full - boundary_values) ** 2), self.group)
 
     def symmetry_loss(self, collocation_points, lb, ub):
         """cell 6:193-214, on base + network: psi_n(-x) = (-1)^n psi_n(x) holds bit for bit (Horner in +-x, even
@@ -511,10 +530,11 @@ class FinalGPE1D(_GPE1DBase):
         self.enforce_boundary = (potential == "box") if enforce_boundary is None else enforce_boundary
 
     def weighted_hermite(self, x, n):
-        return hermite_base_jets(x, n, const_h=False)[:, :1]
+        """R/harmonic_pinn_simulation.py:95-119; same shape as x (the reference's pretraining calls it on X.squeeze())."""
+        return hermite_base_jets(x, n, const_h=False)[:, 0].reshape(x.shape)
 
     def box_eigenfunction(self, x, n):
-        return box_base_jets(x, n, self.L)[:, :1]
+        return box_base_jets(x, n, self.L)[:, 0].reshape(x.shape)
 
     @property
     def _has_factor(self):
@@ -528,7 +548,7 @@ class FinalGPE1D(_GPE1DBase):
         return out
 
     def airy_solution(self, x, n):
-        return airy_base_jets(x, n)[:, :1]
+        return airy_base_jets(x, n)[:, 0].reshape(x.shape)
 
     def _base(self, x, n=None):
         n = self.mode if n is None else n
@@ -569,7 +589,7 @@ class FinalGPE1D(_GPE1DBase):
         """R/harmonic_pinn_simulation.py:198-210 (unscaled network output + base)."""
         out = self.forward(boundary_points)
         full = self.get_complete_solution(boundary_points, out) if self.use_perturbation else out
-        return torch.mean((full - boundary_values) ** 2)
+        return gdist.replicated_term(torch.mean((full - boundary_values) ** 2), self.group)
 
     def normalization_loss(self, u, dx):
         return (gdist.all_reduce_sum(torch.sum(u ** 2), self.group) * dx - 1.0) ** 2
@@ -683,7 +703,7 @@ class OptGPE1D(_GPE1DBase):
         self.beta, self.alpha, self.decay_rate, self.iteration = beta_init, alpha_init, decay_rate, 0
 
     def weighted_hermite(self, x, n):
-        return hermite_base_jets(x, n, const_h=True)[:, :1]
+        return hermite_base_jets(x, n, const_h=True)[:, 0].reshape(x.shape)
 
     def forward(self, inputs):
         return self._net(inputs)
@@ -712,7 +732,7 @@ class OptGPE1D(_GPE1DBase):
 
     def boundary_loss(self, boundary_points, boundary_values, prev_prediction=None):
         u = self.get_complete_solution(boundary_points, self.forward(boundary_points), prev_prediction)
-        return torch.mean((u - boundary_values) ** 2)
+        return gdist.replicated_term(torch.mean((u - boundary_values) ** 2), self.group)
 
     def _M(self, inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, p=None, mode=None):
         """Moments of one jet evaluation; nl(u) = u^3 (= |u^2| u, :341) or |u|^(p-1) u when p is given."""
@@ -840,7 +860,7 @@ class ModesGPE1D(OptGPE1D):
 
     def boundary_loss(self, boundary_points, boundary_values, prev_prediction=None, mode=0):
         u = self.get_complete_solution(boundary_points, self.forward(boundary_points), prev_prediction, mode)
-        return torch.mean((u - boundary_values) ** 2)
+        return gdist.replicated_term(torch.mean((u - boundary_values) ** 2), self.group)
 
     def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
         M = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, None, mode)[0]
@@ -884,7 +904,7 @@ class GPE2D(JetMLP):
 
     def boundary_loss(self, x_bc, y_bc):
         """:83-109: target forced to zero, x10."""
-        return torch.mean(self.forward(x_bc) ** 2) * 10
+        return gdist.replicated_term(torch.mean(self.forward(x_bc) ** 2) * 10, self.group)
 
     def compute_potential(self, inputs, V0=1.0, x0=np.pi / 2, y0=np.pi / 2, sigma=0.5):
         """:244-274 -> [N]; 'harmonic' / 'lattice' state the BASELINE configs 4 / 5."""
@@ -900,12 +920,13 @@ class GPE2D(JetMLP):
 
     def _M(self, inputs):
         self.jets(inputs, derivs=True)                      # refreshes the per-step cache
-        key = ("M", id(inputs), inputs._version)
-        hit = self._jet_cache.get(key)
-        if hit is None or hit[0] is not inputs:
+        key = ("M", id(inputs), inputs._version, torch.is_grad_enabled())
+        hit = self._jet_cache.get(key) if torch.is_grad_enabled() else None
+        if hit is None or hit[0] is not inputs or hit[1].m.requires_grad != torch.is_grad_enabled():
             V = self.compute_potential(inputs.detach()).float().contiguous()
             hit = (inputs, self._moments(inputs, V=V, nl_kind=ops.NL_POW, nl_power=3), V)
-            self._jet_cache[key] = hit
+            if hit[1].m.requires_grad:                      # tied to a live graph: the backward hook drops it
+                self._jet_cache[key] = hit
         return hit[1], hit[2]
 
     def riesz_loss(self, predictions, inputs):
@@ -970,14 +991,14 @@ class ReLoBRaLoGPE2D(JetMLP):
 
     def boundary_loss(self, boundary_points, boundary_values):
         """:128-145."""
-        return torch.mean((self.forward(boundary_points) - boundary_values) ** 2)
+        return gdist.replicated_term(torch.mean((self.forward(boundary_points) - boundary_values) ** 2), self.group)
 
     def _M2(self, inputs):
         """Moments of the two residual columns (cached per step like GPE2D._M)."""
         u, g, h = self.jets(inputs, derivs=True)            # h = (u_xx, u_yy, u_xy)
-        key = ("M", id(inputs), inputs._version)
-        hit = self._jet_cache.get(key)
-        if hit is None or hit[0] is not inputs:
+        key = ("M", id(inputs), inputs._version, torch.is_grad_enabled())
+        hit = self._jet_cache.get(key) if torch.is_grad_enabled() else None
+        if hit is None or hit[0] is not inputs or hit[1][0].m.requires_grad != torch.is_grad_enabled():
             V = self.compute_potential(inputs.detach()).float()
             Ms = []
             for c in (0, 1):
@@ -985,7 +1006,8 @@ class ReLoBRaLoGPE2D(JetMLP):
                                      nl_kind=ops.NL_POW, nl_power=3, lap_cols=2)
                 Ms.append(L.Moments(gdist.all_reduce_sum(m, self.group)))
             hit = (inputs, Ms, V)
-            self._jet_cache[key] = hit
+            if Ms[0].m.requires_grad:
+                self._jet_cache[key] = hit
         return hit[1], hit[2]
 
     @staticmethod
@@ -1078,7 +1100,7 @@ class Helmholtz2D(JetMLP):
 
     def loss_data(self, x_u, u_true):
         """:91-108."""
-        return self.loss_function(self.forward(x_u), u_true)
+        return gdist.replicated_term(self.loss_function(self.forward(x_u), u_true), self.group)
 
     def compute_loss(self, x_f, x_u, u_true, k):
         """:110-132."""
@@ -1124,7 +1146,7 @@ class LearnableKHelmholtz2D(JetMLP):
 
     def loss_BC(self, x_bc, y_bc):
         """:84-103."""
-        return self.adaptive_bc_scale * torch.mean((self.forward(x_bc) - y_bc) ** 2)
+        return self.adaptive_bc_scale * gdist.replicated_term(torch.mean((self.forward(x_bc) - y_bc) ** 2), self.group)
 
     def _check_predictions(self, predictions):
         if predictions is not None and trace_scale(predictions) != 1.0:
