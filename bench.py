@@ -352,18 +352,19 @@ def run_b200(args):
             f_contr = 2 * W * W * (1 + 2 * d) * (L - 1)          # one hidden-layer contraction sweep per point (algorithmic)
             kname = max(tc_ms, key=tc_ms.get)
             kms = tc_ms[kname]
-            alg = {"stash_forward": f_contr, "reverse_sweep": f_contr, "dw_contraction": f_contr}[kname]
-            sym = {"stash_forward": "tcp::jet_fwd_tc_kernel<2,true,ACT_TANH>", "reverse_sweep": "tcp::jet_rev_tc_kernel<2,ACT_TANH>",
-                   "dw_contraction": "tcp::dw_tc_kernel<2,ACT_TANH>"}[kname]
+            alg = {"stash_forward": f_contr, "reverse_sweep": f_contr, "dw_contraction": f_contr, "fused_backward": 2 * f_contr}[kname]
+            sym = {"stash_forward": "tcp::jet_fwd2_tc_kernel<2,true,ACT_TANH>", "reverse_sweep": "tcp::jet_rev_tc_kernel<2,ACT_TANH>",
+                   "dw_contraction": "tcp::dw_tc_kernel<2,ACT_TANH>", "fused_backward": "tcp::bwd_fused_tc_kernel<2,ACT_TANH>"}[kname]
             bf16 = measured.get("bf16_tflops_sustained") or 1400.0
             achieved = alg * n / (kms * 1e-3) / 1e12
             # image blocks of 2 KB per point and hidden matrix l = 1..L-1: st_l written by the stash forward, read by the
             # reverse sweep (all) and the dW contraction (l <= L-2); zbar_l written by the reverse sweep, read by dW
             hbm_bytes = {"stash_forward": 8 + 2048 * (L - 1), "reverse_sweep": 8 + 16 + 2 * 2048 * (L - 1),
-                         "dw_contraction": 8 + 2048 * (L - 1) + 2048 * (L - 2)}[kname]
+                         "dw_contraction": 8 + 2048 * (L - 1) + 2048 * (L - 2),
+                         "fused_backward": 8 + 16 + 2048 * (L - 1) + 2048 * (L - 2)}[kname]
             # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch (= one 262 144-point chunk) from the committed
             # `ncu --set full` captures (profiles/r1b_tc_*_ncu_full_raw.csv); algorithmic bytes for the same launch beside it
-            ncu_traffic = {"stash_forward": 1.554e9, "reverse_sweep": 3.194e9, "dw_contraction": 2.690e9}[kname]
+            ncu_traffic = {"stash_forward": 1.554e9, "reverse_sweep": 3.194e9, "dw_contraction": 2.690e9, "fused_backward": None}[kname]
             line["roofline"] = {
                 "bound": "tensor", "kernel": sym, "achieved": achieved, "peak": bf16, "unit": "TFLOP/s", "frac": achieved / bf16,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",

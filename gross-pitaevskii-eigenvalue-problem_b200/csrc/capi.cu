@@ -64,8 +64,12 @@ __global__ void pack_weights_kernel(PtrArray W, PtrArray B, int D, int L, int Wd
 // dWacc: per-CTA fp32 accumulators of the FFMA path (n_cta of them), or -- acc64 != nullptr -- the single fp64
 // accumulator of the tensor path (the dW contraction adds every CTA's partial sums into it with fp64 atomics, so the
 // sum over CTAs and launches carries no fp32 rounding)
+// `abort_flag` (fused backward only): non-zero when the launch's flow-control watchdog fired -- the gradient is then
+// poisoned with NaN so the failure cannot pass unnoticed.
 __global__ void finish_grads_kernel(const float* __restrict__ dWacc, const double* __restrict__ acc64, int n_cta,
-                                    const float* __restrict__ small_acc, int D, int L, int Wd, int WP, MutPtrArray dW, MutPtrArray dB) {
+                                    const float* __restrict__ small_acc, int D, int L, int Wd, int WP, MutPtrArray dW, MutPtrArray dB,
+                                    const unsigned int* __restrict__ abort_flag) {
+    const float poison = (abort_flag && *abort_flag) ? __int_as_float(0x7fc00000) : 0.f;
     const long long n_hidden_el = (long long)(L - 1) * Wd * Wd;
     const long long n_rest = (long long)Wd * D + (long long)L * Wd + Wd + 1;
     const size_t cta_stride = (size_t)(L - 1) * WP * WP;
@@ -82,12 +86,12 @@ __global__ void finish_grads_kernel(const float* __restrict__ dWacc, const doubl
             } else {
                 for (int c = 0; c < n_cta; ++c) s += (double)dWacc[at + (size_t)c * cta_stride];
             }
-            dW.p[l + 1][(size_t)o * Wd + i] = (float)s;
+            dW.p[l + 1][(size_t)o * Wd + i] = (float)s + poison;
         } else {
             long long j = idx - n_hidden_el;
             if (j < (long long)Wd * D) {
                 const int c = (int)(j / D), i = (int)(j % D);
-                dW.p[0][j] = small_acc[i * WP + c];
+                dW.p[0][j] = small_acc[i * WP + c] + poison;
             } else if ((j -= (long long)Wd * D) < (long long)L * Wd) {
                 const int l = (int)(j / Wd), c = (int)(j % Wd);
                 dB.p[l][c] = small_acc[(D + l) * WP + c];
@@ -377,6 +381,7 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     MlpParams P{L, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd), reinterpret_cast<float*>(base + w.w_bwd),
                 reinterpret_cast<float*>(base + w.small)};
     const XForm xf = make_xform(xform);
+    const unsigned int* abort_flag = nullptr;
     if (n > 0 && w.tc) {
         PtrArray Wp{};
         for (int l = 0; l <= L; ++l) Wp.p[l] = W[l];
@@ -390,7 +395,7 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
         }
         rc = launch_bwd_tc(desc->d, L, desc->act, wimg_f, wimg_r, P.small, x, n, u_bar, g_bar, h_bar,
                            reinterpret_cast<float*>(base + w.stash), resident, reinterpret_cast<float*>(base + w.zb),
-                           reinterpret_cast<double*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc), s);
+                           reinterpret_cast<double*>(base + w.dWacc), reinterpret_cast<float*>(base + w.small_acc), s, &abort_flag);
         if (rc) return rc;
     } else if (n > 0) {
         if (resident) { set_error("this descriptor has no stash (gpe_stash_bytes = 0): use gpe_mlp_jet_bwd"); return -1; }
@@ -413,7 +418,8 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     const int blocks = (int)((total + 255) / 256);
     finish_grads_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float*>(base + w.dWacc),
                                                w.tc ? reinterpret_cast<double*>(base + w.dWacc) : nullptr,
-                                               n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0, reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp);
+                                               n > 0 ? (w.tc ? 1 : w.grid_bwd) : 0, reinterpret_cast<float*>(base + w.small_acc), desc->d, L, desc->width, wp, dWp, dBp,
+                                               abort_flag);
     return check_launch("finish_grads_kernel");
 }
 

@@ -77,11 +77,16 @@ __host__ __device__ inline DwClass dw_class(int cta, int n_cta, int L, int n1) {
 
 // stash / zb: [layer][block][kBlkFloats]; stash_ls / lstride = floats per layer of the stash / the zbar chunk buffer.  stash[l-1] = st_l, zb[l-1] = zbar_l (l = 1..L-1).
 // small: the packed small parameters (W0t[D][128] | b[L][128] | ...), small_acc: their gradient, same layout.
-template <int D, int ACT = -1>
-__global__ void __launch_bounds__(kDwThreads, 1)
-dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __restrict__ x, long long n, long long stash_ls, long long lstride,
-             const float* __restrict__ stash, const float* __restrict__ zb, double* __restrict__ dWacc, float* __restrict__ small_acc,
-             int num_blocks, int n1_cta, int pf_dist) {
+// RING = false: the blocks of one chunk, zbar from the chunk buffer (dw_tc_kernel).
+// RING = true : all blocks of the launch; zbar of half tile h = 2 T + c comes from ring slot T % ns once the reverse-sweep
+//               CTA that owns it has signalled, and the slot is handed back when its images have landed (bwd_fused_tc_kernel).
+// cta_idx / n_cta: this CTA's index among the dW CTAs of the launch.
+constexpr int kDwFlushGroups = 512;   // RING: register accumulators go to the fp64 accumulator every 2048 blocks (16384 points)
+template <int D, int ACT, bool RING>
+__device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restrict__ small, const float* __restrict__ x, long long n,
+                                        long long stash_ls, long long lstride, const float* __restrict__ stash,
+                                        const float* __restrict__ zb, double* __restrict__ dWacc, float* __restrict__ small_acc,
+                                        int num_blocks, int n1_cta, int pf_dist, int cta_idx, int n_cta, const RingCtl& ring) {
     using tc::tmem_alloc; using tc::tmem_dealloc; using tc::tc_fence_before; using tc::tc_fence_after; using tc::tmem_wait_ld;
     using tc::tmem_wait_st; using tc::smem_desc; using tc::instr_desc; using tc::mma_ts; using tc::mma_commit;
     using tc::fence_async_smem; using tc::tmem_ld_32x32b_x32; using tc::tmem_st_32x32b_x8;
@@ -96,10 +101,10 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
     float* w0s = xbuf + kDwStages * 16;                                                         // W0t[D][128] | b0[128]
     const int act = ACT >= 0 ? ACT : act_rt;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-    const DwClass cls = dw_class((int)blockIdx.x, (int)gridDim.x, L, n1_cta);
+    const DwClass cls = dw_class(cta_idx, n_cta, L, n1_cta);
     const int l = cls.layer;
     if (l == 1)
-        for (int i = tid; i < (D + 1) * 128; i += kDwThreads) w0s[i] = small[i];
+        for (int i = tid; i < (D + 1) * 128; i += (int)blockDim.x) w0s[i] = small[i];
 
     if (tid == 0) {
         for (int s = 0; s < kDwStages; ++s) {
@@ -118,12 +123,35 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
     __syncthreads();
     tc_fence_after();
     const uint32_t tb = *tbase_s;
-    const int items = num_blocks > cls.rank ? (num_blocks - cls.rank + cls.count - 1) / cls.count : 0;   // blocks of this CTA
+    // items of this CTA.  Chunk mode: blocks rank, rank + count, ...  Ring mode: half tiles (4 blocks) rank, rank + count, ...;
+    // only the last half tile of the point set can be partial, and its missing blocks are the trailing ones.
+    int items;
+    if (RING) {
+        const int halves = (num_blocks + 3) / 4;
+        const int mine = halves > cls.rank ? (halves - cls.rank + cls.count - 1) / cls.count : 0;
+        items = 4 * mine;
+        if (mine > 0) {
+            const int last_h = cls.rank + (mine - 1) * cls.count;
+            const int rem = num_blocks - 4 * last_h;
+            items -= 4 - (rem < 4 ? rem : 4);
+        }
+    } else {
+        items = num_blocks > cls.rank ? (num_blocks - cls.rank + cls.count - 1) / cls.count : 0;
+    }
     const int groups = (items + kDwGroup - 1) / kDwGroup;
     const float* zsrc = zb + (size_t)(l - 1) * lstride;
     const float* ssrc = stash + (size_t)(l > 1 ? l - 2 : 0) * stash_ls;
+    auto item_half = [&](int i) -> int { return cls.rank + (i >> 2) * cls.count; };                       // RING: half tile of item i
+    auto item_block = [&](int i) -> long long {                                                            // global block (8 points)
+        return RING ? 4ll * item_half(i) + (i & 3) : (long long)cls.rank + (long long)i * cls.count;
+    };
+    auto zsrc_block = [&](int i) -> long long {                                                            // block inside zb
+        if (!RING) return item_block(i);
+        const int h = item_half(i);
+        return (long long)((h >> 1) % ring.ns) * 8 + (h & 1) * 4 + (i & 3);
+    };
     // block `i` of this CTA: all 8 points exist (then its 8 x D coordinates come by TMA; the one ragged block is read directly)
-    auto blk_first = [&](int i) -> long long { return ((long long)cls.rank + (long long)i * cls.count) * kDwPts; };
+    auto blk_first = [&](int i) -> long long { return item_block(i) * kDwPts; };
     const bool x_aligned = (reinterpret_cast<uintptr_t>(x) & 15) == 0;   // cp.async.bulk needs a 16-byte aligned source
 
     if (w < kDwConvWarps) {
@@ -133,6 +161,16 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
         for (int c = 0; c < 32; ++c) acc[c] = 0.f;
         float bsum = 0.f, bcomp = 0.f;          // bias gradient of feature 32 q + lane over this warp's points, compensated
         // add the finished short accumulator of group g into the register accumulator (round to nearest)
+        // register accumulators -> the global fp64 accumulator (one RED per element): the sum over CTAs, launches and
+        // flushes is exact to fp64, only the partial sums between two flushes are fp32
+        auto flush = [&]() {
+            double* dst = dWacc + ((size_t)(l - 1) * 128 + 32 * q + lane) * 128 + 32 * grp;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                atomicAdd(dst + c, (double)acc[c]);
+                acc[c] = 0.f;
+            }
+        };
         auto drain = [&](int g) {
             const int buf = g & 1;
             mbar_wait(&acc_full[buf], (uint32_t)((g >> 1) & 1));
@@ -146,6 +184,7 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_free[buf]);
+            if (RING && (g + 1) % kDwFlushGroups == 0) flush();
         };
         for (int it = 0; it < items; ++it) {
             const int stg = it % kDwStages;
@@ -154,6 +193,11 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
             unsigned char* AH = ZR + kDwImgBytes;
             unsigned char* AL = AH + kDwImgBytes;
             mbar_wait(&raw_full[stg], par);         // every warp waits: the stage (and its barrier phase) is free only now
+            if (RING && w == 0 && lane == 0 && ((it & 3) == 3 || it + 1 == items)) {
+                // the last image of this half tile has landed in shared memory: hand the ring slot back
+                const int h = item_half(it);
+                red_release_gpu_add(ring.cons + 2 * ((h >> 1) % ring.ns) + (h & 1), 1u);
+            }
             {
                 // ---- zbar^T of feature f, points 2 grp and 2 grp + 1 -> TMEM lane f, columns 8 grp .. 8 grp + 7, hi | lo ----
                 const int f = 32 * q + lane;
@@ -233,61 +277,107 @@ dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __
         // ---- register accumulators -> the global fp64 accumulator (one RED per element and CTA): the sum over the ~50 CTAs
         // of a layer and the 64 launches of a 16M-point step is exact to fp64, only the per-CTA partial sums are fp32 ----
         if (items > 0) {
-            const int o = 32 * q + lane;
-            double* dst = dWacc + ((size_t)(l - 1) * 128 + o) * 128 + 32 * grp;
-#pragma unroll
-            for (int c = 0; c < 32; ++c) atomicAdd(dst + c, (double)acc[c]);
-            atomicAdd(&small_acc[(D + l) * 128 + o], bsum);
+            flush();
+            atomicAdd(&small_acc[(D + l) * 128 + 32 * q + lane], bsum);
         }
     } else if (w == kDwConvWarps) {
         if (lane == 0) {
             // ---- MMA issue thread ----
+            // descriptors of the stage's two operand images are built once (the MMA thread's per-MMA descriptor arithmetic
+            // was the issue bottleneck, scripts/tc_trace.py); +16 per K = 8 step, + one stage = kDwStageBytes / 16
             const uint32_t idesc = instr_desc(2, 128, 128, 0, 0);
-            for (int it = 0; it < items; ++it) {
-                const int stg = it % kDwStages, g = it / kDwGroup, buf = g & 1;
-                const bool first = it % kDwGroup == 0;
-                mbar_wait(&full[stg], (uint32_t)((it / kDwStages) & 1));
-                if (first && g >= 2) mbar_wait(&acc_free[buf], (uint32_t)(((g >> 1) - 1) & 1));
-                tc_fence_after();
-                const uint32_t ah = smem_u32(smem + (size_t)stg * kDwStageBytes + kDwImgBytes), al = ah + kDwImgBytes;
-                const uint32_t zh = tb + kDwColZ + (uint32_t)stg * 64, zl = zh + 32;
+            const uint64_t bah0 = smem_desc(smem_u32(smem + kDwImgBytes), 128, 1024), bal0 = smem_desc(smem_u32(smem + 2 * kDwImgBytes), 128, 1024);
+            static_assert(kDwStages == 4 && kDwGroup == 4, "the issue loop below is unrolled over the four stages of a group");
+            for (int it0 = 0; it0 < items; it0 += kDwStages) {
+                const int g = it0 / kDwGroup, buf = g & 1;
                 const uint32_t dcol = tb + kDwColAcc + (uint32_t)buf * 128;
+                const uint32_t par = (uint32_t)((it0 / kDwStages) & 1);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint64_t bah = smem_desc(ah + j * 256, 128, 1024), bal = smem_desc(al + j * 256, 128, 1024);
-                    mma_ts<0, 1>(dcol, zl + 8 * j, bah, idesc, (first && j == 0) ? 0u : 1u);
-                    mma_ts<0, 1>(dcol, zh + 8 * j, bal, idesc, 1u);
-                    mma_ts<0, 1>(dcol, zh + 8 * j, bah, idesc, 1u);
+                for (int stg = 0; stg < kDwStages; ++stg) {
+                    const int it = it0 + stg;
+                    if (it < items) {
+                        mbar_wait(&full[stg], par);
+                        if (stg == 0 && g >= 2) mbar_wait(&acc_free[buf], (uint32_t)(((g >> 1) - 1) & 1));
+                        tc_fence_after();
+                        const uint32_t zh = tb + kDwColZ + (uint32_t)stg * 64, zl = zh + 32;
+                        const uint64_t bah = bah0 + (uint64_t)(stg * (kDwStageBytes / 16)), bal = bal0 + (uint64_t)(stg * (kDwStageBytes / 16));
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            mma_ts<0, 1>(dcol, zl + 8 * j, bah + (uint64_t)(16 * j), idesc, (stg == 0 && j == 0) ? 0u : 1u);
+                            mma_ts<0, 1>(dcol, zh + 8 * j, bal + (uint64_t)(16 * j), idesc, 1u);
+                            mma_ts<0, 1>(dcol, zh + 8 * j, bah + (uint64_t)(16 * j), idesc, 1u);
+                        }
+                        mma_commit(&empty[stg]);
+                        if (stg == kDwStages - 1 || it + 1 == items) mma_commit(&acc_full[buf]);
+                    }
                 }
-                mma_commit(&empty[stg]);
-                if ((it + 1) % kDwGroup == 0 || it + 1 == items) mma_commit(&acc_full[buf]);
             }
         }
-    } else if (lane == 0) {
+    } else if (w == kDwConvWarps + 1 && lane == 0) {
         // ---- TMA producer: one bulk copy per operand image (optionally an L2 bulk prefetch pf_dist blocks ahead) ----
         auto prefetch = [&](int i) {
-            const size_t off = (size_t)blk_first(i) / kDwPts * kBlkFloats;
-            tc::prefetch_l2_bulk(zsrc + off, kDwImgBytes);
-            if (l != 1) tc::prefetch_l2_bulk(ssrc + off, kDwImgBytes);
+            if (!RING) tc::prefetch_l2_bulk(zsrc + (size_t)zsrc_block(i) * kBlkFloats, kDwImgBytes);
+            if (l != 1) tc::prefetch_l2_bulk(ssrc + (size_t)item_block(i) * kBlkFloats, kDwImgBytes);
         };
         for (int i = 0; i < pf_dist && i < items; ++i) prefetch(i);
         for (int it = 0; it < items; ++it) {
             const int stg = it % kDwStages;
             if (pf_dist > 0 && it + pf_dist < items) prefetch(it + pf_dist);
             if (it >= kDwStages) mbar_wait(&empty[stg], (uint32_t)(((it / kDwStages) - 1) & 1));
+            if (RING && (it & 3) == 0) {
+                // first block of a half tile: wait until all kEpiWarps warps of the reverse CTA that owns it have released
+                // zbar_l of that tile, then order the async-proxy reads below after this generic-proxy acquire
+                const int h = item_half(it), T = h >> 1;
+                ring_wait(ring.prod + (size_t)(l - 1) * 2 * ring.nrc + 2 * (T % ring.nrc) + (h & 1),
+                          (unsigned int)(kEpiWarps * (T / ring.nrc + 1)), ring.abort);
+                asm volatile("fence.proxy.async.global;" ::: "memory");
+            }
             unsigned char* ZR = smem + (size_t)stg * kDwStageBytes;
             const long long p0 = blk_first(it);
-            const size_t off = (size_t)p0 / kDwPts * kBlkFloats;
             const bool xtma = l == 1 && x_aligned && p0 + kDwPts <= n;
             mbar_arrive_expect_tx(&raw_full[stg], (l != 1 ? 2 * kDwImgBytes : kDwImgBytes) + (xtma ? kDwPts * D * 4u : 0u));
-            tma_bulk_g2s(ZR, zsrc + off, kDwImgBytes, &raw_full[stg]);
-            if (l != 1) tma_bulk_g2s(ZR + kDwImgBytes, ssrc + off, kDwImgBytes, &raw_full[stg]);
+            tma_bulk_g2s(ZR, zsrc + (size_t)zsrc_block(it) * kBlkFloats, kDwImgBytes, &raw_full[stg]);
+            if (l != 1) tma_bulk_g2s(ZR + kDwImgBytes, ssrc + (size_t)item_block(it) * kBlkFloats, kDwImgBytes, &raw_full[stg]);
             else if (xtma) tma_bulk_g2s(xbuf + stg * 16, x + p0 * D, kDwPts * D * 4u, &raw_full[stg]);
         }
     }
     tc_fence_before();
     __syncthreads();
     if (w == kDwConvWarps) tmem_dealloc<1>(tb, 512);
+}
+
+template <int D, int ACT = -1>
+__global__ void __launch_bounds__(kDwThreads, 1)
+dw_tc_kernel(int L, int act_rt, const float* __restrict__ small, const float* __restrict__ x, long long n, long long stash_ls, long long lstride,
+             const float* __restrict__ stash, const float* __restrict__ zb, double* __restrict__ dWacc, float* __restrict__ small_acc,
+             int num_blocks, int n1_cta, int pf_dist) {
+    dw_role<D, ACT, false>(L, act_rt, small, x, n, stash_ls, lstride, stash, zb, dWacc, small_acc, num_blocks, n1_cta, pf_dist, (int)blockIdx.x,
+                           (int)gridDim.x, RingCtl{});
+}
+
+// ------------------------------------------------------------------------------------------
+// Fused backward: one persistent launch over ALL points.  Clusters [0, nrc) are reverse-sweep CTA pairs (cta_group::2),
+// every CTA of the remaining clusters runs the dW contraction of one hidden matrix on its own (cta_group::1; one kernel
+// holding both group sizes was checked with scripts/tc_probe, test 5).  The grid never exceeds one CTA per SM, so all
+// CTAs are co-resident and the counters of RingCtl cannot deadlock: the lowest unconsumed tile is always producible.
+// Needs the resident stash of all points (the forward wrote it).  HBM traffic: the stash is read once by the sweep and
+// (layers >= 2) once by dW; zbar stays in L2.
+// ------------------------------------------------------------------------------------------
+constexpr int kFusedThreads = kDwThreads > kTcThreads ? kDwThreads : kTcThreads;
+template <int D, int ACT = -1, bool TWO = true>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFusedThreads, 1)
+bwd_fused_tc_kernel(TcParams Pr, const float* __restrict__ x, long long n, const float* __restrict__ u_bar,
+                    const float* __restrict__ g_bar, const float* __restrict__ h_bar, const float* __restrict__ stash,
+                    float* __restrict__ zb, double* __restrict__ dWacc, float* __restrict__ small_acc, long long stash_ls, int nblk8,
+                    int num_pairs, int pf_dist, int n1_cta, RingCtl ring) {
+    const int cluster_id = (int)(blockIdx.x >> 1);
+    if (cluster_id < ring.nrc) {
+        if (TWO) rev2_role<D, ACT, true>(Pr, x, n, u_bar, g_bar, h_bar, stash, zb, small_acc, stash_ls, nblk8, num_pairs, cluster_id, ring.nrc, ring);
+        else rev_role<D, ACT, true>(Pr, x, n, u_bar, g_bar, h_bar, stash, zb, small_acc, stash_ls, nblk8, num_pairs, pf_dist, cluster_id, ring.nrc, ring);
+    } else {
+        dw_role<D, ACT, true>(Pr.n_hidden, Pr.act, Pr.small, x, n, stash_ls, (long long)ring.ns * 8 * kBlkFloats, stash, zb, dWacc, small_acc, nblk8,
+                              n1_cta, 0, (int)blockIdx.x - 2 * ring.nrc, (int)gridDim.x - 2 * ring.nrc, ring);
+    }
 }
 
 }  // namespace tcp

@@ -53,16 +53,30 @@ static int ensure_smem(K kernel, size_t smem, const char* what) {
     return 0;
 }
 
+// Two tiles in flight per CTA pair (A/B knobs, read per call).  Forward: default on (GPE_TC_TWO_TILES=0 selects the
+// one-tile kernel) -- measured on B200 at 4M points: forward 8.7 -> 8.0 ms, stash forward 10.6 -> 9.7 ms.  Reverse sweep:
+// default off (GPE_TC_TWO_TILES_REV=1 selects it) -- 13.2 -> 13.9 ms: its epilogue, not the MMA chain, is what bounds it.
+static bool tc_two_tiles() {
+    const char* ev = getenv("GPE_TC_TWO_TILES");
+    return !(ev && ev[0] == '0');
+}
+static bool tc_two_tiles_rev() {
+    const char* ev = getenv("GPE_TC_TWO_TILES_REV");
+    return ev && ev[0] == '1';
+}
+
 template <int D, bool STASH, int ACT>
 static int fwd_tc_act(const tcp::TcParams& P, const float* x, long long n, float* u, float* g, float* h, float* stash, cudaStream_t s) {
     const int sms = tc_sms();
     const size_t smem = tcp::tc_smem_bytes(D, P.n_hidden);
-    if (int rc = ensure_smem(tcp::jet_fwd_tc_kernel<D, STASH, ACT>, tcp::tc_smem_bytes(D, tcp::kTcMaxMat + 1), "jet_fwd_tc_kernel")) return rc;
+    const bool two = tc_two_tiles();
+    auto kern = two ? tcp::jet_fwd2_tc_kernel<D, STASH, ACT> : tcp::jet_fwd_tc_kernel<D, STASH, ACT>;
+    if (int rc = ensure_smem(kern, tcp::tc_smem_bytes(D, tcp::kTcMaxMat + 1), "jet_fwd_tc_kernel")) return rc;
     cudaError_t e;
     const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
     long long clusters = sms / 2;
     if (pairs < clusters) clusters = pairs;
-    tcp::jet_fwd_tc_kernel<D, STASH, ACT><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (long long)((n + 7) / 8) * tcp::kBlkFloats, STASH ? (int)((n + 7) / 8) : 0, (int)pairs);
+    kern<<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(P, x, n, u, g, h, stash, (long long)((n + 7) / 8) * tcp::kBlkFloats, STASH ? (int)((n + 7) / 8) : 0, (int)pairs);
     e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("jet_fwd_tc_kernel launch: %s (grid %lld, smem %zu)", cudaGetErrorString(e), 2 * clusters, smem); return -4; }
     return 0;
@@ -126,7 +140,7 @@ static int tc_interleave() {
 // reverse sweep: GPE_TC_INTERLEAVE = 0 | 1, default 0 (a non-zero value also sets the forward's unless that is given).
 static int tc_env_mode(const char* name, int dflt) {
     const char* ev = getenv(name);
-    return (ev && ev[0] >= '0' && ev[0] <= '1') ? ev[0] - '0' : dflt;
+    return (ev && ev[0] >= '0' && ev[0] <= '2') ? ev[0] - '0' : dflt;
 }
 static int tc_interleave_fwd() {
     static int v = -1;
@@ -136,16 +150,69 @@ static int tc_interleave_fwd() {
 
 template <int D, int ACT>
 static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
-                  const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
+                  const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s,
+                  const unsigned int** abort_flag) {
     const int sms = tc_sms(), L = Pf.n_hidden;
     const size_t smem = tcp::tc_smem_bytes(D, L), smem_dw = tcp::dw_smem_bytes();
     const size_t smem_max = tcp::tc_smem_bytes(D, tcp::kTcMaxMat + 1);
-    if (int rc = ensure_smem(tcp::jet_fwd_tc_kernel<D, true, ACT>, smem_max, "jet_fwd_tc_kernel")) return rc;
-    if (int rc = ensure_smem(tcp::jet_rev_tc_kernel<D, ACT>, smem_max, "jet_rev_tc_kernel")) return rc;
+    auto fwd_kern = tc_two_tiles() ? tcp::jet_fwd2_tc_kernel<D, true, ACT> : tcp::jet_fwd_tc_kernel<D, true, ACT>;
+    if (int rc = ensure_smem(fwd_kern, smem_max, "jet_fwd_tc_kernel")) return rc;
+    auto rev_kern = tc_two_tiles_rev() ? tcp::jet_rev2_tc_kernel<D, ACT> : tcp::jet_rev_tc_kernel<D, ACT>;
+    if (int rc = ensure_smem(rev_kern, smem_max, "jet_rev_tc_kernel")) return rc;
     if (int rc = ensure_smem(tcp::dw_tc_kernel<D, ACT>, smem_dw, "dw_tc_kernel")) return rc;
     cudaError_t e;
     static int rev_pf = -1;   // GPE_REV_PF: L2 prefetch distance of the reverse sweep, in (tile, layer) steps
     if (rev_pf < 0) { const char* ev = getenv("GPE_REV_PF"); rev_pf = ev ? atoi(ev) : 1; if (rev_pf < 1) rev_pf = 1; }
+    // ---- fused backward: one persistent launch, zbar handed from the sweep to dW through an L2-resident ring ----
+    // GPE_BWD_FUSED=0 keeps the per-chunk kernels; GPE_FUSED_NRC = reverse-sweep clusters (of sms/2), GPE_RING_TILES = ring
+    // slots of 64 points.  Needs the resident stash and enough points to fill the machine.
+    // (read per call, so a test can switch between the two backward schemes inside one process)
+    int fused_env = 1, nrc_env = 0, ring_env = 0;
+    {
+        const char* ev = getenv("GPE_BWD_FUSED"); fused_env = (ev && ev[0] == '1') ? 1 : 0;
+        ev = getenv("GPE_FUSED_NRC"); nrc_env = ev ? atoi(ev) : 0;
+        ev = getenv("GPE_RING_TILES"); ring_env = ev ? atoi(ev) : 0;
+    }
+    if (abort_flag) *abort_flag = nullptr;
+    const int total_clusters = sms / 2;
+    if (resident && fused_env && n >= 65536 && total_clusters >= 8) {
+        const size_t smem_f = smem > smem_dw ? smem : smem_dw;
+        const size_t smem_fmax = smem_max > smem_dw ? smem_max : smem_dw;
+        const bool two_rev = tc_two_tiles_rev();
+        auto fused_kern = two_rev ? tcp::bwd_fused_tc_kernel<D, ACT, true> : tcp::bwd_fused_tc_kernel<D, ACT, false>;
+        if (int rc = ensure_smem(fused_kern, smem_fmax, "bwd_fused_tc_kernel")) return rc;
+        // reverse sweep : dW contraction ~ 5 : 3 in SM time when run one after the other; the sweep keeps two thirds
+        int nrc = nrc_env > 0 ? nrc_env : (total_clusters * 4 + 3) / 7;
+        if (nrc > total_clusters - (L - 1 + 1) / 2) nrc = total_clusters - (L - 1 + 1) / 2;   // at least L-1 dW CTAs
+        if (nrc < 1) nrc = 1;
+        const long long pairs = (n + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
+        int ns = ring_env > 0 ? ring_env : (two_rev ? 160 : 96);
+        if (ns < (two_rev ? 2 : 1) * nrc + 16) ns = (two_rev ? 2 : 1) * nrc + 16;   // every sweep pair holds one (two) slot(s) at a time
+        const long long cap_tiles = chunk / (2 * tcp::kTcPts);
+        // the ring lives in the zbar chunk buffer; the counters sit behind it
+        const size_t n_ctr = (size_t)(L - 1) * 2 * nrc + 2 * (size_t)ns + 4;
+        const size_t ring_floats = (size_t)(L - 1) * ns * 8 * tcp::kBlkFloats;
+        if (ns < cap_tiles && ring_floats * 4 + n_ctr * 4 <= tc_zb_bytes(L, n)) {
+            unsigned int* ctr = reinterpret_cast<unsigned int*>(zb + ring_floats);
+            e = cudaMemsetAsync(ctr, 0, n_ctr * 4, s);
+            if (e != cudaSuccess) { set_error("fused backward: memset: %s", cudaGetErrorString(e)); return -4; }
+            tcp::RingCtl ring{ns, nrc, ctr, ctr + (size_t)(L - 1) * 2 * nrc, ctr + (size_t)(L - 1) * 2 * nrc + 2 * (size_t)ns};
+            const int nblk8 = (int)((n + tcp::kDwPts - 1) / tcp::kDwPts);
+            const long long stash_ls = (long long)nblk8 * tcp::kBlkFloats;
+            const int n_dw = 2 * (total_clusters - nrc);
+            static int n1_env = -1;
+            if (n1_env < 0) { const char* ev = getenv("GPE_DW_N1"); n1_env = ev ? atoi(ev) : 0; }
+            {
+                TcScope t(3, s);
+                fused_kern<<<(unsigned)(2 * total_clusters), tcp::kFusedThreads, smem_f, s>>>(
+                    Pr, x, n, ub, gb, hb, resident, zb, dWacc, small_acc, stash_ls, nblk8, (int)pairs, rev_pf, n1_env > 0 ? n1_env : n_dw / (L - 1), ring);
+            }
+            e = cudaGetLastError();
+            if (e != cudaSuccess) { set_error("fused backward launch: %s", cudaGetErrorString(e)); return -4; }
+            if (abort_flag) *abort_flag = ring.abort;
+            return 0;
+        }
+    }
     for (long long c0 = 0; c0 < n; c0 += chunk) {
         const long long nc = n - c0 < chunk ? n - c0 : chunk;
         const long long pairs = (nc + 2 * tcp::kTcPts - 1) / (2 * tcp::kTcPts);
@@ -159,11 +226,11 @@ static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const fl
         const float* st = resident ? resident + (size_t)(c0 / tcp::kDwPts) * tcp::kBlkFloats : stash;
         if (!resident) {
             TcScope t(0, s);
-            tcp::jet_fwd_tc_kernel<D, true, ACT><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, stash_ls, nblk8, (int)pairs);
+            fwd_kern<<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(Pf, xc, nc, nullptr, nullptr, nullptr, stash, stash_ls, nblk8, (int)pairs);
         }
         {
             TcScope t(1, s);
-            tcp::jet_rev_tc_kernel<D, ACT><<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
+            rev_kern<<<(unsigned)(2 * clusters), tcp::kTcThreads, smem, s>>>(
                 Pr, xc, nc, ub ? ub + c0 : nullptr, gb ? gb + c0 * D : nullptr, hb ? hb + c0 : nullptr, st, zb, small_acc, stash_ls, nblk8, (int)pairs, rev_pf);
         }
         const long long blocks = nblk8;
@@ -187,9 +254,10 @@ static int bwd_tc_act(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const fl
 
 template <int D>
 static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float* x, long long n, const float* ub, const float* gb,
-                  const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s) {
-    return (Pf.act == ACT_TANH && !tc_act_generic()) ? bwd_tc_act<D, ACT_TANH>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s)
-                              : bwd_tc_act<D, -1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s);
+                  const float* hb, float* stash, const float* resident, float* zb, double* dWacc, float* small_acc, long long chunk, cudaStream_t s,
+                  const unsigned int** abort_flag) {
+    return (Pf.act == ACT_TANH && !tc_act_generic()) ? bwd_tc_act<D, ACT_TANH>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag)
+                              : bwd_tc_act<D, -1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag);
 }
 
 // chunk of points processed per (stash forward, reverse sweep, dW contraction) round
@@ -204,11 +272,11 @@ size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd
 
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, const float* resident, float* zb,
-                  double* dWacc, float* small_acc, cudaStream_t s) {
+                  double* dWacc, float* small_acc, cudaStream_t s, const unsigned int** abort_flag) {
     tcp::TcParams Pf{L, act, wimg_fwd, small, tc_interleave_fwd()}, Pr{L, act, wimg_rev, small, tc_interleave()};
     const long long chunk = tc_bwd_chunk(n);
-    return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s)
-                  : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s);
+    return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag)
+                  : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag);
 }
 
 // bytes of a resident stash of ALL n points: st_l image blocks of the hidden matrices l = 1..L-1
@@ -222,3 +290,9 @@ int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, 
 }
 
 }  // namespace gpe
+
+#ifdef GPE_TC_TRACE
+extern "C" int gpe_debug_trace(long long* out, int n) {
+    return (int)cudaMemcpyFromSymbol(out, gpe::tcp::g_tc_trace, sizeof(long long) * (n < 4096 ? n : 4096));
+}
+#endif

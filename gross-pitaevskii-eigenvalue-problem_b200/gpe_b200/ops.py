@@ -146,9 +146,10 @@ def tc_profile(enable: bool) -> None:
 
 
 def tc_timings():
-    """Accumulated milliseconds {stash_forward, reverse_sweep, dw_contraction} since the last call (synchronises)."""
+    """Accumulated milliseconds {stash_forward, reverse_sweep, dw_contraction, fused_backward} since the last call
+    (synchronises).  `fused_backward` is the single persistent launch that runs sweep and contraction side by side."""
     import ctypes
     from . import _lib
-    ms = (ctypes.c_double * 3)()
-    _lib.check(_lib.lib.gpe_tc_timings(ms, 3), "gpe_tc_timings")
-    return {"stash_forward": ms[0], "reverse_sweep": ms[1], "dw_contraction": ms[2]}
+    ms = (ctypes.c_double * 4)()
+    _lib.check(_lib.lib.gpe_tc_timings(ms, 4), "gpe_tc_timings")
+    return {"stash_forward": ms[0], "reverse_sweep": ms[1], "dw_contraction": ms[2], "fused_backward": ms[3]}

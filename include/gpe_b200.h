@@ -155,7 +155,7 @@ int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, cons
  * (north_star: tensor cores "only if TF32/BF16-split accuracy holds", otherwise register-blocked FFMA).
  * gpe_set_tensor_path returns the previous setting.  gpe_tc_profile(1) brackets every tensor-path backward
  * kernel with CUDA events on the launch stream; gpe_tc_timings() synchronises those events, returns the
- * accumulated milliseconds {stash forward, reverse sweep, dW contraction} in ms[0..n) and clears the record. */
+ * accumulated milliseconds {stash forward, reverse sweep, dW contraction, fused backward} in ms[0..n) and clears the record. */
 int gpe_set_tensor_path(int enable);
 int gpe_tc_profile(int enable);
 int gpe_tc_timings(double* ms, int n);

@@ -157,6 +157,60 @@ __global__ void __launch_bounds__(128) gemm_probe(const float* A0, const float* 
     if (w == 0) tmem_dealloc<CG>(tb, 512);
 }
 
+// ------------------------------------------------------------------------------------------ T5
+// One launch, clusters of 2: cluster 0 runs a cta_group::2 MMA (M = 256), the two CTAs of cluster 1 each run their own
+// cta_group::1 MMA (M = 128).  Question: may one kernel hold both cta_group values (role-specialised CTAs)?
+template <int CG>
+__device__ void mix_body(const float* A, const float* B, float* D, uint32_t cta, unsigned char* smem, uint32_t* tbase_s, uint64_t* bar) {
+    constexpr int K = 128, N = 128, NB = N / CG;
+    const int tid = threadIdx.x, w = tid / 32;
+    if (tid == 0) { mbar_init(bar, 1); mbar_fence_init(); }
+    if (w == 0) tmem_alloc<CG>(tbase_s, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = *tbase_s;
+    const float* a = A + (size_t)cta * 128 * K + (size_t)tid * K;
+    for (int c0 = 0; c0 < K; c0 += 8) {
+        uint32_t v[8];
+        for (int c = 0; c < 8; ++c) v[c] = __float_as_uint(a[c0 + c]);
+        tmem_st_32x32b_x8(tb + ((uint32_t)(32 * w) << 16) + 256 + c0, v);
+    }
+    tmem_wait_st();
+    load_img(smem, B + (size_t)cta * NB * K, NB, K, K, tid);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (CG == 2) cluster_sync();
+    tc_fence_after();
+    if (tid == 0 && cta == 0) {
+        constexpr uint32_t idesc = instr_desc(2, 128 * CG, N, 0, 0);
+        for (int j = 0; j < K / 8; ++j)
+            mma_ts<0, CG>(tb, tb + 256 + 8 * j, smem_desc(smem_u32(smem) + j * 256, 128, (K / 4) * 128), idesc, j ? 1u : 0u);
+        if (CG == 2) mma_commit_pair(bar, 3); else mma_commit(bar);
+    }
+    mbar_wait(bar, 0);
+    tc_fence_after();
+    for (int c0 = 0; c0 < N; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tb + ((uint32_t)(32 * w) << 16) + c0, r);
+        tmem_wait_ld();
+        for (int c = 0; c < 32; ++c) D[((size_t)cta * 128 + tid) * N + c0 + c] = __uint_as_float(r[c]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (CG == 2) cluster_sync();
+    if (w == 0) tmem_dealloc<CG>(tb, 512);
+}
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128) mix_probe(const float* A, const float* B, float* D) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ uint32_t tbase_s;
+    __shared__ __align__(8) uint64_t bar;
+    const uint32_t cl = blockIdx.x >> 1, rank = cluster_ctarank();
+    if (cl == 0) mix_body<2>(A, B, D, rank, smem, &tbase_s, &bar);                                  // rows 0..255 of D
+    else mix_body<1>(A + (size_t)(2 + rank) * 128 * 128 - 0, B, D + (size_t)(2 + rank) * 128 * 128, 0u, smem, &tbase_s, &bar);   // rows 256.. / 384..
+}
+
 // ------------------------------------------------------------------------------------------ T3
 template <int CG, bool A_TMEM, int N, int KIND>
 __global__ void __launch_bounds__(128) rate_probe(long long* cycles, int reps) {
@@ -362,5 +416,29 @@ int main(int argc, char** argv) {
         ++idx;
     }
     if (which == 4) { if (sub == 1) run_diag<1>(); else run_diag<2>(); }
+    if (which == 5) {
+        const int M = 512, K = 128, N = 128;
+        std::vector<float> a(M * K), b(N * K);
+        for (auto& v : a) v = tf32_rn(frand());
+        for (auto& v : b) v = tf32_rn(frand());
+        float *dA, *dB, *dD;
+        CK(cudaMalloc(&dA, M * K * 4)); CK(cudaMalloc(&dB, N * K * 4)); CK(cudaMalloc(&dD, M * N * 4));
+        CK(cudaMemcpy(dA, a.data(), M * K * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dB, b.data(), N * K * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemset(dD, 0xFF, M * N * 4));
+        CK(cudaFuncSetAttribute(mix_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 128 * 4));
+        mix_probe<<<4, 128, 128 * 128 * 4>>>(dA, dB, dD);
+        CK(cudaDeviceSynchronize());
+        std::vector<float> d(M * N);
+        CK(cudaMemcpy(d.data(), dD, M * N * 4, cudaMemcpyDeviceToHost));
+        for (int blk = 0; blk < 4; ++blk) {
+            double emax = 0;
+            for (int m = blk * 128; m < blk * 128 + 128; ++m) for (int n = 0; n < N; ++n) {
+                double se = 0;
+                for (int k = 0; k < K; ++k) se += (double)a[m * K + k] * b[n * K + k];
+                emax = fmax(emax, fabs(d[m * N + n] - se));
+            }
+            printf("T5 mixed cta_group kernel: rows %3d..%3d (%s) max err %.3e\n", blk * 128, blk * 128 + 127, blk < 2 ? "cta_group::2 pair" : "cta_group::1 CTA", emax);
+        }
+    }
     return 0;
 }
