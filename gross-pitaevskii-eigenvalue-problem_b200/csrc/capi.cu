@@ -8,6 +8,7 @@
 
 #include "../../include/gpe_b200.h"
 #include "jet_host.h"
+#include "tc_wimg.cuh"
 
 namespace gpe {
 
@@ -26,13 +27,20 @@ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
 // ---------------------------------------------------------------- weight packing
 // wt_fwd[l][k=in][n=out] and w_bwd[l][k=out][n=in], zero-padded to WP; small = W0t | b | wout | bout
+// One launch per call packs everything a call needs (a call used to cost up to three pack launches and a memset, which
+// is what a 10k-point step is made of): the FFMA matrices, the small parameters, and -- tensor path -- the hi/lo weight
+// images of the forward (wimg_f) and / or the reverse sweep (wimg_r: transposed), and it zeroes the accumulators.
 __global__ void pack_weights_kernel(PtrArray W, PtrArray B, int D, int L, int Wd, int WP, float* __restrict__ wt_fwd,
-                                    float* __restrict__ w_bwd, float* __restrict__ small, float* __restrict__ small_acc) {
+                                    float* __restrict__ w_bwd, float* __restrict__ small, float* __restrict__ small_acc,
+                                    float* __restrict__ wimg_f, float* __restrict__ wimg_r, double* __restrict__ acc64, long long n_acc64) {
     const long long n_mat = (long long)(L - 1) * WP * WP;
     const int n_small = (D + L + 1) * WP + 4;
     const long long total = n_mat + n_small;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-         idx += (long long)gridDim.x * blockDim.x) {
+    const long long stride = (long long)gridDim.x * blockDim.x, tid0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (wimg_f) tcp::pack_wimg_elems(W, L, Wd, 0, wimg_f, tid0, stride);
+    if (wimg_r) tcp::pack_wimg_elems(W, L, Wd, 1, wimg_r, tid0, stride);
+    for (long long i = tid0; i < n_acc64; i += stride) acc64[i] = 0.0;
+    for (long long idx = tid0; idx < total; idx += stride) {
         if (idx < n_mat) {
             const int l = (int)(idx / ((long long)WP * WP));
             const int rem = (int)(idx % ((long long)WP * WP));
@@ -129,6 +137,12 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
         return -1;
     }
     if (desc->jet < 0 || desc->jet > 3) { set_error("unknown jet kind %d", desc->jet); return -1; }
+    if (desc->precision < GPE_PREC_FP32 || desc->precision > GPE_PREC_AUTO) { set_error("unknown precision %d", desc->precision); return -1; }
+    if (desc->precision == GPE_PREC_TF32X3 && !(desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden))) {
+        set_error("GPE_PREC_TF32X3: no tcgen05 kernel for d=%d width=%d n_hidden=%d jet=%d act=%d (64 < width <= 128, 2..4 hidden layers, "
+                  "Laplacian-type jets); use GPE_PREC_AUTO or GPE_PREC_FP32", desc->d, desc->width, desc->n_hidden, desc->jet, desc->act);
+        return -1;
+    }
     const int wp = padded_width(desc->width);
     if (desc->width < 1 || !wp) { set_error("hidden width %d unsupported (1..256)", desc->width); return -1; }
     int dev = -1;
@@ -162,6 +176,18 @@ bool tc_enabled() {
     return g_tc_enabled != 0;
 }
 
+// Which kernels serve a descriptor: gpe_mlp_desc.precision decides PER CALL -- GPE_PREC_FP32: the FFMA kernels;
+// GPE_PREC_TF32X3: the tcgen05 kernels (get_plan rejects shapes they do not cover); GPE_PREC_AUTO: tcgen05 where a kernel
+// exists, unless the process default (GPE_TENSOR=0 / gpe_set_tensor_path(0)) says FFMA.
+bool tc_shape_ok(const gpe_mlp_desc* desc) {
+    return desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
+}
+bool use_tensor_path(const gpe_mlp_desc* desc) {
+    if (desc->precision == GPE_PREC_FP32) return false;
+    if (desc->precision == GPE_PREC_TF32X3) return tc_shape_ok(desc);
+    return tc_enabled() && tc_shape_ok(desc);
+}
+
 struct WsLayout {
     size_t wt_fwd, w_bwd, small, wimg, small_acc, dWacc, stash, wimg_rev, zb, total_fwd, total_bwd;
     bool tc;
@@ -183,7 +209,7 @@ WsLayout layout(const gpe_mlp_desc* desc, const JetPlan& p, int wp, long long n)
     w.wt_fwd = off; off = align_up(off + mat);
     w.w_bwd = off; off = align_up(off + mat);
     w.small = off; off = align_up(off + w.n_small * sizeof(float));
-    w.tc = tc_enabled() && desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, L);
+    w.tc = use_tensor_path(desc);
     w.wimg = off;
     if (w.tc) off = align_up(off + tc_wimg_bytes(L));
     w.total_fwd = off;
@@ -209,7 +235,7 @@ int check_launch(const char* what) {
 }
 
 int pack(const gpe_mlp_desc* desc, int wp, const WsLayout& w, const float* const* W, const float* const* b, char* ws,
-         bool with_acc, cudaStream_t s) {
+         bool with_acc, cudaStream_t s, bool img_fwd = false, bool img_rev = false, bool zero_acc64 = false) {
     PtrArray Wp{}, Bp{};
     for (int l = 0; l <= desc->n_hidden; ++l) {
         if (!W[l] || !b[l]) { set_error("null weight/bias pointer at layer %d", l); return -1; }
@@ -218,10 +244,14 @@ int pack(const gpe_mlp_desc* desc, int wp, const WsLayout& w, const float* const
     }
     const long long total = (long long)(desc->n_hidden - 1) * wp * wp + w.n_small;
     const int blocks = (int)((total + 255) / 256 < 592 ? (total + 255) / 256 : 592);
+    const long long n_acc64 = zero_acc64 ? (long long)(desc->n_hidden - 1) * wp * wp : 0;
     pack_weights_kernel<<<blocks, 256, 0, s>>>(Wp, Bp, desc->d, desc->n_hidden, desc->width, wp,
                                                reinterpret_cast<float*>(ws + w.wt_fwd), reinterpret_cast<float*>(ws + w.w_bwd),
                                                reinterpret_cast<float*>(ws + w.small),
-                                               with_acc ? reinterpret_cast<float*>(ws + w.small_acc) : nullptr);
+                                               with_acc ? reinterpret_cast<float*>(ws + w.small_acc) : nullptr,
+                                               img_fwd ? reinterpret_cast<float*>(ws + w.wimg) : nullptr,
+                                               img_rev ? reinterpret_cast<float*>(ws + w.wimg_rev) : nullptr,
+                                               zero_acc64 ? reinterpret_cast<double*>(ws + w.dWacc) : nullptr, n_acc64);
     return check_launch("pack_weights_kernel");
 }
 
@@ -310,15 +340,13 @@ static int jet_fwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     if (ws_bytes < w.total_fwd) { set_error("workspace too small: %zu < %zu", ws_bytes, w.total_fwd); return -1; }
     char* base = static_cast<char*>(ws);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    if ((rc = pack(desc, wp, w, W, b, base, false, s))) return rc;
+    NvtxRange range(w.tc ? "gpe:jet_fwd(tensor)" : "gpe:jet_fwd(ffma)");
+    if ((rc = pack(desc, wp, w, W, b, base, false, s, w.tc, false, false))) return rc;
     MlpParams P{desc->n_hidden, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd),
                 reinterpret_cast<float*>(base + w.w_bwd), reinterpret_cast<float*>(base + w.small)};
     const XForm xf = make_xform(xform);
     if (w.tc) {
-        PtrArray Wp{};
-        for (int l = 0; l <= desc->n_hidden; ++l) Wp.p[l] = W[l];
         float* wimg = reinterpret_cast<float*>(base + w.wimg);
-        if ((rc = tc_pack_wimg(Wp, desc->n_hidden, desc->width, 0, wimg, s))) return rc;
         if (resident && resident_bytes < tc_resident_stash_bytes(desc->n_hidden, n)) {
             set_error("stash too small: %zu < %zu", resident_bytes, tc_resident_stash_bytes(desc->n_hidden, n));
             return -1;
@@ -345,8 +373,7 @@ int gpe_stash_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* bytes) {
     const int rc = get_plan(desc, &p, &wp);
     if (rc) return rc;
     if (n < 0 || !bytes) { set_error("gpe_stash_bytes: bad arguments"); return -1; }
-    const bool tc = tc_enabled() && desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
-    *bytes = (tc && n > 0) ? tc_resident_stash_bytes(desc->n_hidden, n) : 0;
+    *bytes = (use_tensor_path(desc) && n > 0) ? tc_resident_stash_bytes(desc->n_hidden, n) : 0;
     return 0;
 }
 
@@ -371,11 +398,12 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     if (ws_bytes < w.total_bwd) { set_error("workspace too small: %zu < %zu", ws_bytes, w.total_bwd); return -1; }
     char* base = static_cast<char*>(ws);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    if ((rc = pack(desc, wp, w, W, b, base, true, s))) return rc;
+    NvtxRange range(w.tc ? "gpe:jet_bwd(tensor)" : "gpe:jet_bwd(ffma)");
+    if ((rc = pack(desc, wp, w, W, b, base, true, s, w.tc && n > 0, w.tc && n > 0, w.tc))) return rc;
     const int L = desc->n_hidden;
     const size_t mat = (size_t)(L - 1) * wp * wp * sizeof(float);
-    if (mat) {
-        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (w.tc ? (size_t)2 : (size_t)w.grid_bwd) * mat, s);
+    if (mat && !w.tc) {   // FFMA path: per-CTA fp32 accumulators (the tensor path's fp64 accumulator is zeroed by the pack launch)
+        const cudaError_t e = cudaMemsetAsync(base + w.dWacc, 0, (size_t)w.grid_bwd * mat, s);
         if (e != cudaSuccess) { set_error("memset: %s", cudaGetErrorString(e)); return -4; }
     }
     MlpParams P{L, desc->width, desc->act, reinterpret_cast<float*>(base + w.wt_fwd), reinterpret_cast<float*>(base + w.w_bwd),
@@ -383,12 +411,8 @@ static int jet_bwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     const XForm xf = make_xform(xform);
     const unsigned int* abort_flag = nullptr;
     if (n > 0 && w.tc) {
-        PtrArray Wp{};
-        for (int l = 0; l <= L; ++l) Wp.p[l] = W[l];
         float* wimg_f = reinterpret_cast<float*>(base + w.wimg);
         float* wimg_r = reinterpret_cast<float*>(base + w.wimg_rev);
-        if ((rc = tc_pack_wimg(Wp, L, desc->width, 0, wimg_f, s))) return rc;
-        if ((rc = tc_pack_wimg(Wp, L, desc->width, 1, wimg_r, s))) return rc;
         if (resident && resident_bytes < tc_resident_stash_bytes(L, n)) {
             set_error("stash too small: %zu < %zu", resident_bytes, tc_resident_stash_bytes(L, n));
             return -1;

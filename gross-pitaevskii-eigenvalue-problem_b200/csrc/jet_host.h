@@ -1,8 +1,10 @@
 // Host-side declarations shared by the per-width launch units and the C ABI.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stddef.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "jet_common.cuh"
 
 namespace gpe {
@@ -36,6 +38,20 @@ GPE_DECL_WP(256)
 #undef GPE_DECL_WP
 
 void set_error(const char* fmt, ...);
+
+// NVTX ranges around the C-ABI calls (GPE_NVTX=1): fwd-jet / moments / adjoints / reverse show up as named ranges in an
+// nsys or ncu timeline.  Header-only NVTX3; one getenv per process.
+struct NvtxRange {
+    bool on;
+    explicit NvtxRange(const char* name) : on(enabled()) { if (on) nvtxRangePushA(name); }
+    ~NvtxRange() { if (on) nvtxRangePop(); }
+    static bool enabled() {
+        static int v = -1;
+        if (v < 0) { const char* e = getenv("GPE_NVTX"); v = (e && e[0] == '1') ? 1 : 0; }
+        return v == 1;
+    }
+};
+
 
 // tensor-core (tcgen05) path, jet_launch_tc.cu
 bool tc_eligible(int d, int jet, int width, int L);

@@ -24,6 +24,7 @@
 #pragma once
 #include "jet_common.cuh"
 #include "tc_tmem.cuh"
+#include "tc_wimg.cuh"
 
 namespace gpe {
 namespace tcp {
@@ -37,7 +38,6 @@ constexpr int kTcThreads = (kEpiWarps + 1) * 32;   // + MMA / control warp
 constexpr int kTcPts = 32;                         // points per CTA tile
 constexpr int kTcMaxMat = 3;                       // resident hidden matrices (64 KB each per CTA)
 constexpr uint32_t kColAHi = 0, kColALo = 128, kColD0 = 256;
-constexpr int kImgFloats = 64 * 128;               // one half-matrix image (hi or lo)
 
 struct TcParams {
     int n_hidden;          // L
@@ -60,17 +60,6 @@ __host__ __device__ constexpr size_t tc_smem_base_bytes(int D, int L) {
 }
 // + the reverse sweep's shared-memory accumulator of the input-layer gradient, [D + 1][128][kDw0Stride]
 __host__ __device__ constexpr size_t tc_smem_bytes(int D, int L) { return tc_smem_base_bytes(D, L) + (size_t)(D + 1) * 128 * kDw0Stride * 4; }
-
-// byte offset of element (r, c) of a [rows x 128] matrix image: 8-row x 16-byte core matrices, cores of one
-// row group contiguous along c (LBO = 128 B), row groups 4096 B apart (SBO)
-__host__ __device__ __forceinline__ uint32_t img_off128(int r, int c) {
-    return (uint32_t)((r >> 3) * 4096 + (c >> 2) * 128 + (r & 7) * 16 + (c & 3) * 4);
-}
-
-// RN (ties away) to tf32: what `cvt.rna.tf32.f32` computes -- ptxas emulates that instruction on sm_100a with four
-// instructions (add, inf test, select, mask; measured in the round-1 SASS: 20 of the 82 instructions per (point, feature)
-// of the forward epilogue); the add + mask below is the same rounding for every finite value below 2^127.
-__device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
 
 // tanh for the tensor-path epilogues: 1 - 2 / (1 + e^{2x}), one MUFU.EX2 + one MUFU.RCP, branch free, exact limits at
 // +-inf.  Absolute error <= 2e-7 (two units in the last place of 1), i.e. the rounding class of the fp32 sums the
@@ -147,21 +136,8 @@ __device__ __forceinline__ void tc_act_bwd(const float (&st)[D + 2], float (&ab)
     }
 }
 
-// hidden weight images for the tensor path.  transpose = 0: B[n = out][k = in] (forward);
-// transpose = 1: B[n = in][k = out] (reverse sweep).  Zero padded to 128 x 128.
 __global__ void pack_wimg_kernel(PtrArray W, int L, int Wd, int transpose, float* __restrict__ wimg) {
-    const int total = (L - 1) * 128 * 128;
-    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
-        const int l = idx / (128 * 128), rem = idx % (128 * 128);
-        const int nn = rem / 128, k = rem % 128;
-        const int o = transpose ? k : nn, i = transpose ? nn : k;
-        const float v = (o < Wd && i < Wd) ? W.p[l + 1][(size_t)o * Wd + i] : 0.f;
-        const float hi = __uint_as_float(tf32_hi(v));
-        float* base = wimg + ((size_t)l * 2 + (nn >> 6)) * 2 * kImgFloats;
-        const uint32_t off = img_off128(nn & 63, k) >> 2;
-        base[off] = hi;
-        base[kImgFloats + off] = v - hi;
-    }
+    pack_wimg_elems(W, L, Wd, transpose, wimg, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 
 

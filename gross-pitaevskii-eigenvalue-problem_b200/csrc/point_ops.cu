@@ -223,6 +223,7 @@ extern "C" {
 
 int gpe_gram_moments(const gpe_loss_desc* desc, int64_t n, const float* x, const float* u, const float* g, const float* h,
                      const float* base, const float* V, const float* q, const float* nm, double* m, gpe_stream_t stream) {
+    gpe::NvtxRange range("gpe:gram_moments");
     LossArgs A;
     const int rc = loss_args(desc, n, x, u, g, h, base, V, q, nm, &A);
     if (rc) return rc;
@@ -239,6 +240,7 @@ int gpe_gram_moments(const gpe_loss_desc* desc, int64_t n, const float* x, const
 int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, const float* u, const float* g, const float* h,
                       const float* base, const float* V, const float* q, const float* nm, const double* c, float* u_bar,
                       float* g_bar, float* h_bar, float* nm_bar, gpe_stream_t stream) {
+    gpe::NvtxRange range("gpe:gram_adjoints");
     LossArgs A;
     const int rc = loss_args(desc, n, x, u, g, h, base, V, q, nm, &A);
     if (rc) return rc;

@@ -9,8 +9,18 @@ the parameters are replicated, and one evaluation of the loss needs exactly two 
 Both go through `torch.distributed` (NCCL over NVLink on the GPU box, gloo in the CPU tests).  The
 payloads are latency-bound, so they are packed into one buffer each.
 """
+import contextlib
+import os
+
 import torch
 import torch.distributed as dist
+
+
+def _nvtx(name):
+    """Named range around a collective when GPE_NVTX=1 (the kernels' own ranges come from the C library)."""
+    if os.environ.get("GPE_NVTX") == "1" and torch.cuda.is_available():
+        return torch.cuda.nvtx.range(name)
+    return contextlib.nullcontext()
 
 
 def is_active(group=None):
@@ -24,7 +34,8 @@ class _AllReduceSum(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, group):
         y = x.clone()
-        dist.all_reduce(y, op=dist.ReduceOp.SUM, group=group)
+        with _nvtx("gpe:all_reduce#1(moments)"):
+            dist.all_reduce(y, op=dist.ReduceOp.SUM, group=group)
         return y
 
     @staticmethod
@@ -88,7 +99,8 @@ def all_reduce_gradients(params, group=None):
     if not params:
         return
     flat = torch.cat([p.grad.reshape(-1) for p in params])
-    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    with _nvtx("gpe:all_reduce#2(gradient)"):
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     off = 0
     for p in params:
         k = p.grad.numel()

@@ -14,7 +14,8 @@ CUDA graph.  Measured on B200, config 1 with the root-notebook loop body: 3.6 ms
 Rules (CUDA graphs): tensor shapes and the python control flow of the step must not change between replays; use
 `torch.optim.Adam(..., capturable=True)`; read results with `.item()`/`float()` only outside the step function
 (e.g. every k-th epoch for the early-stop test); scalars that change per stage (gamma of the curriculum) must be
-device tensors updated in place with `.fill_()` / `.copy_()`.
+device tensors updated in place with `.fill_()` / `.copy_()`.  Evaluating the model between replays (monitoring every
+k-th epoch) is safe: every replay invalidates the models' per-step caches, and evaluations without grad are never cached.
 """
 from typing import Callable, Optional
 
@@ -47,4 +48,8 @@ class GraphedStep:
     def __call__(self):
         self.graph.replay()
         self.replays += 1
+        # the replay stepped the parameters on the device without touching Tensor._version: results the models cached
+        # for their current autograd graph must not be handed out again (models.invalidate_caches)
+        from .models import invalidate_caches
+        invalidate_caches()
         return self.outputs

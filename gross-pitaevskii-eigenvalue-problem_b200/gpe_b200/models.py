@@ -968,7 +968,8 @@ class ReLoBRaLoGPE2D(JetMLP):
     The file keeps 1-D formulas on [N,2] inputs: V = exp(-(x-a)^2) is [N,2], u_xx = grad(sum grad u) = Hessian.(1,1),
     the residual is [N,2] with one scalar lambda.  Here: one FULL jet evaluation (u, grad u, u_xx, u_yy, u_xy) and one
     moment pass per residual column (its "Laplacian" is u_cc + u_xy, its potential V[:,c]); the ReLoBRaLo weight
-    update (:294-335) stays the reference's host-side python."""
+    update (:294-335) is the reference's host-side python by default and device tensor arithmetic with
+    `device_weights = True` (graph-capturable)."""
     jet_mode = "full"
 
     def __init__(self, layers, hbar=1.0, m=1.0, g=100.0, alpha=0.999, temperature=1.0, rho=0.9999):
@@ -1002,7 +1003,7 @@ class ReLoBRaLoGPE2D(JetMLP):
             V = self.compute_potential(inputs.detach()).float()
             Ms = []
             for c in (0, 1):
-                m = ops.gram_moments(u, g, h[:, [c, 2]].contiguous(), None, V=V[:, c].contiguous(), d=2,
+                m = ops.gram_moments(u, g, torch.stack([h[:, c], h[:, 2]], dim=1), None, V=V[:, c].contiguous(), d=2,
                                      nl_kind=ops.NL_POW, nl_power=3, lap_cols=2)
                 Ms.append(L.Moments(gdist.all_reduce_sum(m, self.group)))
             hit = (inputs, Ms, V)
@@ -1055,6 +1056,38 @@ class ReLoBRaLoGPE2D(JetMLP):
         self.call_count += 1
         return [lam * w for lam, w in zip(self.lambdas, [500.0, 1.0, 2.0, 100.0, 500])]
 
+    #: True: the ReLoBRaLo update runs on the device (no .item(), no host RNG), so the whole step captures into a CUDA graph
+    #: (graphs.GraphedStep; capture after the first two calls, whose alpha differs).  False: the reference's host-side update,
+    #: value for value (five host reads and one CPU torch.bernoulli draw per step).
+    device_weights = False
+
+    def relobralo_weights_device(self, losses):
+        """:294-335 as tensor arithmetic (float64) on the device of the terms.  The reference's `softmax(x - max(x))` is
+        `softmax(x)`; rho is drawn from the device generator; state lives in three device vectors."""
+        vals = torch.stack([t.detach().double().reshape(()) for t in losses])
+        st = self.__dict__.get("_rb_state")
+        if st is None or st["lam"].device != vals.device:
+            st = {k: torch.ones_like(vals) for k in ("lam", "last", "init")}
+            st["manual"] = torch.tensor([500.0, 1.0, 2.0, 100.0, 500.0], dtype=torch.float64, device=vals.device)
+            self.__dict__["_rb_state"] = st
+        if self.call_count == 0:
+            st["lam"].fill_(1.0)
+            st["last"].copy_(vals)
+            st["init"].copy_(vals)
+        hat = torch.softmax(vals / (st["last"] * self.temperature + 1e-8), dim=0)
+        hat0 = torch.softmax(vals / (st["init"] * self.temperature + 1e-8), dim=0)
+        rho = torch.bernoulli(torch.full((), float(self.rho), dtype=torch.float64, device=vals.device))
+        alpha = self.alpha if self.call_count > 1 else (0.0 if self.call_count == 1 else 1.0)
+        st["lam"].copy_(rho * alpha * st["lam"] + (1.0 - rho) * alpha * hat0 + (1.0 - alpha) * hat)
+        st["last"].copy_(vals)
+        self.call_count += 1
+        return st["lam"] * st["manual"]
+
+    @property
+    def lambdas_device(self):
+        st = self.__dict__.get("_rb_state")
+        return None if st is None else st["lam"]
+
     def total_loss(self, collocation_points, boundary_points, boundary_values, eta):
         """:259-341 -> (total, data, riesz, pde, norm); one jet evaluation serves riesz, pde and norm."""
         data = self.boundary_loss(boundary_points, boundary_values)
@@ -1063,7 +1096,11 @@ class ReLoBRaLoGPE2D(JetMLP):
         norm = ((torch.sqrt(self._M2(collocation_points)[0][0].nn2) - 1.0) ** 2).float()
         sym = self.symmetry_loss(collocation_points)
         losses = [data, riesz, pde, norm, sym]
-        total = sum(w * t for w, t in zip(self.relobralo_weights(losses), losses))
+        if self.device_weights:
+            w = self.relobralo_weights_device(losses)
+            total = (w * torch.stack([t.double().reshape(()) for t in losses])).sum().float()
+        else:
+            total = sum(w * t for w, t in zip(self.relobralo_weights(losses), losses))
         return total, data, riesz, pde, norm
 
 

@@ -155,12 +155,14 @@ class _Stage:
 
 def train_gpe_model(gamma_values, modes, p, X_train, lb, ub, layers, epochs, tol, perturb_const, potential_type="harmonic",
                     lr=1e-5, verbose=True, *, model_factory=None, pretrain_epochs=2000, check_every=50, use_graph=True,
-                    init_state=None, device="cuda", keep_rings=False):
+                    init_state=None, device="cuda", keep_rings=False, normal_const=None):
     """R/harmonic_pinn_simulation.py:220-431 -> (models_by_mode, mu_table, training_history, constant_history,
     epochs_history).  Keyword-only extras: model_factory(layers, mode, gamma) (default FinalGPE1D of `potential_type`),
     pretrain_epochs (:338 uses 2000), check_every (how often the host reads the device `done` flag), use_graph,
     init_state (state_dict to start every mode from instead of pre-training / advanced_initialization),
-    keep_rings (also return the per-epoch device logs in training_history[mode][gamma]['per_epoch'])."""
+    keep_rings (also return the per-epoch device logs in training_history[mode][gamma]['per_epoch']),
+    normal_const (float or {mode: float}: continue a run whose normalisation constant is known -- the `constant_history`
+    of a shipped bundle -- instead of fixing it at epoch 0 of the first stage)."""
     if not torch.cuda.is_available():
         raise RuntimeError("gpe_b200.training needs a CUDA device (there is no CPU path)")
     dx = float(X_train[1, 0] - X_train[0, 0])
@@ -173,7 +175,11 @@ def train_gpe_model(gamma_values, modes, p, X_train, lb, ub, layers, epochs, tol
     models_by_mode, mu_table, training_history, constant_history, epochs_history = {}, {}, {}, {}, {}
     gamma_values = sorted(gamma_values)
     for mode in modes:
-        mu_logs, by_gamma, hist_by_gamma, epochs_by_gamma, prev, normal_const = [], {}, {}, {}, None, None
+        mu_logs, by_gamma, hist_by_gamma, epochs_by_gamma, prev = [], {}, {}, {}, None
+        nc_given = normal_const.get(mode) if isinstance(normal_const, dict) else normal_const
+        normal_const_m = float(nc_given) if nc_given is not None else None
+        if normal_const_m is not None:
+            constant_history[mode] = torch.tensor(normal_const_m)
         for gamma in gamma_values:
             model = model_factory(layers, mode, gamma).to(device)
             if prev is not None:
@@ -185,16 +191,16 @@ def train_gpe_model(gamma_values, modes, p, X_train, lb, ub, layers, epochs, tol
             else:
                 model.apply(lambda m: advanced_initialization(m, mode))
             st = _Stage(model, X, bp, bv, dx, gamma, p, potential_type, perturb_const, lr, epochs, tol)
-            st.normal_const = normal_const
+            st.normal_const = normal_const_m
             # epoch 0 of a mode's first stage fixes the normalisation constant (:366-371); it runs eagerly
-            first = normal_const is None
+            first = normal_const_m is None
             if first and gamma != 0:
                 raise ValueError("the first gamma of a mode must be 0: the reference sets normal_const there (:366)")
             st.body(first_of_mode=first)
             ran = 1
-            normal_const = st.normal_const
+            normal_const_m = st.normal_const
             if first:
-                constant_history[mode] = torch.tensor(normal_const)
+                constant_history[mode] = torch.tensor(normal_const_m)
             step = st.body
             if use_graph and epochs - ran > 8:
                 step = GraphedStep(st.body, st.opt, warmup=2)          # two more eager epochs, then one capture

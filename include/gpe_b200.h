@@ -20,10 +20,18 @@
  *
  * Conventions: every pointer except the `W`/`b`/`dW`/`db` pointer ARRAYS (host arrays of device
  * pointers) and the descriptor structs is a DEVICE pointer owned by the caller; fp32, contiguous.
- * The library allocates nothing, keeps no mutable global state besides cached device
- * attributes, never synchronises the host, and enqueues all work on `stream`.  Gradients are
- * WRITTEN, not accumulated.  Return value 0 = success, negative = error (see gpe_last_error()).
+ * The library allocates no device memory, never synchronises the host, and enqueues all work on
+ * `stream`; calls are re-entrant across streams and threads.  Gradients are WRITTEN, not accumulated.
+ * Return value 0 = success, negative = error (see gpe_last_error(), thread-local).
  * There is no CPU fallback: without a CUDA device every compute entry point fails.
+ *
+ * Process-wide state (all of it; mutex-protected where it is written after start-up):
+ *   - caches keyed by device: launch plans, SM counts, "shared-memory attribute already set" per (kernel, device);
+ *   - the default of GPE_PREC_AUTO: gpe_set_tensor_path() / GPE_TENSOR (per-call control: gpe_mlp_desc.precision);
+ *   - the optional profiling event list of gpe_tc_profile() / gpe_tc_timings();
+ *   - tuning knobs read from the environment PER CALL: GPE_TC_TWO_TILES, GPE_TC_TWO_TILES_REV, GPE_BWD_FUSED,
+ *     GPE_FUSED_NRC, GPE_RING_TILES (and once per process: GPE_TC_INTERLEAVE*, GPE_REV_PF, GPE_DW_N1, GPE_DW_PF,
+ *     GPE_TC_ACT_GENERIC, GPE_NVTX).
  */
 #ifndef GPE_B200_H
 #define GPE_B200_H
@@ -55,10 +63,13 @@ enum {
     GPE_JET_LAPLACIAN = 3  /* u, du/dx_i, Laplacian (one fused stream)  h is [N,1]                   */
 };
 
-/* GPE_PREC_FP32: register-blocked FFMA (fp32 throughout).
+/* Arithmetic of the hidden-layer contractions, chosen PER CALL by gpe_mlp_desc.precision:
+ * GPE_PREC_FP32: register-blocked FFMA (fp32 throughout), any supported shape.
  * GPE_PREC_TF32X3: tcgen05 tensor cores, every fp32 operand split into hi+lo TF32 halves and
- * three MMAs per product (hi*hi + hi*lo + lo*hi), fp32 accumulation in TMEM.
- * GPE_PREC_AUTO: TF32X3 where a tensor-core kernel exists for the shape, else FP32. */
+ * three MMAs per product (hi*hi + hi*lo + lo*hi), fp32 accumulation in TMEM; a shape without a
+ * tensor-core kernel is an error (-1), never a silent change of path.
+ * GPE_PREC_AUTO: TF32X3 where a tensor-core kernel exists for the shape (and the process default
+ * gpe_set_tensor_path / GPE_TENSOR allows it), else FP32. */
 enum { GPE_PREC_FP32 = 0, GPE_PREC_TF32X3 = 1, GPE_PREC_AUTO = 2 };
 
 typedef struct {
@@ -150,8 +161,8 @@ int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, cons
                       gpe_stream_t stream);
 
 /* ---- tensor-core (tcgen05) path control ----
- * The 3xTF32 tensor path is the default wherever it applies (64 < width <= 128, Laplacian jets, <= 3 hidden
- * matrices); GPE_TENSOR=0 in the environment or gpe_set_tensor_path(0) selects the FFMA kernels instead
+ * The 3xTF32 tensor path is the GPE_PREC_AUTO default wherever it applies (64 < width <= 128, Laplacian jets, <= 3 hidden
+ * matrices); GPE_TENSOR=0 in the environment or gpe_set_tensor_path(0) makes GPE_PREC_AUTO select the FFMA kernels instead
  * (north_star: tensor cores "only if TF32/BF16-split accuracy holds", otherwise register-blocked FFMA).
  * gpe_set_tensor_path returns the previous setting.  gpe_tc_profile(1) brackets every tensor-path backward
  * kernel with CUDA events on the launch stream; gpe_tc_timings() synchronises those events, returns the

@@ -926,6 +926,60 @@ class HelmholtzCircle(Helmholtz2D):
         return self.loss_function(f.view(-1), torch.zeros_like(f).view(-1))
 
 
+class HelmholtzCircle2(Helmholtz2D):
+    """`HelmholtzPINN` of S/helmholtz_2D_circle_2.py:28-179: LeakyReLU MLP (:53) behind the min-max feature scaling
+    (:89-94); the inputs ARE the polar coordinates (r, theta) and the residual is written directly in them.  Shapes as
+    in the reference: r, theta are [N] and the autograd columns [N,1], so the residual is an [N,N] table."""
+
+    def __init__(self, layers, lb=(0.0, 0.0), ub=(1.0, 2 * math.pi)):
+        super().__init__(layers, activation="leaky_relu", lb=list(lb), ub=list(ub))
+
+    def loss_PDE(self, x_f, n=1, m=1):
+        """:108-160."""
+        g = x_f.clone().requires_grad_(True)
+        r, theta = g[:, 0], g[:, 1]
+        u = self.forward(g)
+        du = d_dx(u, g)
+        u_r, u_t = du[:, [0]], du[:, [1]]
+        u_rr = d_dx(u_r, g)[:, [0]]
+        u_tt = d_dx(u_t, g)[:, [1]]
+        if x_f.dtype == torch.float32:
+            k = torch.sqrt(torch.tensor(np.pi ** 2 * (m ** 2 + n ** 2), dtype=torch.float32, device=g.device))
+        else:
+            k = torch.tensor(math.sqrt(math.pi ** 2 * (m ** 2 + n ** 2)), dtype=x_f.dtype, device=g.device)
+        q = (k ** 2) * torch.sin(n * r * theta) * torch.sin(m * r * theta)
+        f = u_rr + (1 / r) * u_r + (1 / r ** 2) * u_tt + k ** 2 * u - q
+        return self.loss_function(f, torch.zeros_like(f))
+
+
+class HelmholtzCircle3(Helmholtz2D):
+    """`HelmholtzPINN` of S/helmholtz_2D_circle_3.py:20-132: tanh MLP, no input scaling, polar residual from Cartesian
+    autograd columns ([N]) against u [N,1] -> [N,N]; u_thetatheta = d(u_theta)/d(theta) with u_x, u_y held fixed
+    (theta is not a leaf: the graph reaches it only through cos / sin) divided by r (:96-97); source k^2 J_0(k r) cos(n theta)."""
+
+    def __init__(self, layers):
+        super().__init__(layers, activation="tanh")
+
+    def loss_pde(self, x_f, n, k):
+        """:58-110."""
+        g = x_f.clone().requires_grad_(True)
+        u = self.forward(g)
+        r = torch.sqrt(g[:, 0] ** 2 + g[:, 1] ** 2)
+        theta = torch.atan2(g[:, 1], g[:, 0])
+        du = d_dx(u, g)
+        u_x, u_y = du[:, 0], du[:, 1]
+        u_r = u_x * torch.cos(theta) + u_y * torch.sin(theta)
+        u_theta = -u_x * torch.sin(theta) + u_y * torch.cos(theta)
+        u_xx = d_dx(u_x, g)[:, 0]
+        u_yy = d_dx(u_y, g)[:, 1]
+        u_rr = u_xx * torch.cos(theta) ** 2 + u_yy * torch.sin(theta) ** 2
+        u_tt = torch.autograd.grad(u_theta, theta, grad_outputs=torch.ones_like(u_theta), create_graph=True)[0] / r
+        lap = u_rr + (1 / r) * u_r + (1 / r ** 2) * u_tt
+        q = k ** 2 * torch.special.bessel_j0(k * r) * torch.cos(n * theta)
+        res = lap + k ** 2 * u - q
+        return self.loss_function(res, torch.zeros_like(res))
+
+
 # --------------------------------------------------------------------------------------
 # helpers shared by tests / bench
 # --------------------------------------------------------------------------------------

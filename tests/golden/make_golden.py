@@ -480,6 +480,41 @@ def case_helmholtz_circle(layers, n_pts):
     return out
 
 
+def case_helmholtz_circle23(which, layers, n_pts):
+    """S/helmholtz_2D_circle_2.py (LeakyReLU, inputs = (r, theta), loss_PDE(x, n, m) :108-160) and
+    S/helmholtz_2D_circle_3.py (tanh, Cartesian inputs, loss_pde(x_f, n, k) :58-110).  circle_2's forward casts to
+    float32 (:97), so only float32 outputs exist for it; circle_3 runs in both precisions."""
+    rng = np.random.default_rng(31 + which)
+    torch.manual_seed(1234)
+    out = {}
+    if which == 2:
+        mod = rl.load_script("helmholtz_2D_circle_2.py")
+        mod.device = torch.device("cpu")
+        mod.lb, mod.ub = np.array([0.0, 0.0]), np.array([1.0, 2 * np.pi])
+        Xn = np.stack([0.05 + 0.95 * rng.random(n_pts), rng.random(n_pts) * 2 * np.pi], 1).astype(np.float32).astype(np.float64)
+        model = mod.HelmholtzPINN(layers)
+        _pack("w.", _state(model), out)
+        loss = model.loss_PDE(torch.tensor(Xn, dtype=torch.float32), 1, 1)
+        _pack("f32.", dict(pde=_np(loss), grads=_grads(model, loss)), out)
+        out.update(lb=mod.lb, ub=mod.ub)
+    else:
+        mod = rl.load_script("helmholtz_2D_circle_3.py")
+        mod.device = torch.device("cpu")
+        rad, ang = 0.05 + 0.95 * np.sqrt(rng.random(n_pts)), rng.random(n_pts) * 2 * np.pi
+        Xn = np.stack([rad * np.cos(ang), rad * np.sin(ang)], 1).astype(np.float32).astype(np.float64)
+        model = mod.HelmholtzPINN(layers)
+        _pack("w.", _state(model), out)
+        k = 2.404825557695773          # first zero of J_0: the disc eigenmode the file trains for
+        for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+            m2 = mod.HelmholtzPINN(layers).to(dt)
+            m2.load_state_dict({kk: v.to(dt) for kk, v in model.state_dict().items()})
+            loss = m2.loss_pde(torch.tensor(Xn, dtype=dt), 0, k)
+            _pack(tag + ".", dict(pde=_np(loss), grads=_grads(m2, loss)), out)
+        out.update(k=k, n=0)
+    out.update(X=Xn, layers=np.array(layers))
+    return out
+
+
 def case_opt_variant(kind, mode, eta, layers, n_pts, p=2):
     """The three later copies of the F-opt class:
     self_adaptive  S/gross_pitaevskii_1D_Different_Optimizers_Self_Adaptive.py:27-429 (log_alpha weights),
@@ -542,6 +577,12 @@ def main():
         "final_neg_gamma_shipped_m1_gm8": lambda: case_final_random(
             -8, 3, 1, None, 4000, shipped=("comparison_results_neg_int_strength_p3_harmonic/curriculum_pinn_models_p3_harmonic.pkl",
                                            "curriculum_state_dicts", 1.0)),
+        # gamma > 0 stages of the shipped curriculum run (gamma = 0 -> 20 -> ... -> 100), same protocol as the negative-gamma
+        # file: constants None, u_pred = 0.01 model(X)
+        "final_curriculum_shipped_m0_g20": lambda: case_final_random(
+            20, 3, 0, None, 4000, shipped=("comparison_results_p3_harmonic/curriculum_pinn_models_p3_harmonic.pkl", "curriculum_state_dicts", 1.0)),
+        "final_curriculum_shipped_m1_g60": lambda: case_final_random(
+            60, 3, 1, None, 4000, shipped=("comparison_results_p3_harmonic/curriculum_pinn_models_p3_harmonic.pkl", "curriculum_state_dicts", 1.0)),
         "box_to_gaussian_res_g10_p3_m0": lambda: case_final_random(10.0, 3, 0, [1, 64, 64, 64, 1], 800, kind="box_to_gaussian"),
         "box_to_gaussian_res_g4_p4_m2": lambda: case_final_random(4.0, 4, 2, [1, 48, 48, 48, 48, 1], 500, kind="box_to_gaussian"),
         "box_to_gaussian_plain_g5_p3_m1": lambda: case_final_random(
@@ -572,6 +613,8 @@ def main():
         "helmholtz_tanh": lambda: case_helmholtz([2, 100, 100, 100, 1], 200, 40, "tanh"),
         "helmholtz_circle": lambda: case_helmholtz_circle([2, 64, 64, 64, 1], 150),
         "helmholtz_learnable_k": lambda: case_helmholtz_learnable_k([2, 64, 64, 64, 1], 300, 40),
+        "helmholtz_circle_2": lambda: case_helmholtz_circle23(2, [2, 64, 64, 64, 1], 120),
+        "helmholtz_circle_3": lambda: case_helmholtz_circle23(3, [2, 64, 64, 64, 1], 120),
     }
     only = sys.argv[1:]
     for name, fn in cases.items():

@@ -280,3 +280,97 @@ def test_airy_base_on_device_matches_the_scipy_construction():
             assert err.max() < 2e-7, (n, npts, err)
     with pytest.raises(ValueError):
         airy_base_jets(torch.zeros(4, 1), 16)
+
+
+# ---------------------------------------------------------------------------------------------
+# collocation generators (run where they are told to: here on the CPU)
+# ---------------------------------------------------------------------------------------------
+def test_latin_hypercube_hits_every_stratum_once_per_dimension():
+    from gpe_b200 import collocation
+    n, d, lo, hi = 4096, 2, -6.0, 6.0
+    X = collocation.latin_hypercube(n, d, lo, hi, seed=11, device="cpu", dtype=torch.float64)
+    assert X.shape == (n, d) and float(X.min()) >= lo and float(X.max()) <= hi
+    for k in range(d):
+        strata = torch.floor((X[:, k] - lo) / (hi - lo) * n).long().clamp(max=n - 1)
+        assert torch.equal(torch.sort(strata).values, torch.arange(n)), k          # a permutation of the n strata
+    # the two dimensions are permuted independently
+    sx = torch.floor((X[:, 0] - lo) / (hi - lo) * n)
+    sy = torch.floor((X[:, 1] - lo) / (hi - lo) * n)
+    assert float((sx == sy).double().mean()) < 0.01
+    # seed-deterministic; the per-rank streams of a data-parallel run (seed + rank) differ
+    assert torch.equal(X, collocation.latin_hypercube(n, d, lo, hi, seed=11, device="cpu", dtype=torch.float64))
+    Y = collocation.latin_hypercube(n, d, lo, hi, seed=12, device="cpu", dtype=torch.float64)
+    assert not torch.equal(X, Y) and len(set(map(tuple, X.tolist())) & set(map(tuple, Y.tolist()))) == 0
+    # per-dimension bounds
+    Z = collocation.latin_hypercube(1000, 2, [0.0, -1.0], [1.0, 3.0], seed=3, device="cpu", dtype=torch.float64)
+    assert 0.0 <= float(Z[:, 0].min()) and float(Z[:, 0].max()) <= 1.0 and -1.0 <= float(Z[:, 1].min()) and float(Z[:, 1].max()) <= 3.0
+
+
+def test_square_boundary_lies_on_the_perimeter():
+    from gpe_b200 import collocation
+    lo, hi = -6.0, 6.0
+    P = collocation.square_boundary(500, lo, hi, seed=5, device="cpu", dtype=torch.float64)
+    assert P.shape == (500, 2)
+    on_edge = (P[:, 0] == lo) | (P[:, 0] == hi) | (P[:, 1] == lo) | (P[:, 1] == hi)
+    assert bool(on_edge.all()) and float(P.min()) >= lo and float(P.max()) <= hi
+    for col, val in ((1, lo), (1, hi), (0, lo), (0, hi)):                          # 125 points per edge
+        assert int((P[:, col] == val).sum()) >= 125
+    assert torch.equal(P, collocation.square_boundary(500, lo, hi, seed=5, device="cpu", dtype=torch.float64))
+
+
+def test_disc_points_follow_the_reference_distribution():
+    """S/gross_pitaevskii_2D.py:277-295: r ~ U(0, R), theta ~ U(0, 2 pi) -- uniform in r, NOT in area."""
+    from gpe_b200 import collocation
+    c, R, n = (np.pi / 2, np.pi / 2), np.pi / 2, 200_000
+    P = collocation.disc_points(n, c, R, seed=2, device="cpu", dtype=torch.float64)
+    r = torch.sqrt((P[:, 0] - c[0]) ** 2 + (P[:, 1] - c[1]) ** 2)
+    assert float(r.max()) <= R * (1 + 1e-12)
+    hist = torch.histc(r, bins=10, min=0.0, max=R) / n
+    assert float((hist - 0.1).abs().max()) < 0.005                                # r uniform: an area-uniform sample would give 0.01 .. 0.19
+    th = torch.atan2(P[:, 1] - c[1], P[:, 0] - c[0])
+    hist_t = torch.histc(th, bins=8, min=-np.pi, max=np.pi) / n
+    assert float((hist_t - 0.125).abs().max()) < 0.005
+    B = collocation.disc_boundary(500, c, R, device="cpu", dtype=torch.float64)
+    rb = torch.sqrt((B[:, 0] - c[0]) ** 2 + (B[:, 1] - c[1]) ** 2)
+    assert float((rb - R).abs().max()) < 1e-12 and torch.allclose(B[0], B[-1], atol=1e-12)
+
+
+# ---------------------------------------------------------------------------------------------
+# replicated boundary term under data parallelism (ADVICE round 1): counted once, not world times
+# ---------------------------------------------------------------------------------------------
+def _replicated_worker(rank, world, port, out):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from gpe_b200 import distributed as gdist
+        torch.manual_seed(3)
+        net = torch.nn.Sequential(torch.nn.Linear(2, 16), torch.nn.Tanh(), torch.nn.Linear(16, 1)).double()
+        Xall = torch.rand(64, 2, dtype=torch.float64, generator=torch.Generator().manual_seed(4))
+        Xb = torch.rand(10, 2, dtype=torch.float64, generator=torch.Generator().manual_seed(5))     # the same points on every rank
+        lo, hi = gdist.shard_bounds(64, rank, world)
+        interior = gdist.all_reduce_sum(torch.sum(net(Xall[lo:hi]) ** 2)) / 64.0                  # sharded term
+        boundary = gdist.replicated_term(10.0 * torch.mean(net(Xb) ** 2))                         # replicated term
+        loss = interior + boundary
+        loss.backward()
+        gdist.all_reduce_gradients(net.parameters())
+        if rank == 0:
+            torch.save({"loss": loss.detach(), "grad": torch.cat([p.grad.reshape(-1) for p in net.parameters()])}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_replicated_boundary_term_is_counted_once_gloo(tmp_path):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "rep.pt")
+    mp.spawn(_replicated_worker, args=(2, 29600 + (os.getpid() % 2000), out), nprocs=2, join=True)
+    got = torch.load(out)
+    torch.manual_seed(3)
+    net = torch.nn.Sequential(torch.nn.Linear(2, 16), torch.nn.Tanh(), torch.nn.Linear(16, 1)).double()
+    Xall = torch.rand(64, 2, dtype=torch.float64, generator=torch.Generator().manual_seed(4))
+    Xb = torch.rand(10, 2, dtype=torch.float64, generator=torch.Generator().manual_seed(5))
+    loss = torch.mean(net(Xall) ** 2) + 10.0 * torch.mean(net(Xb) ** 2)
+    loss.backward()
+    want = torch.cat([p.grad.reshape(-1) for p in net.parameters()])
+    assert abs(float(got["loss"]) - float(loss)) < 1e-12 * abs(float(loss))
+    assert float((got["grad"] - want).norm() / want.norm()) < 1e-12

@@ -14,13 +14,27 @@ from helpers import scalar, load_weights, golden_grads, flat, rel_err, model_gra
     OPT_VARIANT_GOLDENS, opt_variant_model_and_kwargs
 
 pytestmark = pytest.mark.gpu
-TOL = 1e-5
-GTOL = 2e-5
+TOL = 1e-5    # north-star: loss terms AND parameter gradients within 1e-5 relative (measured: 1-4e-6)
+GTOL = 1e-5
 
 
 def close(a, b, tol=TOL):
     a, b = scalar(a), scalar(b)
     return abs(a - b) <= tol * max(abs(b), 1e-30)
+
+
+def bc_close(bc, ref):
+    """boundary_loss = mean(u_b^2) at two points where u_b ~ 1e-3 is a cancelling sum of O(1) hidden activations: its
+    fp32 value carries an ABSOLUTE error of ~eps(1) = 6e-8, i.e. 2 u_b 6e-8 ~ 5e-10 on the term, whatever evaluates it
+    (the reference's own float32 run differs from its float64 run by as much)."""
+    return abs(scalar(bc) - scalar(ref)) <= TOL * abs(scalar(ref)) + 5e-10
+
+
+def norm_close(nrm, ref):
+    """normalization_loss = (S - 1)^2 with S = sum(u^2) dx ~ 1 is the square of an fp32 cancellation: compare S itself
+    (|S - 1| = sqrt of the term) to 1e-6 instead of its squared residual to a loose relative bound."""
+    a, b = abs(scalar(nrm)) ** 0.5, abs(scalar(ref)) ** 0.5
+    return abs(a - b) <= 1e-6 * (1.0 + b)
 
 
 def cuda_model(cls, gold, *args, prefix="w.", **kw):
@@ -61,9 +75,9 @@ def test_paper_notebook(golden, name):
     e, lam_e, _ = model.riesz_loss(X, model.forward(X), gamma, p)
     pde, res, mu, u = model.pde_loss(X, model.forward(X), gamma, p)
     for key, val in dict(pde=pde, riesz=e, lam_riesz=lam_e, mu=mu, bc=bc, sym=sym, total=total).items():
-        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
-    assert close(lam, g["f64.lam_riesz"] if int(g["mode"]) == 0 else g["f64.mu"], 2 * TOL)
-    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
+        assert close(val, g[f"f64.{key}"], TOL), (key, float(val), float(g[f"f64.{key}"]))
+    assert close(lam, g["f64.lam_riesz"] if int(g["mode"]) == 0 else g["f64.mu"], TOL)
+    assert norm_close(nrm, g["f64.norm"]), (float(nrm), float(g["f64.norm"]))
     assert rel_err(u.detach().cpu().numpy()[:, 0], g["f64.u"]) < TOL
     assert rel_err(res.detach().cpu().numpy()[:, 0], g["f64.residual"]) < 5 * TOL
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
@@ -72,7 +86,8 @@ def test_paper_notebook(golden, name):
 @pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
                                        ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well"),
                                        ("final_box_vanilla_g10_p3_m0", "box"), ("final_box_option_g5_p3_m1", "box"),
-                                       ("final_neg_gamma_shipped_m1_gm8", "harmonic")])
+                                       ("final_neg_gamma_shipped_m1_gm8", "harmonic"),
+                                       ("final_curriculum_shipped_m0_g20", "harmonic"), ("final_curriculum_shipped_m1_g60", "harmonic")])
 def test_final_random(golden, name, kind):
     import gpe_b200
     g = golden(name)
@@ -85,10 +100,10 @@ def test_final_random(golden, name, kind):
     total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
                                                    float(g["gamma"]), int(g["p"]), float(g["perturb_const"]), float(g["const"]))
     for key, val in dict(pde=pde, total=total, mu=mu).items():
-        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+        assert close(val, g[f"f64.{key}"], TOL), (key, float(val), float(g[f"f64.{key}"]))
     # (sum u^2 dx - 1)^2 of a nearly normalised state: squares an O(1e-4) fp32 difference
-    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
-    assert abs(float(bc) - float(g["f64.bc"])) <= 2 * TOL * abs(float(g["f64.bc"])) + 1e-12
+    assert norm_close(nrm, g["f64.norm"]), (float(nrm), float(g["f64.norm"]))
+    assert bc_close(bc, g["f64.bc"]), (float(bc), float(g["f64.bc"]))
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
@@ -103,7 +118,7 @@ def _b2g_check(model, g, tol, gtol):
                                                    float(g["gamma"]), int(g["p"]), float(g["perturb_const"]), float(g["const"]))
     for key, val in dict(pde=pde, total=total, mu=mu).items():
         assert close(val, g[f"f64.{key}"], tol), (key, float(val), float(g[f"f64.{key}"]))
-    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
+    assert norm_close(nrm, g["f64.norm"]), (float(nrm), float(g["f64.norm"]))
     assert abs(float(bc) - float(g["f64.bc"])) <= tol * abs(float(g["f64.bc"])) + 1e-12
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < gtol
 
@@ -117,7 +132,7 @@ def test_box_to_gaussian_residual_blocks(golden, name):
     model = cuda_model(gpe_b200.BoxToGaussianGPE1D, g, [int(v) for v in g["layers"]], mode=int(g["mode"]),
                        gamma=float(g["gamma"]), use_residual="_res_" in name)
     assert ("network.2.lin1.weight" in model.state_dict()) == ("_res_" in name)
-    _b2g_check(model, g, 2 * TOL, GTOL)
+    _b2g_check(model, g, TOL, GTOL)
 
 
 def test_compat_box_to_gaussian_residual_blocks(golden):
@@ -127,7 +142,7 @@ def test_compat_box_to_gaussian_residual_blocks(golden):
     g = golden("box_to_gaussian_res_g10_p3_m0")
     model = patch(load_weights(po.BoxToGaussianGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]),
                                                      gamma=float(g["gamma"])), g).cuda())
-    _b2g_check(model, g, 2e-5, 5e-5)
+    _b2g_check(model, g, TOL, GTOL)
 
 
 @pytest.mark.parametrize("kind", ["harmonic", "box", "gravity_well"])
@@ -144,8 +159,8 @@ def test_final_fixture_mu_table(golden, kind):
                            gamma=0.0, potential=kind)
         total, pde, bc, nrm, mu = po.final_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
                                                        0.0, 3, 0.01, float(g[f"m{mode}.const"]))
-        assert abs(float(mu) - float(g[f"m{mode}.mu_table"])) < 2e-5 * abs(float(g[f"m{mode}.mu_table"])), mode
-        assert abs(float(mu) - float(g[f"m{mode}.f64.mu"])) < 2e-5 * abs(float(g[f"m{mode}.f64.mu"])), mode
+        assert abs(float(mu) - float(g[f"m{mode}.mu_table"])) < TOL * abs(float(g[f"m{mode}.mu_table"])), mode
+        assert abs(float(mu) - float(g[f"m{mode}.f64.mu"])) < TOL * abs(float(g[f"m{mode}.f64.mu"])), mode
         # converged losses are ~1e-6 differences of O(1) numbers: fp32 agreement is loose by nature
         for key, val in dict(pde=pde, total=total).items():
             ref = float(g[f"m{mode}.f64.{key}"])
@@ -166,7 +181,7 @@ def test_beta_sweep_variants(golden, name):
     total, pde, bc, nrm, mu = po.variant_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
                                                      pde_args, float(g["perturb_const"]), float(g["const"]))
     shipped = "shipped" in name
-    assert close(mu, g["f64.mu"], 2e-5), (float(mu), float(g["f64.mu"]))
+    assert close(mu, g["f64.mu"], TOL), (float(mu), float(g["f64.mu"]))
     if shipped:      # converged weights: losses are ~1e-6 differences of O(1) numbers (see test_final_fixture_mu_table)
         for key, val in dict(pde=pde, total=total).items():
             ref = float(g[f"f64.{key}"])
@@ -174,9 +189,9 @@ def test_beta_sweep_variants(golden, name):
         assert abs(float(mu) - float(g["mu_logged"])) < 2e-3 * abs(float(g["mu_logged"]))
         return
     for key, val in dict(pde=pde, total=total).items():
-        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
-    assert abs(float(nrm) - float(g["f64.norm"])) <= 1e-3 * abs(float(g["f64.norm"])) + 1e-9
-    assert abs(float(bc) - float(g["f64.bc"])) <= 2 * TOL * abs(float(g["f64.bc"])) + 1e-12
+        assert close(val, g[f"f64.{key}"], TOL), (key, float(val), float(g[f"f64.{key}"]))
+    assert norm_close(nrm, g["f64.norm"]), (float(nrm), float(g["f64.norm"]))
+    assert bc_close(bc, g["f64.bc"]), (float(bc), float(g["f64.bc"]))
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
@@ -199,7 +214,7 @@ def test_opt_variants(golden, name):
         got["sym"] = ret[5]
         assert rel_err(ret[6].detach().cpu().numpy(), g["f64.alpha"]) < TOL
     for key, val in got.items():
-        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+        assert close(val, g[f"f64.{key}"], TOL), (key, float(val), float(g[f"f64.{key}"]))
     assert abs(float(ret[4]) - float(g["f64.norm"])) <= 1e-4 * abs(float(g["f64.norm"])) + 1e-9
     assert rel_err(flat(model_grads(model, ret[0])), flat(golden_grads(g, "f64.grads"))) < GTOL
 
@@ -292,8 +307,8 @@ def test_compat_root(golden):
     total, pde, bc, nrm, sym, mu = po.root_train_terms(model, X, bp, torch.zeros((2, 1), device="cuda"), float(g["dx"]),
                                                        float(g["gamma"]), int(g["p"]), lb, ub)
     for key, val in dict(pde=pde, bc=bc, norm=nrm, sym=sym, total=total, mu=mu).items():
-        assert close(val, g[f"f64.{key}"], 2e-5), (key, float(val), float(g[f"f64.{key}"]))
-    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+        assert close(val, g[f"f64.{key}"], TOL), (key, float(val), float(g[f"f64.{key}"]))
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 def test_compat_g2d_and_helmholtz(golden):
@@ -303,15 +318,15 @@ def test_compat_g2d_and_helmholtz(golden):
     X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
     xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
     total = model.loss(X, xb, None)
-    assert close(total, g["f64.total"], 2e-5)
-    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+    assert close(total, g["f64.total"], TOL)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
     g = golden("helmholtz_tanh")
     model = patch(load_weights(po.Helmholtz2D([int(v) for v in g["layers"]], activation="tanh"), g).cuda())
     X = torch.tensor(g["X"], dtype=torch.float32, device="cuda")
     xb, ub = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda"), torch.tensor(g["ub"], dtype=torch.float32, device="cuda")
     total = model.compute_loss(X, xb, ub, float(g["k"]))
-    assert close(total, g["f64.total"], 2e-5)
-    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+    assert close(total, g["f64.total"], TOL)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 def _relobralo_check(model, g, tol_scale=1.0):
@@ -322,12 +337,12 @@ def _relobralo_check(model, g, tol_scale=1.0):
     torch.manual_seed(77)
     for c in range(int(g["calls"])):
         total, data, riesz, pde, norm = model.total_loss(X, xb, bv, eta)
-        assert close(total, g[f"f64.c{c}.total"], 2 * TOL * tol_scale), (c, float(total), float(g[f"f64.c{c}.total"]))
-        assert rel_err(np.array(model.lambdas), g[f"f64.c{c}.lambdas"]) < 2 * TOL * tol_scale, c
+        assert close(total, g[f"f64.c{c}.total"], TOL * tol_scale), (c, float(total), float(g[f"f64.c{c}.total"]))
+        assert rel_err(np.array(model.lambdas), g[f"f64.c{c}.lambdas"]) < TOL * tol_scale, c
     grads = model_grads(model, total)
     _, res, lam = model.pde_loss(X, model.forward(X), eta)
     for key, val in dict(data=data, riesz=riesz, pde=pde, sym=model.symmetry_loss(X), mu=lam).items():
-        assert close(val, g[f"f64.{key}"], 2 * TOL * tol_scale), (key, float(val), float(g[f"f64.{key}"]))
+        assert close(val, g[f"f64.{key}"], TOL * tol_scale), (key, float(val), float(g[f"f64.{key}"]))
     assert abs(float(norm) - float(g["f64.norm"])) <= 1e-4 * abs(float(g["f64.norm"])) + 1e-9
     assert rel_err(res.detach().cpu().numpy(), g["f64.residual"]) < 5 * TOL * tol_scale
     assert rel_err(flat(grads), flat(golden_grads(g, "f64.grads"))) < GTOL * tol_scale
@@ -345,7 +360,7 @@ def test_compat_relobralo_2d(golden):
     """The same file through patch(): its own loss code (Hessian.(1,1) by nested autograd.grad) on the jet node."""
     from gpe_b200.models import patch
     g = golden("g2d_relobralo_eta10")
-    _relobralo_check(patch(load_weights(po.ReLoBRaLoGPE2D([int(v) for v in g["layers"]]), g).cuda()), g, tol_scale=2.5)
+    _relobralo_check(patch(load_weights(po.ReLoBRaLoGPE2D([int(v) for v in g["layers"]]), g).cuda()), g, tol_scale=1.0)
 
 
 def test_g2d_minimal(golden):
@@ -356,7 +371,7 @@ def test_g2d_minimal(golden):
     X = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
     xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
     total = model.total_loss(X, xb, None)
-    assert close(total, g["f64.total"], 2 * TOL)
+    assert close(total, g["f64.total"], TOL)
     assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
@@ -382,8 +397,30 @@ def test_compat_helmholtz_circle(golden):
     assert rel_err(du.detach().cpu().numpy(), g["f32.du"]) < 1e-5
     assert rel_err(d2.detach().cpu().numpy(), g["f32.d2"]) < 1e-5
     got = model.loss_PDE(X)
-    assert close(got, want, 2e-5), (float(got), float(want))
-    assert rel_err(flat(model_grads(model, got)), want_g) < 5e-5
+    assert close(got, want, TOL), (float(got), float(want))
+    assert rel_err(flat(model_grads(model, got)), want_g) < GTOL
+
+
+def test_compat_helmholtz_circle_2_and_3(golden):
+    """S/helmholtz_2D_circle_2.py and _circle_3.py through patch(): the files' own polar losses run unchanged on the
+    kernel's u, grad u and Hessian (FULL jet); truth = the oracle in float64, pinned to the real classes in
+    test_oracle_golden.test_helmholtz_circle_2_and_3."""
+    from gpe_b200.models import patch
+    g = golden("helmholtz_circle_2")
+    layers = [int(v) for v in g["layers"]]
+    ref = load_weights(po.HelmholtzCircle2(layers, lb=g["lb"], ub=g["ub"]), g).double()
+    want = ref.loss_PDE(torch.tensor(g["X"], dtype=torch.float64), 1, 1)
+    want_g = flat(model_grads(ref, want))
+    model = patch(load_weights(po.HelmholtzCircle2(layers, lb=g["lb"], ub=g["ub"]), g).cuda(), input_lb=g["lb"], input_ub=g["ub"])
+    got = model.loss_PDE(torch.tensor(g["X"], dtype=torch.float32, device="cuda"), 1, 1)
+    assert close(got, want, TOL), (float(got), float(want))
+    assert rel_err(flat(model_grads(model, got)), want_g) < GTOL
+    g = golden("helmholtz_circle_3")
+    layers = [int(v) for v in g["layers"]]
+    model = patch(load_weights(po.HelmholtzCircle3(layers), g).cuda())
+    got = model.loss_pde(torch.tensor(g["X"], dtype=torch.float32, device="cuda"), int(g["n"]), float(g["k"]))
+    assert close(got, g["f64.pde"], TOL), (float(got), float(g["f64.pde"]))
+    assert rel_err(flat(model_grads(model, got)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 def test_helmholtz_learnable_k(golden):
@@ -399,7 +436,7 @@ def test_helmholtz_learnable_k(golden):
     pred = model.forward(X)
     terms = dict(pde=model.pde_loss(X, pred), riesz=model.riesz_loss(pred, X), bc=model.loss_BC(xb, yb), total=model.loss(xb, yb, X))
     for key, val in terms.items():
-        assert close(val, g[f"f64.{key}"], 2 * TOL), (key, float(val), float(g[f"f64.{key}"]))
+        assert close(val, g[f"f64.{key}"], TOL), (key, float(val), float(g[f"f64.{key}"]))
     grads, ref = model_grads(model, terms["total"]), golden_grads(g, "f64.grads")
     assert rel_err(flat(grads), flat(ref)) < GTOL
     for i in (0, 1):                                   # the two scalar parameters on their own
@@ -416,8 +453,8 @@ def test_compat_helmholtz_learnable_k(golden):
     xb = torch.tensor(g["Xb"], dtype=torch.float32, device="cuda")
     yb = torch.tensor(g["yb"], dtype=torch.float32, device="cuda")
     total = model.loss(xb, yb, X)
-    assert close(total, g["f64.total"], 2e-5)
-    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < 5e-5
+    assert close(total, g["f64.total"], TOL)
+    assert rel_err(flat(model_grads(model, total)), flat(golden_grads(g, "f64.grads"))) < GTOL
 
 
 def test_helmholtz2d_input_scaling():
@@ -434,8 +471,8 @@ def test_helmholtz2d_input_scaling():
     k = float(np.sqrt(2.0) * np.pi)
     want = ref.loss_pde(X64, k)
     got = gpu.loss_pde(X64.float().cuda().requires_grad_(True), k)
-    assert close(got, want, 2e-5), (float(got), float(want))
-    assert rel_err(flat(model_grads(gpu, got)), flat(model_grads(ref, want))) < 5e-5
+    assert close(got, want, TOL), (float(got), float(want))
+    assert rel_err(flat(model_grads(gpu, got)), flat(model_grads(ref, want))) < GTOL
 
 
 def test_reverse_kernel_runs_once_per_step(golden):

@@ -94,7 +94,8 @@ def test_final_fixture_mu_table(golden, kind):
 @pytest.mark.parametrize("name,kind", [("final_harmonic_g20_p3_m1", "harmonic"), ("final_harmonic_g5_p4_m2", "harmonic"),
                                        ("final_box_g10_p3_m0", "box"), ("final_gravity_g10_p3_m1", "gravity_well"),
                                        ("final_box_vanilla_g10_p3_m0", "box"), ("final_box_option_g5_p3_m1", "box"),
-                                       ("final_neg_gamma_shipped_m1_gm8", "harmonic")])
+                                       ("final_neg_gamma_shipped_m1_gm8", "harmonic"),
+                                       ("final_curriculum_shipped_m0_g20", "harmonic"), ("final_curriculum_shipped_m1_g60", "harmonic")])
 @pytest.mark.parametrize("tag", ["f64", "f32"])
 def test_final_random(golden, name, kind, tag):
     g = golden(name)
@@ -291,6 +292,24 @@ def test_helmholtz_circle(golden):
         loss = model.loss_PDE(torch.tensor(g["X"], dtype=dt))
         assert close(loss, g["f32.pde"], tol)
         assert rel_err(flat(model_grads(model, loss)), flat(golden_grads(g, "f32.grads"))) < tol
+
+
+def test_helmholtz_circle_2_and_3(golden):
+    """The other two disc files: S/helmholtz_2D_circle_2.py loss_PDE(x, n, m) (:108-160, LeakyReLU, inputs are
+    (r, theta); float32 only, its forward casts) and S/helmholtz_2D_circle_3.py loss_pde(x_f, n, k) (:58-110, tanh, polar
+    residual from Cartesian columns, d u_theta / d theta through the cos / sin nodes only)."""
+    g = golden("helmholtz_circle_2")
+    for dt, tol in ((torch.float32, 1e-6), (torch.float64, 1e-5)):
+        model = load_weights(po.HelmholtzCircle2([int(v) for v in g["layers"]], lb=g["lb"], ub=g["ub"]), g).to(dt)
+        loss = model.loss_PDE(torch.tensor(g["X"], dtype=dt), 1, 1)
+        assert close(loss, g["f32.pde"], tol)
+        assert rel_err(flat(model_grads(model, loss)), flat(golden_grads(g, "f32.grads"))) < tol
+    g = golden("helmholtz_circle_3")
+    for tag, dt, tol in (("f32", torch.float32, 1e-5), ("f64", torch.float64, 1e-9)):
+        model = load_weights(po.HelmholtzCircle3([int(v) for v in g["layers"]]), g).to(dt)
+        loss = model.loss_pde(torch.tensor(g["X"], dtype=dt), int(g["n"]), float(g["k"]))
+        assert close(loss, g[f"{tag}.pde"], tol)
+        assert rel_err(flat(model_grads(model, loss)), flat(golden_grads(g, f"{tag}.grads"))) < tol
 
 
 def test_nn_moment_identity(golden):
