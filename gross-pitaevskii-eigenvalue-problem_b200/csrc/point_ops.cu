@@ -214,6 +214,46 @@ int loss_grid(long long n) {
     return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
 
+// ---------------------------------------------------------------- fused scalar algebra of the loss terms
+// Every loss term of the reference (residual mean squares with a Rayleigh / energy-quotient mu inside, Riesz energies, the
+// [N,N]-broadcast factorisations, normalisation and symmetry terms) is a smooth function of the <= 3 x 32 moments.  The
+// host describes that function once as a straight-line program (gpe_b200/expr.py: nodes = constants, inputs, + - * /, neg,
+// sqrt); this kernel evaluates it in float64 together with its Jacobian by forward-mode differentiation -- thread j carries
+// d/d input_j through the program -- so a loss method costs two launches (moments, this) instead of ~60 fp64 ATen
+// kernels plus their autograd graph, and its backward is one [T] x [T, n_in] product.
+constexpr int kProgMaxNodes = 1024;
+enum { PROG_CONST = 0, PROG_INPUT = 1, PROG_ADD = 2, PROG_SUB = 3, PROG_MUL = 4, PROG_DIV = 5, PROG_NEG = 6, PROG_SQRT = 7 };
+
+__global__ void __launch_bounds__(128) scalar_program_kernel(const int* __restrict__ ops, const double* __restrict__ cval, int n_nodes,
+                                                             const double* __restrict__ in, int n_in, const int* __restrict__ outs,
+                                                             int n_out, double* __restrict__ vals, double* __restrict__ jac) {
+    // every thread evaluates the whole program (values are the same in all of them) and its own tangent column: no
+    // synchronisation; the node arrays live in local memory (a few hundred nodes: L1-resident)
+    double val[kProgMaxNodes], tan[kProgMaxNodes];
+    for (int j = threadIdx.x; j < n_in || j == (int)threadIdx.x; j += blockDim.x) {
+        for (int i = 0; i < n_nodes; ++i) {
+            const int op = ops[3 * i], a = ops[3 * i + 1], b = ops[3 * i + 2];
+            double v, t;
+            switch (op) {
+                case PROG_CONST: v = cval[i]; t = 0.0; break;
+                case PROG_INPUT: v = in[a]; t = (a == j) ? 1.0 : 0.0; break;
+                case PROG_ADD: v = val[a] + val[b]; t = tan[a] + tan[b]; break;
+                case PROG_SUB: v = val[a] - val[b]; t = tan[a] - tan[b]; break;
+                case PROG_MUL: v = val[a] * val[b]; t = tan[a] * val[b] + val[a] * tan[b]; break;
+                case PROG_DIV: v = val[a] / val[b]; t = (tan[a] - v * tan[b]) / val[b]; break;
+                case PROG_NEG: v = -val[a]; t = -tan[a]; break;
+                default: v = sqrt(val[a]); t = tan[a] / (2.0 * v); break;
+            }
+            val[i] = v;
+            tan[i] = t;
+        }
+        for (int k = 0; k < n_out; ++k) {
+            if (j < n_in) jac[(size_t)k * n_in + j] = tan[outs[k]];
+            if (j == 0) vals[k] = val[outs[k]];
+        }
+    }
+}
+
 }  // namespace
 }  // namespace gpe
 
@@ -257,3 +297,16 @@ int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, cons
 }
 
 }  // extern "C"
+
+extern "C" int gpe_scalar_program(const int32_t* ops, const double* consts, int n_nodes, const double* inputs, int n_in,
+                                  const int32_t* outs, int n_out, double* vals, double* jac, gpe_stream_t stream) {
+    gpe::NvtxRange range("gpe:scalar_program");
+    if (!ops || !consts || !inputs || !outs || !vals || !jac) { gpe::set_error("gpe_scalar_program: null pointer argument"); return -1; }
+    if (n_nodes < 1 || n_nodes > gpe::kProgMaxNodes) { gpe::set_error("gpe_scalar_program: %d nodes (1..%d)", n_nodes, gpe::kProgMaxNodes); return -1; }
+    if (n_in < 1 || n_out < 1) { gpe::set_error("gpe_scalar_program: n_in and n_out must be positive"); return -1; }
+    const int threads = n_in >= 128 ? 128 : (n_in + 31) / 32 * 32;
+    gpe::scalar_program_kernel<<<1, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(ops, consts, n_nodes, inputs, n_in, outs, n_out, vals, jac);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { gpe::set_error("scalar_program_kernel: %s", cudaGetErrorString(e)); return -4; }
+    return 0;
+}

@@ -304,6 +304,26 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> gram_adjoints(const c10::optional<Ten
     return {ub, gb, hb, nb};
 }
 
+// gpe::scalar_program: the loss terms and their Jacobian with respect to the moments, one launch
+std::tuple<Tensor, Tensor> scalar_program(const Tensor& ops, const Tensor& consts, const Tensor& inputs, const Tensor& outs) {
+    TORCH_CHECK(ops.is_cuda() && ops.scalar_type() == at::kInt && ops.is_contiguous() && ops.dim() == 2 && ops.size(1) == 3,
+                "gpe_b200: `ops` must be a contiguous CUDA int32 tensor [n, 3]");
+    TORCH_CHECK(consts.is_cuda() && consts.scalar_type() == at::kDouble && consts.is_contiguous() && consts.numel() == ops.size(0),
+                "gpe_b200: `consts` must be a contiguous CUDA float64 tensor [n]");
+    TORCH_CHECK(inputs.is_cuda() && inputs.scalar_type() == at::kDouble && inputs.is_contiguous() && inputs.dim() == 1,
+                "gpe_b200: `inputs` must be a contiguous CUDA float64 vector");
+    TORCH_CHECK(outs.is_cuda() && outs.scalar_type() == at::kInt && outs.is_contiguous() && outs.dim() == 1,
+                "gpe_b200: `outs` must be a contiguous CUDA int32 vector");
+    c10::cuda::CUDAGuard guard(inputs.device());
+    const int64_t T = outs.numel(), n_in = inputs.numel();
+    Tensor vals = at::empty({T}, inputs.options()), jac = at::empty({T, n_in}, inputs.options());
+    auto stream = reinterpret_cast<gpe_stream_t>(at::cuda::getCurrentCUDAStream().stream());
+    check_rc(gpe_scalar_program(ops.data_ptr<int32_t>(), consts.data_ptr<double>(), (int)ops.size(0), inputs.data_ptr<double>(), (int)n_in,
+                                outs.data_ptr<int32_t>(), (int)T, vals.data_ptr<double>(), jac.data_ptr<double>(), stream),
+             "gpe_scalar_program");
+    return {vals, jac};
+}
+
 double ffma_probe(int64_t mode, int64_t iters, const Tensor& sink) {
     TORCH_CHECK(sink.is_cuda() && sink.scalar_type() == at::kFloat && sink.numel() >= 1, "sink must be a CUDA float tensor");
     c10::cuda::CUDAGuard guard(sink.device());
@@ -470,6 +490,7 @@ TORCH_LIBRARY(gpe, m) {
     m.def("gram_adjoints(Tensor? x, Tensor u, Tensor? g, Tensor? h, Tensor? base, Tensor? V, Tensor? q, Tensor? nm, int d, "
           "int nl_kind, float nl_power, float scale, int bfactor, int sym_sign, int lap_cols, Tensor c) -> "
           "(Tensor, Tensor, Tensor, Tensor)");
+    m.def("scalar_program(Tensor ops, Tensor consts, Tensor inputs, Tensor outs) -> (Tensor, Tensor)");
     m.def("ffma_probe(int mode, int iters, Tensor sink) -> float");
 }
 
@@ -480,6 +501,7 @@ TORCH_LIBRARY_IMPL(gpe, CUDA, m) {
     m.impl("mlp_jet_bwd_stashed", &mlp_jet_bwd_stashed);
     m.impl("gram_moments", &gram_moments);
     m.impl("gram_adjoints", &gram_adjoints);
+    m.impl("scalar_program", &scalar_program);
     m.impl("ffma_probe", &ffma_probe);
 }
 

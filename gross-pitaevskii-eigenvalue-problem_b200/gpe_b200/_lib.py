@@ -67,7 +67,7 @@ lib.gpe_gram_adjoints.argtypes = [_loss_p, _i64] + [_vp] * 8 + [_vp] + [_vp] * 4
 lib.gpe_ffma_probe.argtypes = [ctypes.c_int, ctypes.c_int, _vp, ctypes.POINTER(ctypes.c_double), _vp]
 EXPORTS = ("gpe_version", "gpe_last_error", "gpe_workspace_bytes", "gpe_mlp_jet_fwd", "gpe_mlp_jet_bwd",
            "gpe_gram_moments", "gpe_gram_adjoints", "gpe_ffma_probe", "gpe_set_tensor_path", "gpe_tc_profile",
-           "gpe_tc_timings", "gpe_stash_bytes", "gpe_mlp_jet_fwd_stash", "gpe_mlp_jet_bwd_stashed")
+           "gpe_tc_timings", "gpe_stash_bytes", "gpe_mlp_jet_fwd_stash", "gpe_mlp_jet_bwd_stashed", "gpe_scalar_program")
 for _f in EXPORTS[2:]:
     getattr(lib, _f).restype = ctypes.c_int
 

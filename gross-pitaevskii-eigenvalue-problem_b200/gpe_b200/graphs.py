@@ -11,7 +11,9 @@ CUDA graph.  Measured on B200, config 1 with the root-notebook loop body: 3.6 ms
     for epoch in range(n):
         loss, mu = step()            # replays; the returned tensors are static buffers, overwritten by the next replay
 
-Rules (CUDA graphs): tensor shapes and the python control flow of the step must not change between replays; use
+Rules (CUDA graphs): drop every reference to losses / outputs of earlier EAGER steps on the same parameters before
+constructing a GraphedStep (a live loss keeps its graph, whose AccumulateGrad nodes stay bound to the eager stream, and
+the capture fails with "legacy stream depend on a capturing blocking stream"); tensor shapes and the python control flow of the step must not change between replays; use
 `torch.optim.Adam(..., capturable=True)`; read results with `.item()`/`float()` only outside the step function
 (e.g. every k-th epoch for the early-stop test); scalars that change per stage (gamma of the curriculum) must be
 device tensors updated in place with `.fill_()` / `.copy_()`.  Evaluating the model between replays (monitoring every
@@ -33,6 +35,8 @@ class GraphedStep:
                 if "capturable" in group and not group["capturable"]:
                     raise ValueError("construct the optimizer with capturable=True to capture its step in a CUDA graph")
         self.fn = fn
+        import gc
+        gc.collect()      # autograd graphs of earlier eager steps pin their AccumulateGrad nodes to the stream they ran on
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):          # warm-up on a side stream: lazy initialisation, allocator pools, plan caches

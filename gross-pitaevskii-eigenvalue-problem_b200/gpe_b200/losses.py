@@ -11,9 +11,30 @@ second moments does not suffer the fp32 cancellation SURVEY.md fact 7 warns abou
 With a process group, the moment vector is all-reduced (SUM) first; m[(1,1)] is then the global
 point count, so every mean below is a global mean.
 """
+import os
+
 import torch
 
 from ._lib import (F_LAP, F_NL, F_ONE, F_Q, F_U, F_V, F_VU, MOM_GRAD2, MOM_NN2, MOM_SYM2, NFEAT, mom)
+
+
+def sqrt(v):
+    """Square root of a float64 torch scalar or of a recorded scalar (expr.Expr)."""
+    return torch.sqrt(v) if isinstance(v, torch.Tensor) else v ** 0.5
+
+
+def fused_terms(moments, build, key=None):
+    """The terms `build(*M)` of one loss method as float64 0-dim tensors.  `moments`: Moments objects (one per moment
+    vector the terms read).  On CUDA the arithmetic is recorded once and runs as ONE kernel that also returns the
+    Jacobian with respect to the moments (expr.py, `gpe::scalar_program`) -- GPE_FUSED_TERMS=0 keeps the float64 torch
+    scalars (one small kernel per operator), which is also what CPU moment vectors (the host-logic tests) get."""
+    if moments[0].m.is_cuda and os.environ.get("GPE_FUSED_TERMS", "1") != "0":
+        from . import expr
+        try:
+            return expr.evaluate([M.m for M in moments], build, key)
+        except TypeError:
+            pass        # a coefficient arrived as a tensor (e.g. a learnable wave number): torch scalars carry its gradient
+    return tuple(build(*moments))
 
 
 class Moments:

@@ -199,7 +199,7 @@ class JetMLP(nn.Module):
         um = self.jets(x, derivs=False, xform=(tuple(a), tuple(b)))[0]
         m = ops.gram_moments(u, None, None, um, d=x.shape[1], sym_sign=sign)
         M = L.Moments(gdist.all_reduce_sum(m, self.group))
-        return (M.sym2 / M.n).float()
+        return L.fused_terms([M], lambda S: [S.sym2 / S.n], key=("sym",))[0].float()
 
 
 def _col(t):
@@ -260,7 +260,31 @@ def _hermite_norm(n):
     return (2.0 ** n * math.factorial(n) * math.sqrt(math.pi)) ** (-0.5)
 
 
+# Base states depend on the collocation tensor only: a training loop evaluates them on the same tensor every epoch (the
+# reference recomputes them per call, through scipy on the host).  Small cache keyed by the tensor's identity, version and
+# storage; entries die with their tensor.
+_base_cache = {}
+
+
+def _cached_base(kind, x, args, fn):
+    import weakref
+    key = (kind, id(x), x._version, x.data_ptr(), tuple(x.shape)) + tuple(args)
+    hit = _base_cache.get(key)
+    if hit is not None and hit[0]() is x:
+        return hit[1]
+    out = fn()
+    if len(_base_cache) >= 16:
+        _base_cache.pop(next(iter(_base_cache)))
+    _base_cache[key] = (weakref.ref(x), out)
+    return out
+
+
 def hermite_base_jets(x, n, const_h):
+    """Cached `_hermite_base_jets` (see there)."""
+    return _cached_base("hermite", x, (int(n), bool(const_h)), lambda: _hermite_base_jets(x, n, const_h))
+
+
+def _hermite_base_jets(x, n, const_h):
     """[N,3] = (psi, psi', psi'') of psi_n(x) = c_n H_n(x) exp(-x^2/2), evaluated in fp64.
     const_h=True reproduces the reference's scipy variant, where H_n is a constant for autograd and only
     the Gaussian is differentiated (NBroot cell 6:41-48): psi' = -x psi,
@@ -280,7 +304,11 @@ def hermite_base_jets(x, n, const_h):
 
 
 def box_base_jets(x, n, length):
-    """sqrt(2/L) sin((n+1) pi x / L) and its analytic derivatives (R/box_pinn_simulation.py:141-180)."""
+    """sqrt(2/L) sin((n+1) pi x / L) and its analytic derivatives (R/box_pinn_simulation.py:141-180); cached per tensor."""
+    return _cached_base("box", x, (int(n), float(length)), lambda: _box_base_jets(x, n, length))
+
+
+def _box_base_jets(x, n, length):
     xd = x.detach().reshape(-1).double()
     k, c = (n + 1) * math.pi / length, math.sqrt(2.0 / length)
     s, co = torch.sin(k * xd), torch.cos(k * xd)
@@ -348,6 +376,11 @@ def airy_ai(x):
 
 
 def airy_base_jets(x, n):
+    """Cached `_airy_base_jets` (see there)."""
+    return _cached_base("airy", x, (int(n),), lambda: _airy_base_jets(x, n))
+
+
+def _airy_base_jets(x, n):
     """[N,3] = (psi, psi', psi'') of the gravity-well base psi_n = Ai(x + alpha_n) / sqrt(sum(Ai^2) dx), as
     R/gravity_well_pinn_simulation.py:135-160 builds it -- dx = x[1] - x[0] of the (float32) grid it is given,
     psi'' = np.gradient(psi', dx) (a finite difference, not the Airy equation), float64 arithmetic, cast to float32 -- but
@@ -376,8 +409,12 @@ class _GPE1DBase(JetMLP):
         """Shared fused pde_loss: returns (mse, mu, Moments)."""
         M = self._moments(inputs, base=base, V=V, scale=scale, nl_kind=nl_kind, nl_power=p, bfactor=bfactor)
         wH = L.hamiltonian_weights(kinetic, eta)
-        mu = L.rayleigh_mu(M, wH) if mu_kind == "rayleigh" else L.energy_mu(M, eta)
-        return L.residual_mse(M, wH, mu), mu, M
+
+        def build(S):
+            mu = L.rayleigh_mu(S, wH) if mu_kind == "rayleigh" else L.energy_mu(S, eta)
+            return [L.residual_mse(S, wH, mu), mu]
+        mse, mu = L.fused_terms([M], build, key=("pde1d", float(kinetic), float(eta), mu_kind))
+        return mse, mu, M
 
     def _full_fields(self, inputs, base, V, scale, kinetic, eta, nl, mu, bfactor=0):
         """Per-point full solution and residual as ordinary (differentiable) torch tensors [N,1], for the
@@ -493,14 +530,19 @@ class PaperGPE1D(RootGPE1D):
         """cell 6:82-131 -> (pde_loss, pde_residual [N,1], lambda_pde + mode, u [N,1])."""
         M, base, V, scale = self._paper_moments(inputs, predictions, p, potential_type, precomputed_potential)
         wH = L.hamiltonian_weights(-0.5, gamma)
-        mu = L.rayleigh_mu(M, wH)
+
+        def build(S):
+            mu_ = L.rayleigh_mu(S, wH)
+            return [L.residual_mse(S, wH, mu_), mu_]
+        mse, mu = L.fused_terms([M], build, key=("pde1d", -0.5, float(gamma), "rayleigh"))
         res, full = self._full_fields(inputs, base, V, scale, -0.5, gamma, _abs_pow(p), mu)
-        return L.residual_mse(M, wH, mu).float(), res, (mu + self.mode).float(), full
+        return mse.float(), res, (mu + self.mode).float(), full
 
     def riesz_loss(self, inputs, predictions, gamma, p, potential_type="harmonic", precomputed_potential=None):
         """cell 6:133-183 -> (E, E + mode, u); the grid spacing cancels between the sums and the norm factor."""
         M, base, V, scale = self._paper_moments(inputs, predictions, p, potential_type, precomputed_potential)
-        e = (0.5 * M.grad2 + M.P(L.F_U, L.F_VU) + (gamma / (p + 1)) * M.P(L.F_U, L.F_NL)) / M.P(L.F_U, L.F_U)
+        (e,) = L.fused_terms([M], lambda S: [(0.5 * S.grad2 + S.P(L.F_U, L.F_VU) + (gamma / (p + 1)) * S.P(L.F_U, L.F_NL)) / S.P(L.F_U, L.F_U)],
+                             key=("paper_riesz", float(gamma), float(p)))
         full = scale * self.jets(inputs)[0].unsqueeze(1) + base[:, :1]
         return e.float(), (e + self.mode).float(), full
 
@@ -748,14 +790,36 @@ class OptGPE1D(_GPE1DBase):
     def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None):
         """:239-282 (mean form)."""
         M = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction)[0]
-        return L.riesz_energy(M, eta, "mean").float()
+        return self._riesz_mean(M, eta)
+
+    @staticmethod
+    def _riesz_mean(M, eta, nl_coef=0.5):
+        return L.fused_terms([M], lambda S: [L.riesz_energy(S, eta, "mean", nl_coef)], key=("riesz_mean", float(eta), float(nl_coef)))[0].float()
+
+    @staticmethod
+    def _energy_pde(M, eta):
+        """(mean residual^2, mu) with the energy-quotient mu (:323, :341-346)."""
+        wH = L.hamiltonian_weights(-1.0, eta)
+
+        def build(S):
+            mu_ = L.energy_mu(S, eta)
+            return [L.residual_mse(S, wH, mu_), mu_]
+        return L.fused_terms([M], build, key=("pde1d", -1.0, float(eta), "energy"))
+
+    @staticmethod
+    def _opt_terms(M, eta, nl_coef=0.5):
+        """(riesz, pde, norm) of the five-term totals from one program."""
+        wH = L.hamiltonian_weights(-1.0, eta)
+
+        def build(S):
+            mu_ = L.energy_mu(S, eta)
+            return [L.riesz_energy(S, eta, "mean", nl_coef), L.residual_mse(S, wH, mu_), (L.sqrt(S.nn2) - 1.0) ** 2]
+        return L.fused_terms([M], build, key=("opt_terms", float(eta), float(nl_coef)))
 
     def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None):
         """:284-346 -> (pde_loss, pde_residual [N,1], lambda_pde); energy-quotient mu."""
         M, base, V, scale = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction)
-        wH = L.hamiltonian_weights(-1.0, eta)
-        mu = L.energy_mu(M, eta)
-        mse = L.residual_mse(M, wH, mu)
+        mse, mu = self._energy_pde(M, eta)
         res, _ = self._full_fields(inputs, base, V, scale, -1.0, eta, lambda u: torch.abs(u ** 2) * u, mu)
         return mse.float(), res, mu.float()
 
@@ -772,10 +836,7 @@ class OptGPE1D(_GPE1DBase):
         pred = self.forward(collocation_points)
         M, _, _, _ = self._M(collocation_points, pred, eta, potential_type, precomputed_potential, prev_prediction)
         data = self.boundary_loss(boundary_points, boundary_values, prev_prediction)
-        riesz = L.riesz_energy(M, eta, "mean").float()
-        mu = L.energy_mu(M, eta)
-        pde = L.residual_mse(M, L.hamiltonian_weights(-1.0, eta), mu).float()
-        norm = ((torch.sqrt(M.nn2) - 1.0) ** 2).float()
+        riesz, pde, norm = (t.float() for t in self._opt_terms(M, eta))
         sym = self.symmetry_loss(collocation_points, lb, ub)
         length = ub - lb
         terms = [data, riesz / length, pde / length, norm, sym]
@@ -799,9 +860,7 @@ class _OptAdditive(OptGPE1D):
         pred = self.forward(collocation_points)
         M, _, _, _ = self._M(collocation_points, pred, eta, potential_type, precomputed_potential, prev_prediction, p)
         data = self.boundary_loss(boundary_points, boundary_values, prev_prediction)
-        riesz = L.riesz_energy(M, eta, "mean", 0.5 if p is None else 2.0 / (p + 1)).float()
-        pde = L.residual_mse(M, L.hamiltonian_weights(-1.0, eta), L.energy_mu(M, eta)).float()
-        norm = ((torch.sqrt(M.nn2) - 1.0) ** 2).float()
+        riesz, pde, norm = (t.float() for t in self._opt_terms(M, eta, 0.5 if p is None else 2.0 / (p + 1)))
         return data, riesz, pde, norm, self.symmetry_loss(collocation_points, lb, ub)
 
 
@@ -830,15 +889,14 @@ class PowersGPE1D(_OptAdditive):
     def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, p=2):
         """:200-248: 1/2 (mean u'^2 + mean V u^2 + 2 eta/(p+1) mean |u|^(p+1))."""
         M = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, p)[0]
-        return L.riesz_energy(M, eta, "mean", 2.0 / (p + 1)).float()
+        return self._riesz_mean(M, eta, 2.0 / (p + 1))
 
     def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None, p=2):
         """:250-317 -> (pde_loss, pde_residual [N,1], lambda_pde)."""
         M, base, V, scale = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, p)
-        wH = L.hamiltonian_weights(-1.0, eta)
-        mu = L.energy_mu(M, eta)
+        mse, mu = self._energy_pde(M, eta)
         res, _ = self._full_fields(inputs, base, V, scale, -1.0, eta, _abs_pow(p), mu)
-        return L.residual_mse(M, wH, mu).float(), res, mu.float()
+        return mse.float(), res, mu.float()
 
     def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights, potential_type,
                    precomputed_potential=None, prev_prediction=None, p=2):
@@ -864,14 +922,13 @@ class ModesGPE1D(OptGPE1D):
 
     def riesz_loss(self, predictions, inputs, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
         M = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, None, mode)[0]
-        return L.riesz_energy(M, eta, "mean").float()
+        return self._riesz_mean(M, eta)
 
     def pde_loss(self, inputs, predictions, eta, potential_type, precomputed_potential=None, prev_prediction=None, mode=0):
         M, base, V, scale = self._M(inputs, predictions, eta, potential_type, precomputed_potential, prev_prediction, None, mode)
-        wH = L.hamiltonian_weights(-1.0, eta)
-        mu = L.energy_mu(M, eta)
+        mse, mu = self._energy_pde(M, eta)
         res, _ = self._full_fields(inputs, base, V, scale, -1.0, eta, lambda u: torch.abs(u ** 2) * u, mu)
-        return L.residual_mse(M, wH, mu).float(), res, mu.float()
+        return mse.float(), res, mu.float()
 
     def total_loss(self, collocation_points, boundary_points, boundary_values, eta, lb, ub, weights, potential_type,
                    precomputed_potential=None, prev_prediction=None, mode=0):
@@ -879,9 +936,7 @@ class ModesGPE1D(OptGPE1D):
         pred = self.forward(collocation_points)
         M = self._M(collocation_points, pred, eta, potential_type, precomputed_potential, prev_prediction, None, mode)[0]
         data = self.boundary_loss(boundary_points, boundary_values, prev_prediction, mode)
-        riesz = L.riesz_energy(M, eta, "mean").float()
-        pde = L.residual_mse(M, L.hamiltonian_weights(-1.0, eta), L.energy_mu(M, eta)).float()
-        norm = ((torch.sqrt(M.nn2) - 1.0) ** 2).float()
+        riesz, pde, norm = (t.float() for t in self._opt_terms(M, eta))
         length = ub - lb
         return data + pde / length + riesz / length + norm, data, riesz, pde, norm
 
@@ -929,36 +984,42 @@ class GPE2D(JetMLP):
                 self._jet_cache[key] = hit
         return hit[1], hit[2]
 
+    def _terms(self, M):
+        """(pde + L_f + L_lambda, mu, Riesz energy) from one program (:192-211, :146-149)."""
+        g_, ref = self.g, self.semantics == "reference"
+
+        def build(S):
+            if ref:
+                mu_ = L.g2d_reference_mu(S, g_)
+                mse_ = L.g2d_reference_residual_mse(S, g_, mu_)
+            else:
+                mu_ = L.energy_mu(S, g_)
+                mse_ = L.residual_mse(S, L.hamiltonian_weights(-1.0, g_), mu_)
+            return [mse_ + 1.0 / (S.mean(F_U, F_U) + 1e-2) + 1.0 / (mu_ ** 2 + 1e-6), mu_, L.riesz_energy(S, g_, "sum")]
+        return L.fused_terms([M], build, key=("g2d", float(g_), ref))
+
     def riesz_loss(self, predictions, inputs):
         """:112-151 (sum form)."""
-        return L.riesz_energy(self._M(inputs)[0], self.g, "sum").float()
+        return self._terms(self._M(inputs)[0])[2].float()
 
     def pde_loss(self, inputs, predictions):
         """:154-213 -> (pde_loss + L_f + L_lambda, pde_residual, lambda_pde)."""
         M, V = self._M(inputs)
-        if self.semantics == "reference":
-            mu = L.g2d_reference_mu(M, self.g)
-            mse = L.g2d_reference_residual_mse(M, self.g, mu)
-        else:
-            mu = L.energy_mu(M, self.g)
-            mse = L.residual_mse(M, L.hamiltonian_weights(-1.0, self.g), mu)
-        L_f = 1.0 / (M.mean(F_U, F_U) + 1e-2)
-        L_lambda = 1.0 / (mu ** 2 + 1e-6)
+        pde_all, mu, _ = self._terms(M)
         u, g, h = self.jets(inputs)
         lap, uc = h[:, 0], u.unsqueeze(1)
         if self.semantics == "reference" and inputs.shape[0] <= 4096:     # the reference's [N,N] residual
             res = -lap + V * uc + self.g * torch.abs(uc ** 2) * uc - mu.float() * uc
         else:                                                            # [N,1]; an [N,N] matrix cannot exist at scale
             res = -lap.unsqueeze(1) + V.unsqueeze(1) * uc + self.g * torch.abs(uc ** 2) * uc - mu.float() * uc
-        return (mse + L_f + L_lambda).float(), res, mu.float()
+        return pde_all.float(), res, mu.float()
 
     def loss(self, x, x_bc, u_bc):
-        """:215-242."""
+        """:215-242 (one program gives pde + L_f + L_lambda and the Riesz energy; the [N,1] residual field of pde_loss is not
+        built here: nobody would read it)."""
         data = self.boundary_loss(x_bc, u_bc)
-        M, _ = self._M(x)
-        riesz = L.riesz_energy(M, self.g, "sum").float()
-        pde, _, _ = self.pde_loss(x, None)
-        return data + pde + riesz
+        pde, _, riesz = self._terms(self._M(x)[0])
+        return data + pde.float() + riesz.float()
 
     total_loss = loss            # S/gross_pitaevskii_2D_minimal.py:201-222: the same sum under another name
 
@@ -1019,17 +1080,25 @@ class ReLoBRaLoGPE2D(JetMLP):
 
     def riesz_loss(self, predictions, inputs, eta):
         """:147-180 (means over the [N,2] tables)."""
-        (M0, M1), _ = self._M2(inputs)
-        n = M0.n
-        e = 0.5 * (M0.grad2 / (2.0 * n) + (M0.P(F_U, F_VU) + M1.P(F_U, F_VU)) / (2.0 * n) + 0.5 * eta * M0.P(F_U, F_NL) / n)
-        return e.float()
+        Ms, _ = self._M2(inputs)
+        return self._rb_terms(Ms, eta)[0].float()
+
+    def _rb_terms(self, Ms, eta):
+        """(riesz, pde, lambda, norm) of the two residual columns from one program over both moment vectors."""
+        wH = L.hamiltonian_weights(-1.0, eta)
+
+        def build(S0, S1):
+            n = S0.n
+            e = 0.5 * (S0.grad2 / (2.0 * n) + (S0.P(F_U, F_VU) + S1.P(F_U, F_VU)) / (2.0 * n) + 0.5 * eta * S0.P(F_U, F_NL) / n)
+            lam = self._lambda((S0, S1), eta)
+            mse = 0.5 * (L.residual_mse(S0, wH, lam) + L.residual_mse(S1, wH, lam))
+            return [e, mse, lam, (L.sqrt(S0.nn2) - 1.0) ** 2]
+        return L.fused_terms(list(Ms), build, key=("relobralo", float(eta)))
 
     def pde_loss(self, inputs, predictions, eta):
         """:182-230 -> (pde_loss, pde_residual [N,2], lambda_pde)."""
         Ms, V = self._M2(inputs)
-        lam = self._lambda(Ms, eta)
-        wH = L.hamiltonian_weights(-1.0, eta)
-        mse = 0.5 * (L.residual_mse(Ms[0], wH, lam) + L.residual_mse(Ms[1], wH, lam))
+        _, mse, lam, _ = self._rb_terms(Ms, eta)
         u, g, h = self.jets(inputs)
         uc = u.unsqueeze(1)
         res = -(h[:, :2] + h[:, 2:3]) + V * uc + eta * torch.abs(uc ** 2) * uc - lam.float() * uc
@@ -1093,7 +1162,7 @@ class ReLoBRaLoGPE2D(JetMLP):
         data = self.boundary_loss(boundary_points, boundary_values)
         riesz = self.riesz_loss(None, collocation_points, eta)
         pde, _, _ = self.pde_loss(collocation_points, None, eta)
-        norm = ((torch.sqrt(self._M2(collocation_points)[0][0].nn2) - 1.0) ** 2).float()
+        norm = self._rb_terms(self._M2(collocation_points)[0], eta)[3].float()
         sym = self.symmetry_loss(collocation_points)
         losses = [data, riesz, pde, norm, sym]
         if self.device_weights:
@@ -1132,7 +1201,9 @@ class Helmholtz2D(JetMLP):
         xd = x_f.detach()
         q = (k ** 2 * torch.sin(self.a1 * np.pi * xd[:, 0]) * torch.sin(self.a2 * np.pi * xd[:, 1])).float().contiguous()
         M = self._moments(x_f, q=q, derivs=True)
-        mse = L.helmholtz_reference_mse(M, k ** 2) if self.semantics == "reference" else L.helmholtz_pointwise_mse(M, k ** 2)
+        ref, k2 = self.semantics == "reference", float(k) ** 2
+        (mse,) = L.fused_terms([M], lambda S: [L.helmholtz_reference_mse(S, k2) if ref else L.helmholtz_pointwise_mse(S, k2)],
+                               key=("helmholtz", k2, ref))
         return mse.float()
 
     def loss_data(self, x_u, u_true):

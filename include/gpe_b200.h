@@ -160,6 +160,18 @@ int gpe_gram_adjoints(const gpe_loss_desc* desc, int64_t n, const float* x, cons
                       const double* c, float* u_bar, float* g_bar, float* h_bar, float* nm_bar,
                       gpe_stream_t stream);
 
+/* ---- fused scalar algebra of the loss terms ------------------------------------------------------
+ * The loss methods of the reference end in scalar arithmetic on the reduced quantities (mu = <u,Hu>/<u,u>, mean r^2, the
+ * Riesz energy, 1/(mu^2 + 1e-6) ...: NBroot cell 6:117-125, R/harmonic_pinn_simulation.py:186-196,
+ * S/gross_pitaevskii_2D.py:192-211, S/helmholtz_2D.py:84-89).  Here that arithmetic is a straight-line program over the
+ * moment vector(s): node i = (ops[3i], ops[3i+1], ops[3i+2]) = (opcode, a, b) with opcodes GPE_PROG_*; CONST takes
+ * consts[i], INPUT reads inputs[a], the others combine earlier nodes a (and b).  Evaluated in float64 together with the
+ * Jacobian d vals / d inputs (forward mode): vals [n_out], jac [n_out, n_in] row-major.  All pointers device pointers. */
+enum { GPE_PROG_CONST = 0, GPE_PROG_INPUT = 1, GPE_PROG_ADD = 2, GPE_PROG_SUB = 3, GPE_PROG_MUL = 4, GPE_PROG_DIV = 5,
+       GPE_PROG_NEG = 6, GPE_PROG_SQRT = 7, GPE_PROG_MAX_NODES = 1024 };
+int gpe_scalar_program(const int32_t* ops, const double* consts, int n_nodes, const double* inputs, int n_in,
+                       const int32_t* outs, int n_out, double* vals, double* jac, gpe_stream_t stream);
+
 /* ---- tensor-core (tcgen05) path control ----
  * The 3xTF32 tensor path is the GPE_PREC_AUTO default wherever it applies (64 < width <= 128, Laplacian jets, <= 3 hidden
  * matrices); GPE_TENSOR=0 in the environment or gpe_set_tensor_path(0) makes GPE_PREC_AUTO select the FFMA kernels instead

@@ -280,6 +280,11 @@ def test_relobralo_weights_on_the_device(golden):
     gh = torch.autograd.grad(th, list(host.parameters()))
     gd = torch.autograd.grad(td, list(dev.parameters()))
     assert _rel(torch.cat([t.reshape(-1) for t in gd]), torch.cat([t.reshape(-1) for t in gh])) < 1e-5
+    # a live loss tensor keeps the AccumulateGrad nodes of its parameters bound to the stream it was made on, which a later
+    # capture on another stream must not touch: drop every reference to the eager graphs first
+    del th, td, gh, gd
+    import gc
+    gc.collect()
     opt = torch.optim.Adam(dev.parameters(), lr=1e-4, capturable=True)
 
     def body():
@@ -291,3 +296,66 @@ def test_relobralo_weights_on_the_device(golden):
     step = GraphedStep(body, opt, warmup=2)
     vals = [float(step()) for _ in range(20)]
     assert np.isfinite(vals).all() and len(set(vals)) > 10                      # the replays step the weights and the lambdas
+
+
+# ------------------------------------------------------------------------------------------- fused scalar algebra
+def test_fused_loss_terms_match_the_torch_scalar_algebra(golden):
+    """gpe::scalar_program (one launch: every term of a loss method + its Jacobian w.r.t. the moments, forward mode) against
+    the float64 torch scalars it replaces (GPE_FUSED_TERMS=0): values to 1e-13, parameter gradients to 1e-9, for the
+    Rayleigh family, the energy family with its five-term total, the 2-D [N,N] semantics and Helmholtz."""
+    import gpe_b200
+
+    def both(make, run):
+        out = {}
+        for flag in ("0", "1"):
+            with _Env(GPE_FUSED_TERMS=flag):
+                model = make()
+                terms = run(model)
+                total = sum(t.double().sum() for t in terms)
+                grads = torch.autograd.grad(total, [p for p in model.parameters()], allow_unused=True)
+                out[flag] = ([float(t.double().sum()) for t in terms], torch.cat([g.reshape(-1).double() for g in grads if g is not None]))
+        for a, b in zip(out["1"][0], out["0"][0]):
+            assert abs(a - b) <= 1e-6 * abs(b) + 1e-30, (a, b)          # .float() of identical float64 values
+        assert _rel(out["1"][1], out["0"][1]) < 1e-6
+
+    g = golden("root_m1_p3")
+    X1 = torch.tensor(g["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    lb, ub = float(g["lb"]), float(g["ub"])
+    bp, bv = torch.tensor([[lb], [ub]], device="cuda"), torch.zeros(2, 1, device="cuda")
+    both(lambda: load_weights(gpe_b200.RootGPE1D([int(v) for v in g["layers"]], mode=int(g["mode"]), gamma=float(g["gamma"])), g).cuda(),
+         lambda m: po.root_train_terms(m, X1, bp, bv, float(g["dx"]), float(g["gamma"]), int(g["p"]), lb, ub)[:5])
+    g2 = golden("opt_m1_eta50")
+    X2 = torch.tensor(g2["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    both(lambda: load_weights(gpe_b200.OptGPE1D([int(v) for v in g2["layers"]], g=50.0, mode=1), g2).cuda(),
+         lambda m: m.total_loss(X2, bp, bv, 50.0, -10.0, 10.0, [50.0, 1.0, 2.0, 10.0, 25.0], "harmonic")[:5] + (m.last_weighted_sum,))
+    g3 = golden("g2d_g100")
+    X3 = torch.tensor(g3["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    Xb = torch.tensor(g3["Xb"], dtype=torch.float32, device="cuda")
+    for sem in ("reference", "pointwise"):
+        both(lambda: load_weights(gpe_b200.GPE2D([int(v) for v in g3["layers"]], g=float(g3["g"]), semantics=sem), g3).cuda(),
+             lambda m: (m.loss(X3, Xb, None), m.pde_loss(X3, None)[2], m.riesz_loss(None, X3)))
+    g4 = golden("helmholtz_tanh")
+    X4 = torch.tensor(g4["X"], dtype=torch.float32, device="cuda", requires_grad=True)
+    for sem in ("reference", "pointwise"):
+        both(lambda: load_weights(gpe_b200.Helmholtz2D([int(v) for v in g4["layers"]], activation="tanh", semantics=sem), g4).cuda(),
+             lambda m: (m.loss_pde(X4, float(g4["k"])),))
+
+
+def test_scalar_program_against_autograd():
+    """The opcode interpreter itself: a program with every opcode against torch autograd in float64."""
+    from gpe_b200 import expr
+    torch.manual_seed(3)
+    m = (torch.rand(32, dtype=torch.float64, device="cuda") + 0.5).requires_grad_(True)
+
+    def f(S):
+        a, b, c = S.P(1, 1), S.grad2, S.nn2
+        return [(a * b - c) / (a + 2.0) + (-b) * 0.25 + (c + a) ** 0.5, (a - b) ** 3 / c, 3.0 - a]
+    got = expr.evaluate([m], f)
+    from gpe_b200.losses import Moments
+    want = f(Moments(m))
+    for a, b in zip(got, want):
+        assert abs(float(a) - float(b)) <= 1e-14 * abs(float(b))
+    w = torch.tensor([0.3, -1.7, 2.2], dtype=torch.float64, device="cuda")
+    ga = torch.autograd.grad((torch.stack(list(got)) * w).sum(), m)[0]
+    gb = torch.autograd.grad(sum(wi * t for wi, t in zip(w, want)), m)[0]
+    assert float((ga - gb).abs().max()) <= 1e-13 * float(gb.abs().max())
