@@ -58,21 +58,35 @@ def main():
         gdist.all_reduce_gradients(params, group)
         return float(loss), float(mu), torch.cat([p.grad.reshape(-1) for p in params]).double()
 
+    def boundary_only(group):
+        """Gradient of the replicated boundary term alone (it must be counted once, not `world` times --
+        in the full gradient the Riesz term hides it)."""
+        model.group = group
+        for p in params:
+            p.grad = None
+        model.boundary_loss(Xb, None).backward()
+        gdist.all_reduce_gradients(params, group)
+        return torch.cat([p.grad.reshape(-1) for p in params]).double()
+
     loss1, mu1, g1 = evaluate(X_all, solo)
+    b1 = boundary_only(solo)
     lo, hi = gdist.shard_bounds(args.points, rank, world)
     lossN, muN, gN = evaluate(X_all[lo:hi].contiguous(), None)
+    bN = boundary_only(None)
     rel = float((gN - g1).norm() / g1.norm())
+    rel_b = float((bN - b1).norm() / b1.norm())
     gmin, gmax = gN.clone(), gN.clone()
     dist.all_reduce(gmin, op=dist.ReduceOp.MIN)
     dist.all_reduce(gmax, op=dist.ReduceOp.MAX)
-    worst = torch.tensor([abs(lossN - loss1) / abs(loss1), abs(muN - mu1) / abs(mu1), rel], device=dev, dtype=torch.float64)
+    worst = torch.tensor([abs(lossN - loss1) / abs(loss1), abs(muN - mu1) / abs(mu1), rel, rel_b], device=dev, dtype=torch.float64)
     dist.all_reduce(worst, op=dist.ReduceOp.MAX)
-    ok = bool(worst[0] < 1e-5 and worst[1] < 1e-6 and worst[2] < 1e-5 and torch.equal(gmin, gmax))
+    ok = bool(worst[0] < 1e-5 and worst[1] < 1e-6 and worst[2] < 1e-5 and worst[3] < 1e-6 and torch.equal(gmin, gmax))
     if rank == 0:
         line = {"n_gpus": world, "points": args.points, "shard_sizes": [gdist.shard_bounds(args.points, r, world)[1] -
                                                                        gdist.shard_bounds(args.points, r, world)[0] for r in range(world)],
                 "loss_single": loss1, "loss_sharded": lossN, "mu_single": mu1, "mu_sharded": muN,
                 "rel_loss": float(worst[0]), "rel_mu": float(worst[1]), "rel_grad": float(worst[2]),
+                "rel_grad_boundary_term_only": float(worst[3]),
                 "ranks_hold_identical_gradients": bool(torch.equal(gmin, gmax)), "ok": ok}
         os.write(real_stdout, (json.dumps(line) + "\n").encode())
     dist.destroy_process_group()
