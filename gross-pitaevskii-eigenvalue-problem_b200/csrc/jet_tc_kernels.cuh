@@ -1332,31 +1332,24 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
                         const uint32_t dcol = k2ColD + 128u * (g % 3u);
                         mbar_wait(&d_full[g % 3u], (g / 3u) & 1u);
                         tc_fence_after();
-                        float xin[D];
-                        if (l == 0) {
-#pragma unroll
-                            for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
-                        }
                         uint32_t nLo[4], nHi[4];
                         IO::ld(lane_lo + dcol + kCw * sub, nLo);
                         IO::ld(lane_hi + dcol + kCw * sub, nHi);
+                        if (l >= 1) {
+                            // ---- middle layers ----
 #pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const int f = 32 * c + fb;
-                            float nxt[8];
-                            if (l >= 1) {
+                            for (int c = 0; c < 4; ++c) {
+                                float nxt[8];
                                 if (c < 3) load_stash(sb, l, c + 1, nxt);
                                 else if (has_next) load_stash(sbn, ln, 0, nxt);
-                            }
-                            tmem_wait_ld();
-                            uint32_t LoHi[4], HiHi[4];
+                                tmem_wait_ld();
+                                uint32_t LoHi[4], HiHi[4];
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
-                            if (c < 3) {
-                                IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
-                                IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
-                            }
-                            if (l >= 1) {
+                                for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                                if (c < 3) {
+                                    IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                                    IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
+                                }
                                 float ab[2][R];
 #pragma unroll
                                 for (int e = 0; e < 2; ++e) {
@@ -1372,8 +1365,23 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
                                 hand_over(ab);
 #pragma unroll
                                 for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
-                            } else {
-                                // input layer: forward jets from x; dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val
+                            }
+                        } else {
+                            // ---- input layer: forward jets from x; dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val ----
+                            float xin[D];
+#pragma unroll
+                            for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                const int f = 32 * c + fb;
+                                tmem_wait_ld();
+                                uint32_t LoHi[4], HiHi[4];
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                                if (c < 3) {
+                                    IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                                    IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
+                                }
                                 const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
                                 float2 w2[D];
 #pragma unroll
