@@ -579,124 +579,153 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
             GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 3);
             ++nch;
         };
-        for (int it = 0; it < iters; ++it) {
-            long long pt[2];
-            bool vt[2], st_ok[2];
-            float xin[2][D];
-            float* spt[2];
+        // Program order of the epilogue warps (the MMA steps keep their order: input layers of an iteration first):
+        //   prologue   L0(X0) L0(Y0)
+        //   iteration  L1(X) L1(Y) .. L_{L-2}(X) L_{L-2}(Y)   then   L0(X') L_last(X) L0(Y') L_last(Y)
+        // i.e. the input layers of the NEXT pair of tiles are handed over between the last-layer epilogues of this pair, so
+        // the tensor pipe has their MMAs to run while the epilogue produces outputs that feed no MMA.  Accumulator g mod 3
+        // is free in that order: L0(X') starts step g' (buffer of step g'-3, read long ago); L_last(X) then frees the
+        // buffer of step g'-2, which step g'+1 (fed by L0(Y')) takes; L_last(Y) reads the buffer of step g'-1.
+        struct Tile {
+            long long p;
+            bool valid, st_ok;
+            float* sp;
+        };
+        auto tile_state = [&](int it, int t) {
+            const long long T = cluster_id + (long long)(2 * it + t) * num_clusters;   // >= num_pairs: a dummy tile
+            Tile s;
+            s.p = (T * 2 + cta) * kTcPts + 8 * q + pl;
+            s.valid = T < num_pairs && s.p < n;
+            s.st_ok = STASH && T < num_pairs && (s.p >> 3) < nblk8;   // whole image blocks are written: tail rows stay finite
+            s.sp = stash + slot_off(s.st_ok ? s.p : 0, sub, tq);
+            return s;
+        };
+        // input layer: z0 = W_0 x + b_0, dz0/dx_k = W_0[:,k], no second derivatives
+        auto input_layer = [&](const Tile& ts) {
+            float xin[D];
 #pragma unroll
-            for (int t = 0; t < 2; ++t) {
-                const long long T = cluster_id + (long long)(2 * it + t) * num_clusters;   // >= num_pairs: a dummy tile
-                pt[t] = (T * 2 + cta) * kTcPts + 8 * q + pl;
-                vt[t] = T < num_pairs && pt[t] < n;
-#pragma unroll
-                for (int i = 0; i < D; ++i) xin[t][i] = vt[t] ? __ldg(x + pt[t] * D + i) : 0.f;
-                st_ok[t] = STASH && T < num_pairs && (pt[t] >> 3) < nblk8;   // whole image blocks are written: tail rows stay finite
-                spt[t] = stash + slot_off(st_ok[t] ? pt[t] : 0, sub, tq);
-            }
-            // ---- input layer of both tiles: z0 = W_0 x + b_0, dz0/dx_k = W_0[:,k], no second derivatives ----
-#pragma unroll
-            for (int t = 0; t < 2; ++t) {
+            for (int i = 0; i < D; ++i) xin[i] = ts.valid ? __ldg(x + ts.p * D + i) : 0.f;
 #pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    const int f = 32 * c + fb;
-                    const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
-                    float2 w2[D];
+            for (int c = 0; c < 4; ++c) {
+                const int f = 32 * c + fb;
+                const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
+                float2 w2[D];
 #pragma unroll
-                    for (int k = 0; k < D; ++k) w2[k] = *reinterpret_cast<const float2*>(W0t + k * 128 + f);
-                    float a[2][R];
+                for (int k = 0; k < D; ++k) w2[k] = *reinterpret_cast<const float2*>(W0t + k * 128 + f);
+                float a[2][R];
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        float z0 = e ? b2.y : b2.x;
+                for (int e = 0; e < 2; ++e) {
+                    float z0 = e ? b2.y : b2.x;
 #pragma unroll
-                        for (int k = 0; k < D; ++k) {
-                            const float wk = e ? w2[k].y : w2[k].x;
-                            z0 = fmaf(wk, xin[t][k], z0);
-                            a[e][1 + k] = wk;
-                        }
-                        a[e][0] = z0;
-                        a[e][1 + D] = 0.f;
-                        tc_act_fwd<D, ACT>(a[e], act);
+                    for (int k = 0; k < D; ++k) {
+                        const float wk = e ? w2[k].y : w2[k].x;
+                        z0 = fmaf(wk, xin[k], z0);
+                        a[e][1 + k] = wk;
                     }
+                    a[e][0] = z0;
+                    a[e][1 + D] = 0.f;
+                    tc_act_fwd<D, ACT>(a[e], act);
+                }
+                hand_over(a);
+            }
+        };
+        // hidden layer l >= 1 of tile t of iteration it: z_l arrives in the accumulator of MMA step g
+        auto hidden_layer = [&](int it, int l, int t, const Tile& ts) {
+            const float* bl = bias + l * 128;
+            const bool last = l == L - 1;
+            const uint32_t g = (uint32_t)it * 2u * (uint32_t)nmat + 2u * (uint32_t)(l - 1) + (uint32_t)t;
+            const uint32_t dcol = k2ColD + 128u * (g % 3u);
+            mbar_wait(&d_full[g % 3u], (g / 3u) & 1u);
+            tc_fence_after();
+            float* spl = ts.sp + (size_t)(l - 1) * stash_ls;
+            float o[R];
+#pragma unroll
+            for (int s = 0; s < R; ++s) o[s] = 0.f;
+            uint32_t nLo[4], nHi[4];
+            IO::ld(lane_lo + dcol + kCw * sub, nLo);
+            IO::ld(lane_hi + dcol + kCw * sub, nHi);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int f = 32 * c + fb;
+                tmem_wait_ld();
+                uint32_t LoHi[4], HiHi[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                if (c < 3) {   // the next chunk's accumulator columns travel while this chunk is computed
+                    IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                    IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
+                }
+                const float2 b2 = *reinterpret_cast<const float2*>(bl + f);
+                float a[2][R], sv8[8];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+#pragma unroll
+                    for (int s = 0; s < R; ++s) a[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
+                    a[e][0] += e ? b2.y : b2.x;
+#pragma unroll
+                    for (int s = 1; s < 4; ++s) sv8[4 * e + s] = s < R ? a[e][s] : 0.f;
+                    sv8[4 * e] = tc_act_fwd<D, ACT>(a[e], act);
+                }
+                if (ts.st_ok) stg_v8(spl + (size_t)c * 1024, sv8);
+                if (!last) {
                     hand_over(a);
+                } else {
+                    const float2 wo = *reinterpret_cast<const float2*>(wout + f);
+#pragma unroll
+                    for (int s = 0; s < R; ++s) o[s] = fmaf(wo.y, a[1][s], fmaf(wo.x, a[0][s], o[s]));
                 }
             }
-            // ---- hidden layers 1 .. L-1, tiles alternating ----
-#pragma unroll 1
-            for (int l = 1; l < L; ++l) {
-                const float* bl = bias + l * 128;
-                const bool last = l == L - 1;
+            if (last) {
+                // output layer: reduce over the 4 lanes of a point, then over the warps of the quadrant
+                float* comb = t ? comb1 : comb0;
 #pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    const uint32_t g = (uint32_t)it * 2u * (uint32_t)nmat + 2u * (uint32_t)(l - 1) + (uint32_t)t;   // the MMA step that produced z_l of tile t
-                    const uint32_t dcol = k2ColD + 128u * (g % 3u);
-                    mbar_wait(&d_full[g % 3u], (g / 3u) & 1u);
-                    tc_fence_after();
-                    float* spl = spt[t] + (size_t)(l - 1) * stash_ls;
-                    float o[R];
-#pragma unroll
-                    for (int s = 0; s < R; ++s) o[s] = 0.f;
-                    uint32_t nLo[4], nHi[4];
-                    IO::ld(lane_lo + dcol + kCw * sub, nLo);
-                    IO::ld(lane_hi + dcol + kCw * sub, nHi);
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const int f = 32 * c + fb;
-                        tmem_wait_ld();
-                        uint32_t LoHi[4], HiHi[4];
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
-                        if (c < 3) {   // the next chunk's accumulator columns travel while this chunk is computed
-                            IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
-                            IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
-                        }
-                        const float2 b2 = *reinterpret_cast<const float2*>(bl + f);
-                        float a[2][R], sv8[8];
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-#pragma unroll
-                            for (int s = 0; s < R; ++s) a[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
-                            a[e][0] += e ? b2.y : b2.x;
-#pragma unroll
-                            for (int s = 1; s < 4; ++s) sv8[4 * e + s] = s < R ? a[e][s] : 0.f;
-                            sv8[4 * e] = tc_act_fwd<D, ACT>(a[e], act);
-                        }
-                        if (st_ok[t]) stg_v8(spl + (size_t)c * 1024, sv8);
-                        if (!last) {
-                            hand_over(a);
-                        } else {
-                            const float2 wo = *reinterpret_cast<const float2*>(wout + f);
-#pragma unroll
-                            for (int s = 0; s < R; ++s) o[s] = fmaf(wo.y, a[1][s], fmaf(wo.x, a[0][s], o[s]));
-                        }
-                    }
-                    if (last) {
-                        // output layer: reduce over the 4 lanes of a point, then over the warps of the quadrant
-                        float* comb = t ? comb1 : comb0;
-#pragma unroll
-                        for (int s = 0; s < R; ++s) {
-                            o[s] += __shfl_xor_sync(0xffffffffu, o[s], 1);
-                            o[s] += __shfl_xor_sync(0xffffffffu, o[s], 2);
-                        }
-                        if (tq == 0) {
-#pragma unroll
-                            for (int s = 0; s < R; ++s) comb[(w * 8 + pl) * 4 + s] = o[s];
-                        }
-                        asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
-                        if (sub == 0 && tq == 0 && vt[t] && out_u) {
-#pragma unroll
-                            for (int k = 1; k < kWpq; ++k) {
-                                const float* oc = comb + ((w + 4 * k) * 8 + pl) * 4;
-#pragma unroll
-                                for (int s = 0; s < R; ++s) o[s] += oc[s];
-                            }
-                            out_u[pt[t]] = o[0] + bout;
-#pragma unroll
-                            for (int i = 0; i < D; ++i) out_g[pt[t] * D + i] = o[1 + i];
-                            out_h[pt[t]] = o[1 + D];
-                        }
-                    }
+                for (int s = 0; s < R; ++s) {
+                    o[s] += __shfl_xor_sync(0xffffffffu, o[s], 1);
+                    o[s] += __shfl_xor_sync(0xffffffffu, o[s], 2);
                 }
+                if (tq == 0) {
+#pragma unroll
+                    for (int s = 0; s < R; ++s) comb[(w * 8 + pl) * 4 + s] = o[s];
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+                if (sub == 0 && tq == 0 && ts.valid && out_u) {
+#pragma unroll
+                    for (int k = 1; k < kWpq; ++k) {
+                        const float* oc = comb + ((w + 4 * k) * 8 + pl) * 4;
+#pragma unroll
+                        for (int s = 0; s < R; ++s) o[s] += oc[s];
+                    }
+                    out_u[ts.p] = o[0] + bout;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) out_g[ts.p * D + i] = o[1 + i];
+                    out_h[ts.p] = o[1 + D];
+                }
+            }
+        };
+        Tile cur0{}, cur1{};
+        if (iters > 0) {
+            cur0 = tile_state(0, 0);
+            cur1 = tile_state(0, 1);
+            input_layer(cur0);
+            input_layer(cur1);
+        }
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll 1
+            for (int l = 1; l < L - 1; ++l) {
+                hidden_layer(it, l, 0, cur0);
+                hidden_layer(it, l, 1, cur1);
+            }
+            if (it + 1 < iters) {
+                const Tile nx0 = tile_state(it + 1, 0), nx1 = tile_state(it + 1, 1);
+                input_layer(nx0);
+                hidden_layer(it, L - 1, 0, cur0);
+                input_layer(nx1);
+                hidden_layer(it, L - 1, 1, cur1);
+                cur0 = nx0;
+                cur1 = nx1;
+            } else {
+                hidden_layer(it, L - 1, 0, cur0);
+                hidden_layer(it, L - 1, 1, cur1);
             }
         }
     } else if (cta == 0 && lane == 0) {
@@ -1225,6 +1254,7 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
                 mbar_wait(&a_free[slot], ((nch >> 1) - 1) & 1u);
                 tc_fence_after();
             }
+            GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 2);
             const uint32_t col = k2ColA + 64u * slot + (uint32_t)(kCw * sub);
             IO::st(lane_lo + col, LoHi);
             IO::st(lane_hi + col, HiHi);
@@ -1234,6 +1264,7 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(&a_ready[slot], 0);
+            GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 3);
             ++nch;
         };
         auto store_zbar = [&](float* dst, const float (&ab)[2][R]) {
