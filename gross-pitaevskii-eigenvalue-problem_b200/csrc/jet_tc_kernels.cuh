@@ -1297,164 +1297,205 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
             if (tid == 0) { prefetch_stash(L - 1, tile_of(0, 0)); prefetch_stash(L - 1, tile_of(0, 1)); }
             load_stash(stash_ptr(tile_of(0, 0)), L - 1, 0, cur);
         }
-        for (int it = 0; it < iters; ++it) {
-#pragma unroll 1
-            for (int l = L - 1; l >= 0; --l) {
-#pragma unroll 1
-                for (int t = 0; t < 2; ++t) {
-                    const long long T = tile_of(it, t);
-                    const long long p = point_of(T);
-                    const bool live = T < num_pairs;                      // a dummy tile past the end: computed, never stored
-                    const bool valid = live && p < n;
-                    const bool in_blk = live && (p >> 3) < nblk8;         // whole blocks are read and written
-                    const float* sb = stash_ptr(T);
-                    // the stash this thread needs next, in program order: (same tile, next chunk) .. (other tile, same layer) ..
-                    // (first tile, next layer) .. (first tile of the next iteration, top layer)
-                    const long long Tn = t == 0 ? tile_of(it, 1) : (l > 1 ? tile_of(it, 0) : tile_of(it + 1, 0));
-                    const int ln = t == 0 ? l : (l > 1 ? l - 1 : L - 1);
-                    const bool has_next = l >= 1 && (t == 0 || l > 1 || it + 1 < iters);
-                    const float* sbn = stash_ptr(Tn);
-                    if (tid == 0 && l >= 1) prefetch_stash(l > 1 ? l - 1 : L - 1, l > 1 ? T : tile_of(it + 1, t));   // this tile's next image
-                    const long long pz = RING ? (long long)(T % ring.ns) * (2 * kTcPts) + cta * kTcPts + 8 * q + pl : (in_blk ? p : 0);
-                    float* zbase = zb + slot_off(pz, sub, tq);
-                    if (l == L - 1) {
-                        // ---- top hidden layer: abar = adj * wout; output-layer gradient ----
-                        float adj[R];
-                        adj[0] = (valid && u_bar) ? __ldg(u_bar + p) : 0.f;
+        // Program order of the epilogue warps (the MMA steps and the stash reads keep their order; the input layer hands
+        // nothing over and reads no stash):
+        //   prologue   top(X0) top(Y0)
+        //   iteration  l = L-2 .. 1: mid(l, X) mid(l, Y)   then   top(X') in(X) top(Y') in(Y)
+        // so the first MMA steps of the NEXT pair run while the input-layer epilogues (which feed no MMA) are computed.
+        // Accumulator g mod 3 is free in that order exactly as in jet_fwd2_tc_kernel.
+        struct Tile {
+            long long T, p;
+            bool live, valid, in_blk;
+            const float* sb;
+            float* zbase;
+        };
+        auto tile_state = [&](int it, int t) {
+            Tile s;
+            s.T = tile_of(it, t);
+            s.p = point_of(s.T);
+            s.live = s.T < num_pairs;                      // a dummy tile past the end: computed, never stored
+            s.valid = s.live && s.p < n;
+            s.in_blk = s.live && (s.p >> 3) < nblk8;       // whole blocks are read and written
+            s.sb = stash_ptr(s.T);
+            const long long pz = RING ? (long long)(s.T % ring.ns) * (2 * kTcPts) + cta * kTcPts + 8 * q + pl : (s.in_blk ? s.p : 0);
+            s.zbase = zb + slot_off(pz, sub, tq);
+            return s;
+        };
+        // a layer with stash (l >= 1) of tile t of iteration it
+        auto stash_layer = [&](int it, int l, int t) {
+            const Tile ts = tile_state(it, t);
+            const long long T = ts.T, p = ts.p;
+            const bool live = ts.live, valid = ts.valid, in_blk = ts.in_blk;
+            const float* sb = ts.sb;
+            float* zbase = ts.zbase;
+            // the stash this thread needs next, in program order: (same tile, next chunk) .. (other tile, same layer) ..
+            // (first tile, next layer) .. (first tile of the next iteration, top layer)
+            const long long Tn = t == 0 ? tile_of(it, 1) : (l > 1 ? tile_of(it, 0) : tile_of(it + 1, 0));
+            const int ln = t == 0 ? l : (l > 1 ? l - 1 : L - 1);
+            const bool has_next = t == 0 || l > 1 || it + 1 < iters;
+            const float* sbn = stash_ptr(Tn);
+            if (tid == 0) prefetch_stash(l > 1 ? l - 1 : L - 1, l > 1 ? T : tile_of(it + 1, t));   // this tile's next image
+            if (l == L - 1) {
+                // ---- top hidden layer: abar = adj * wout; output-layer gradient ----
+                float adj[R];
+                adj[0] = (valid && u_bar) ? __ldg(u_bar + p) : 0.f;
 #pragma unroll
-                        for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? __ldg(g_bar + p * D + i) : 0.f;
-                        adj[1 + D] = (valid && h_bar) ? __ldg(h_bar + p) : 0.f;
-                        if (sub == 0 && tq == 0) dbout_acc += adj[0];
-                        if (RING && live) {   // tile T lives in ring slot T % ns: wait until the dW CTAs have drained its previous tenant
-                            if (lane == 0) ring_wait(ring.cons + 2 * (T % ring.ns) + cta, (unsigned int)((L - 1) * (T / ring.ns)), ring.abort);
-                            __syncwarp();
+                for (int i = 0; i < D; ++i) adj[1 + i] = (valid && g_bar) ? __ldg(g_bar + p * D + i) : 0.f;
+                adj[1 + D] = (valid && h_bar) ? __ldg(h_bar + p) : 0.f;
+                if (sub == 0 && tq == 0) dbout_acc += adj[0];
+                if (RING && live) {   // tile T lives in ring slot T % ns: wait until the dW CTAs have drained its previous tenant
+                    if (lane == 0) ring_wait(ring.cons + 2 * (T % ring.ns) + cta, (unsigned int)((L - 1) * (T / ring.ns)), ring.abort);
+                    __syncwarp();
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int f = 32 * c + fb;
+                    float nxt[8];
+                    if (c < 3) load_stash(sb, l, c + 1, nxt);
+                    else if (has_next) load_stash(sbn, ln, 0, nxt);
+                    const float2 wo = *reinterpret_cast<const float2*>(wout + f);
+                    float ab[2][R];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float st[R], a[R];
+#pragma unroll
+                        for (int s = 0; s < R; ++s) st[s] = cur[4 * e + s];
+                        tc_act_from_stash<D, ACT>(st, a, act);
+                        float dw = dwout_acc[c][e];
+#pragma unroll
+                        for (int s = 0; s < R; ++s) {
+                            dw = fmaf(adj[s], a[s], dw);
+                            ab[e][s] = adj[s] * (e ? wo.y : wo.x);
                         }
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const int f = 32 * c + fb;
-                            float nxt[8];
-                            if (c < 3) load_stash(sb, l, c + 1, nxt);
-                            else if (has_next) load_stash(sbn, ln, 0, nxt);
-                            const float2 wo = *reinterpret_cast<const float2*>(wout + f);
-                            float ab[2][R];
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                float st[R], a[R];
-#pragma unroll
-                                for (int s = 0; s < R; ++s) st[s] = cur[4 * e + s];
-                                tc_act_from_stash<D, ACT>(st, a, act);
-                                float dw = dwout_acc[c][e];
-#pragma unroll
-                                for (int s = 0; s < R; ++s) {
-                                    dw = fmaf(adj[s], a[s], dw);
-                                    ab[e][s] = adj[s] * (e ? wo.y : wo.x);
-                                }
-                                dwout_acc[c][e] = dw;
-                                tc_act_bwd<D, ACT>(st, ab[e], act);
-                            }
-                            if (in_blk) store_zbar(zbase + (size_t)(l - 1) * lstride + (size_t)c * 1024, ab);
-                            hand_over(ab);
-#pragma unroll
-                            for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
-                        }
-                    } else {
-                        // ---- layers L-2 .. 0: abar_l arrives in the accumulator of MMA step (k = L-2-l, tile t) ----
-                        const uint32_t g = (uint32_t)it * 2u * (uint32_t)nmat + 2u * (uint32_t)(L - 2 - l) + (uint32_t)t;
-                        const uint32_t dcol = k2ColD + 128u * (g % 3u);
-                        mbar_wait(&d_full[g % 3u], (g / 3u) & 1u);
-                        tc_fence_after();
-                        uint32_t nLo[4], nHi[4];
-                        IO::ld(lane_lo + dcol + kCw * sub, nLo);
-                        IO::ld(lane_hi + dcol + kCw * sub, nHi);
-                        if (l >= 1) {
-                            // ---- middle layers ----
-#pragma unroll
-                            for (int c = 0; c < 4; ++c) {
-                                float nxt[8];
-                                if (c < 3) load_stash(sb, l, c + 1, nxt);
-                                else if (has_next) load_stash(sbn, ln, 0, nxt);
-                                tmem_wait_ld();
-                                uint32_t LoHi[4], HiHi[4];
-#pragma unroll
-                                for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
-                                if (c < 3) {
-                                    IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
-                                    IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
-                                }
-                                float ab[2][R];
-#pragma unroll
-                                for (int e = 0; e < 2; ++e) {
-                                    float st[R];
-#pragma unroll
-                                    for (int s = 0; s < R; ++s) {
-                                        st[s] = cur[4 * e + s];
-                                        ab[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
-                                    }
-                                    tc_act_bwd<D, ACT>(st, ab[e], act);
-                                }
-                                if (in_blk) store_zbar(zbase + (size_t)(l - 1) * lstride + (size_t)c * 1024, ab);
-                                hand_over(ab);
-#pragma unroll
-                                for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
-                            }
-                        } else {
-                            // ---- input layer: forward jets from x; dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val ----
-                            float xin[D];
-#pragma unroll
-                            for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
-#pragma unroll
-                            for (int c = 0; c < 4; ++c) {
-                                const int f = 32 * c + fb;
-                                tmem_wait_ld();
-                                uint32_t LoHi[4], HiHi[4];
-#pragma unroll
-                                for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
-                                if (c < 3) {
-                                    IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
-                                    IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
-                                }
-                                const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
-                                float2 w2[D];
-#pragma unroll
-                                for (int k = 0; k < D; ++k) w2[k] = *reinterpret_cast<const float2*>(W0t + k * 128 + f);
-#pragma unroll
-                                for (int e = 0; e < 2; ++e) {
-                                    float st[R], ab[R];
-                                    float z0 = e ? b2.y : b2.x;
-#pragma unroll
-                                    for (int k = 0; k < D; ++k) {
-                                        const float wk = e ? w2[k].y : w2[k].x;
-                                        z0 = fmaf(wk, xin[k], z0);
-                                        st[1 + k] = wk;
-                                    }
-                                    st[1 + D] = 0.f;
-                                    if (ACT == ACT_TANH || ACT == ACT_SHIFTED_TANH) {
-                                        st[0] = tanh_tc(z0);
-                                    } else {
-                                        float zz[R];
-#pragma unroll
-                                        for (int s = 1; s < R; ++s) zz[s] = st[s];
-                                        zz[0] = z0;
-                                        act_jet_fwd<D, JET_LAPLACIAN>(zz, act, st[0]);
-                                    }
-#pragma unroll
-                                    for (int s = 0; s < R; ++s) ab[s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
-                                    tc_act_bwd<D, ACT>(st, ab, act);
-#pragma unroll
-                                    for (int k = 0; k < D; ++k) dw0_acc[c][e][k] += fmaf(ab[0], xin[k], ab[1 + k]);
-                                    dw0_acc[c][e][D] += ab[0];
-                                }
-                            }
-                        }
+                        dwout_acc[c][e] = dw;
+                        tc_act_bwd<D, ACT>(st, ab[e], act);
                     }
-                    if (RING && l >= 1 && live) {   // zbar_l of this half tile is out: one release-arrive per warp
-                        __syncwarp();
-                        if (lane == 0) {
-                            __threadfence();
-                            red_release_gpu_add(ring.prod + (size_t)(l - 1) * 2 * ring.nrc + 2 * cluster_id + cta, 1u);
+                    if (in_blk) store_zbar(zbase + (size_t)(l - 1) * lstride + (size_t)c * 1024, ab);
+                    hand_over(ab);
+#pragma unroll
+                    for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
+                }
+            } else {
+                const uint32_t g = (uint32_t)it * 2u * (uint32_t)nmat + 2u * (uint32_t)(L - 2 - l) + (uint32_t)t;
+                const uint32_t dcol = k2ColD + 128u * (g % 3u);
+                mbar_wait(&d_full[g % 3u], (g / 3u) & 1u);
+                tc_fence_after();
+                uint32_t nLo[4], nHi[4];
+                IO::ld(lane_lo + dcol + kCw * sub, nLo);
+                IO::ld(lane_hi + dcol + kCw * sub, nHi);
+                // ---- middle layers ----
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    float nxt[8];
+                    if (c < 3) load_stash(sb, l, c + 1, nxt);
+                    else if (has_next) load_stash(sbn, ln, 0, nxt);
+                    tmem_wait_ld();
+                    uint32_t LoHi[4], HiHi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                    if (c < 3) {
+                        IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                        IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
+                    }
+                    float ab[2][R];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float st[R];
+#pragma unroll
+                        for (int s = 0; s < R; ++s) {
+                            st[s] = cur[4 * e + s];
+                            ab[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
                         }
+                        tc_act_bwd<D, ACT>(st, ab[e], act);
+                    }
+                    if (in_blk) store_zbar(zbase + (size_t)(l - 1) * lstride + (size_t)c * 1024, ab);
+                    hand_over(ab);
+#pragma unroll
+                    for (int s = 0; s < 8; ++s) cur[s] = nxt[s];
+                }
+            }
+            if (RING && live) {   // zbar_l of this half tile is out: one release-arrive per warp
+                __syncwarp();
+                if (lane == 0) {
+                    __threadfence();
+                    red_release_gpu_add(ring.prod + (size_t)(l - 1) * 2 * ring.nrc + 2 * cluster_id + cta, 1u);
+                }
+            }
+        };
+        // the input layer of tile t of iteration it: abar_0 arrives in the accumulator of the tile's last MMA step
+        auto input_layer = [&](int it, int t) {
+            const Tile ts = tile_state(it, t);
+            const long long p = ts.p;
+            const bool valid = ts.valid;
+            const uint32_t g = (uint32_t)it * 2u * (uint32_t)nmat + 2u * (uint32_t)(L - 2) + (uint32_t)t;
+            const uint32_t dcol = k2ColD + 128u * (g % 3u);
+            mbar_wait(&d_full[g % 3u], (g / 3u) & 1u);
+            tc_fence_after();
+            uint32_t nLo[4], nHi[4];
+            IO::ld(lane_lo + dcol + kCw * sub, nLo);
+            IO::ld(lane_hi + dcol + kCw * sub, nHi);
+                // ---- input layer: forward jets from x; dW_0[f][k] = sum_p zbar_val x_k + zbar_dk, db_0[f] = sum_p zbar_val ----
+                float xin[D];
+#pragma unroll
+                for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int f = 32 * c + fb;
+                    tmem_wait_ld();
+                    uint32_t LoHi[4], HiHi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) LoHi[j] = nLo[j], HiHi[j] = nHi[j];
+                    if (c < 3) {
+                        IO::ld(lane_lo + dcol + 32 * (c + 1) + kCw * sub, nLo);
+                        IO::ld(lane_hi + dcol + 32 * (c + 1) + kCw * sub, nHi);
+                    }
+                    const float2 b2 = *reinterpret_cast<const float2*>(bias + f);
+                    float2 w2[D];
+#pragma unroll
+                    for (int k = 0; k < D; ++k) w2[k] = *reinterpret_cast<const float2*>(W0t + k * 128 + f);
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float st[R], ab[R];
+                        float z0 = e ? b2.y : b2.x;
+#pragma unroll
+                        for (int k = 0; k < D; ++k) {
+                            const float wk = e ? w2[k].y : w2[k].x;
+                            z0 = fmaf(wk, xin[k], z0);
+                            st[1 + k] = wk;
+                        }
+                        st[1 + D] = 0.f;
+                        if (ACT == ACT_TANH || ACT == ACT_SHIFTED_TANH) {
+                            st[0] = tanh_tc(z0);
+                        } else {
+                            float zz[R];
+#pragma unroll
+                            for (int s = 1; s < R; ++s) zz[s] = st[s];
+                            zz[0] = z0;
+                            act_jet_fwd<D, JET_LAPLACIAN>(zz, act, st[0]);
+                        }
+#pragma unroll
+                        for (int s = 0; s < R; ++s) ab[s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
+                        tc_act_bwd<D, ACT>(st, ab, act);
+#pragma unroll
+                        for (int k = 0; k < D; ++k) dw0_acc[c][e][k] += fmaf(ab[0], xin[k], ab[1 + k]);
+                        dw0_acc[c][e][D] += ab[0];
                     }
                 }
+        };
+        if (iters > 0) {
+#pragma unroll 1
+            for (int t = 0; t < 2; ++t) stash_layer(0, L - 1, t);
+        }
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll 1
+            for (int l = L - 2; l >= 1; --l) {
+#pragma unroll 1
+                for (int t = 0; t < 2; ++t) stash_layer(it, l, t);
+            }
+#pragma unroll 1
+            for (int t = 0; t < 2; ++t) {
+                if (it + 1 < iters) stash_layer(it + 1, L - 1, t);
+                input_layer(it, t);
             }
         }
         // flush the output-layer gradient: sum over the 8 points of the warp, one atomic per feature
