@@ -150,15 +150,38 @@ __global__ void pack_wimg_kernel(PtrArray W, int L, int Wd, int transpose, float
 // plain CTA-scope ones -- what travels between the two CTAs here is tensor memory, ordered by the tcgen05 fences.
 // ------------------------------------------------------------------------------------------
 // the three products of one K = 32 chunk: corrections first, then hi*hi (all read the same A columns)
-__device__ __forceinline__ void mma_chunk_3x(uint32_t dcol, uint32_t ahi, uint32_t alo, uint64_t bhi, uint64_t blo, uint32_t idesc,
-                                             uint32_t accum_first) {
+// The MMAs of one 32-feature chunk of A (TMEM: ahi = 32 tf32 columns, ac = 32 correction columns) against the matching K
+// slice of a weight image (bhi / bc: descriptors of the tf32 hi image / the correction image, already advanced to the chunk).
+// Correction products (see tc_wimg.cuh): four kind::f16 MMAs on bf16 pairs, one per 8-feature group -- TMEM columns
+// 8 s .. 8 s + 3 hold bf16(a), 8 s + 4 .. 8 s + 7 hold bf16(a_lo), the image holds bf16(w_lo) | bf16(w) in the same k order.
+__device__ __forceinline__ void mma_chunk_corr(uint32_t dcol, uint32_t ahi, uint32_t ac, uint64_t bhi, uint64_t bc, uint32_t idesc,
+                                               uint32_t accum_first) {
+#if GPE_TC_BF16_CORR
+    constexpr uint32_t idesc16 = tc::instr_desc(1, 256, 128, 0, 0);
+#pragma unroll
+    for (int sgrp = 0; sgrp < 4; ++sgrp)
+        tc::mma_ts<1, 2>(dcol, ac + 8 * sgrp, bc + (uint64_t)(16 * sgrp), idesc16, sgrp == 0 ? accum_first : 1u);
+#else
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
-        tc::mma_ts<0, 2>(dcol, alo + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, kk == 0 ? accum_first : 1u);
-        tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, blo + (uint64_t)(16 * kk), idesc, 1u);
+        tc::mma_ts<0, 2>(dcol, ac + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, kk == 0 ? accum_first : 1u);
+        tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, bc + (uint64_t)(16 * kk), idesc, 1u);
     }
+#endif
+}
+__device__ __forceinline__ void mma_chunk_hh(uint32_t dcol, uint32_t ahi, uint64_t bhi, uint32_t idesc, uint32_t accum_first) {
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, 1u);
+    for (int kk = 0; kk < 4; ++kk) tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, kk == 0 ? accum_first : 1u);
+}
+// the small products first, then hi*hi: the accumulator is rounded toward zero after every MMA
+__device__ __forceinline__ void mma_chunk_3x(uint32_t dcol, uint32_t ahi, uint32_t ac, uint64_t bhi, uint64_t bc, uint32_t idesc,
+                                             uint32_t accum_first) {
+#ifndef GPE_TC_PROBE_ONE_PRODUCT   // (energy probe builds issue hi*hi alone: wrong numerics)
+    mma_chunk_corr(dcol, ahi, ac, bhi, bc, idesc, accum_first);
+    mma_chunk_hh(dcol, ahi, bhi, idesc, 1u);
+#else
+    mma_chunk_hh(dcol, ahi, bhi, idesc, accum_first);
+#endif
 }
 
 // ------------------------------------------------------------------------------------------
@@ -174,19 +197,40 @@ template <> struct FragIO<2> {
     static __device__ __forceinline__ void ld(uint32_t a, uint32_t (&r)[8]) { tc::tmem_ld_16x256b_x2(a, r); }
     static __device__ __forceinline__ void st(uint32_t a, const uint32_t (&r)[8]) { tc::tmem_st_16x256b_x2(a, r); }
 };
-// split the 4 stream slots of one (point, feature) into the hi / lo fragment registers
+// A-operand fragments of one (point, feature pair): the 4 stream slots are 4 TMEM lanes (lane half lo: slots 0, 1; lane
+// half hi: slots 2, 3), the two features are adjacent columns.  Hi: tf32 values (16x256b store, 8 columns per warp);
+// C: the correction columns of the same warp -- bf16 pairs {a | a_lo} (16x128b.x2 store: columns 0..3 | 4..7), or the
+// fp32 lo values when GPE_TC_BF16_CORR = 0.
+struct AFrag { uint32_t LoHi[4], HiHi[4], LoC[4], HiC[4]; };
 template <int R>
-__device__ __forceinline__ void put_slots(const float* a, int i, int e, uint32_t (&LoHi)[4 * kNI], uint32_t (&HiHi)[4 * kNI],
-                                          uint32_t (&LoLo)[4 * kNI], uint32_t (&HiLo)[4 * kNI]) {
+__device__ __forceinline__ void make_afrag(const float (&a)[2][R], AFrag& f) {
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
-        const float v = s < R ? a[s] : 0.f;
-        const uint32_t h = tf32_hi(v);
-        const uint32_t l = __float_as_uint(v - __uint_as_float(h));
-        const int r = 4 * i + 2 * (s & 1) + e;
-        if (s < 2) LoHi[r] = h, LoLo[r] = l;
-        else HiHi[r] = h, HiLo[r] = l;
+        const float v0 = s < R ? a[0][s] : 0.f, v1 = s < R ? a[1][s] : 0.f;
+        const uint32_t h0 = tf32_hi(v0), h1 = tf32_hi(v1);
+        const float l0 = v0 - __uint_as_float(h0), l1 = v1 - __uint_as_float(h1);
+        uint32_t* H = s < 2 ? f.LoHi : f.HiHi;
+        uint32_t* C = s < 2 ? f.LoC : f.HiC;
+        H[2 * (s & 1)] = h0, H[2 * (s & 1) + 1] = h1;
+#if GPE_TC_BF16_CORR
+        C[s & 1] = pack_bf16x2(v0, v1);
+        C[2 + (s & 1)] = pack_bf16x2(l0, l1);
+#else
+        C[2 * (s & 1)] = __float_as_uint(l0), C[2 * (s & 1) + 1] = __float_as_uint(l1);
+#endif
     }
+}
+// col_hi / col_c: this warp's 8 columns of the chunk in the tf32 area / the correction area
+__device__ __forceinline__ void store_afrag(uint32_t lane_lo, uint32_t lane_hi, uint32_t col_hi, uint32_t col_c, const AFrag& f) {
+    tc::tmem_st_16x256b_x1(lane_lo + col_hi, f.LoHi);
+    tc::tmem_st_16x256b_x1(lane_hi + col_hi, f.HiHi);
+#if GPE_TC_BF16_CORR
+    tc::tmem_st_16x128b_x2(lane_lo + col_c, f.LoC);
+    tc::tmem_st_16x128b_x2(lane_hi + col_c, f.HiC);
+#else
+    tc::tmem_st_16x256b_x1(lane_lo + col_c, f.LoC);
+    tc::tmem_st_16x256b_x1(lane_hi + col_c, f.HiC);
+#endif
 }
 
 // 32-byte vector access to one (point, feature pair) slot of an image block (dw_tc_kernel.cuh: blk_off)
@@ -270,14 +314,10 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
         uint32_t dc0 = 0u, dc1 = 0u;                       // completed phases of d_full[0] / d_full[1]
         // split the four stream slots of features (f, f + 1) and hand the chunk to the MMA thread
         auto hand_over = [&](int c, const float (&a)[2][R]) {
-            uint32_t LoHi[4], HiHi[4], LoLo[4], HiLo[4];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) put_slots<R>(a[e], 0, e, LoHi, HiHi, LoLo, HiLo);
+            AFrag fr;
+            make_afrag<R>(a, fr);
             const uint32_t col = (uint32_t)(32 * c + kCw * sub);
-            IO::st(lane_lo + kColAHi + col, LoHi);
-            IO::st(lane_hi + kColAHi + col, HiHi);
-            IO::st(lane_lo + kColALo + col, LoLo);
-            IO::st(lane_hi + kColALo + col, HiLo);
+            store_afrag(lane_lo, lane_hi, kColAHi + col, kColALo + col, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -412,21 +452,17 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                     }
                 } else {
                     // the two small cross products of every chunk first, the 16 hi*hi products last: the accumulator is rounded
-                    // toward zero after every MMA, so the 32 correction MMAs land while it is ~2^-11 of its final size and only
+                    // toward zero after every MMA, so the correction MMAs land while it is ~2^-11 of its final size and only
                     // 16 roundings count
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         mbar_wait(&a_ready[c], acnt & 1u);
                         tc_fence_after();
-#pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) {
-                            const int j = 4 * c + kk;
-                            mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, dhi + (uint64_t)(16 * j), idesc, j > 0 ? 1u : 0u);
-                            mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, dlo + (uint64_t)(16 * j), idesc, 1u);
-                        }
+                        mma_chunk_corr(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
+                                       c > 0 ? 1u : 0u);
                     }
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, dhi + (uint64_t)(16 * j), idesc, 1u);
+                    for (int c = 0; c < 4; ++c) mma_chunk_hh(dcol, tb + kColAHi + 32 * c, dhi + (uint64_t)(64 * c), idesc, 1u);
                 }
                 mma_commit_pair(&d_full[l & 1], 3);
             }
@@ -558,9 +594,8 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
         uint32_t nch = 0;                                  // chunks handed over so far (ring position)
         // split the four stream slots of features (f, f + 1), wait for the ring slot, hand the chunk to the MMA thread
         auto hand_over = [&](const float (&a)[2][R]) {
-            uint32_t LoHi[4], HiHi[4], LoLo[4], HiLo[4];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) put_slots<R>(a[e], 0, e, LoHi, HiHi, LoLo, HiLo);
+            AFrag fr;
+            make_afrag<R>(a, fr);
             const uint32_t slot = nch & 1u;
             if (nch >= 2) {                                // the MMAs that read this slot two chunks ago have retired
                 mbar_wait(&a_free[slot], ((nch >> 1) - 1) & 1u);
@@ -568,10 +603,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
             }
             GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 2);
             const uint32_t col = k2ColA + 64u * slot + (uint32_t)(kCw * sub);
-            IO::st(lane_lo + col, LoHi);
-            IO::st(lane_hi + col, HiHi);
-            IO::st(lane_lo + col + 32, LoLo);
-            IO::st(lane_hi + col + 32, HiLo);
+            store_afrag(lane_lo, lane_hi, col, col + 32, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -881,14 +913,10 @@ __device__ __forceinline__ void rev_role(const TcParams& P, const float* __restr
         const size_t lstride = RING ? (size_t)ring.ns * 8 * 4096 : (size_t)nblk8 * 4096;
         const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
         auto hand_over = [&](int c, const float (&a)[2][R]) {
-            uint32_t LoHi[4], HiHi[4], LoLo[4], HiLo[4];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) put_slots<R>(a[e], 0, e, LoHi, HiHi, LoLo, HiLo);
+            AFrag fr;
+            make_afrag<R>(a, fr);
             const uint32_t col = (uint32_t)(32 * c + kCw * sub);
-            IO::st(lane_lo + kColAHi + col, LoHi);
-            IO::st(lane_hi + kColAHi + col, HiHi);
-            IO::st(lane_lo + kColALo + col, LoLo);
-            IO::st(lane_hi + kColALo + col, HiLo);
+            store_afrag(lane_lo, lane_hi, kColAHi + col, kColALo + col, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -1141,21 +1169,17 @@ __device__ __forceinline__ void rev_role(const TcParams& P, const float* __restr
                     }
                 } else {
                     // the two small cross products of every chunk first, the 16 hi*hi products last: the accumulator is rounded
-                    // toward zero after every MMA, so the 32 correction MMAs land while it is ~2^-11 of its final size and only
+                    // toward zero after every MMA, so the correction MMAs land while it is ~2^-11 of its final size and only
                     // 16 roundings count
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         mbar_wait(&a_ready[c], acnt & 1u);
                         tc_fence_after();
-#pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) {
-                            const int j = 4 * c + kk;
-                            mma_ts<0, 2>(dcol, tb + kColALo + 8 * j, dhi + (uint64_t)(16 * j), idesc, j > 0 ? 1u : 0u);
-                            mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, dlo + (uint64_t)(16 * j), idesc, 1u);
-                        }
+                        mma_chunk_corr(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
+                                       c > 0 ? 1u : 0u);
                     }
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) mma_ts<0, 2>(dcol, tb + kColAHi + 8 * j, dhi + (uint64_t)(16 * j), idesc, 1u);
+                    for (int c = 0; c < 4; ++c) mma_chunk_hh(dcol, tb + kColAHi + 32 * c, dhi + (uint64_t)(64 * c), idesc, 1u);
                 }
                 mma_commit_pair(&d_full[(l - 1) & 1], 3);
             }
@@ -1246,9 +1270,8 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
         const size_t lstride = RING ? (size_t)ring.ns * 8 * 4096 : (size_t)nblk8 * 4096;
         const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
         auto hand_over = [&](const float (&a)[2][R]) {
-            uint32_t LoHi[4], HiHi[4], LoLo[4], HiLo[4];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) put_slots<R>(a[e], 0, e, LoHi, HiHi, LoLo, HiLo);
+            AFrag fr;
+            make_afrag<R>(a, fr);
             const uint32_t slot = nch & 1u;
             if (nch >= 2) {                                // the MMAs that read this slot two chunks ago have retired
                 mbar_wait(&a_free[slot], ((nch >> 1) - 1) & 1u);
@@ -1256,10 +1279,7 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
             }
             GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 2);
             const uint32_t col = k2ColA + 64u * slot + (uint32_t)(kCw * sub);
-            IO::st(lane_lo + col, LoHi);
-            IO::st(lane_hi + col, HiHi);
-            IO::st(lane_lo + col + 32, LoLo);
-            IO::st(lane_hi + col + 32, HiLo);
+            store_afrag(lane_lo, lane_hi, col, col + 32, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();

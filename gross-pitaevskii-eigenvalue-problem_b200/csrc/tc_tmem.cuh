@@ -84,5 +84,10 @@ __device__ __forceinline__ void tmem_st_16x256b_x2(uint32_t taddr, const uint32_
 __device__ __forceinline__ void tmem_ld_16x128b_x1(uint32_t taddr, uint32_t (&r)[2]) {
     asm volatile("tcgen05.ld.sync.aligned.16x128b.x1.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr));
 }
+// two repetitions (8 columns): registers {0, 1} = repetition 0 (columns 0..3), {2, 3} = repetition 1 (columns 4..7)
+__device__ __forceinline__ void tmem_st_16x128b_x2(uint32_t taddr, const uint32_t (&r)[4]) {
+    asm volatile("tcgen05.st.sync.aligned.16x128b.x2.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3])
+                 : "memory");
+}
 
 }  // namespace tc

@@ -19,8 +19,33 @@ __host__ __device__ __forceinline__ uint32_t img_off128(int r, int c) {
 // of the forward epilogue); the add + mask below is the same rounding for every finite value below 2^127.
 __device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
 
+// Correction products of the fp32-accurate split.  x = hi + lo with hi = tf32(x):  a w ~= a_hi w_hi + (a_lo w_hi + a_hi w_lo).
+// GPE_TC_BF16_CORR = 1 (default): the bracket, 2^-11 of the result, runs as kind::f16 MMAs on bf16 operands (K = 16 per MMA,
+// i.e. half the MMAs of a tf32 product; 8 mantissa bits are plenty for a term that small): 8 MMAs per 32-feature chunk
+// instead of 12.  = 0: all three products in tf32 (the round-1 scheme).
+#ifndef GPE_TC_BF16_CORR
+#define GPE_TC_BF16_CORR 1
+#endif
+
+// bf16x2 {upper = hi16, lower = lo16}, round to nearest
+__device__ __forceinline__ uint32_t pack_bf16x2(float lower, float upper) {
+    uint32_t d;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(upper), "f"(lower));
+    return d;
+}
+
+// byte offset of (row r, k) in the correction image of one half matrix: [64 rows x 256 k] bf16, 8-row x 16-byte core
+// matrices (8 k each), cores contiguous along k (LBO = 128 B), row groups 4096 B apart (SBO).  The k axis is ordered the way
+// the epilogue warps write the A operand: for every group of 8 features (chunk c, warp column group s) 16 consecutive k:
+//   k = 16 (4 c + s) + j      j = 0..7  : bf16(w_lo) of feature 32 c + 8 s + j      (meets bf16(a)    in TMEM columns 0..3)
+//                             j = 8..15 : bf16(w)    of feature 32 c + 8 s + j - 8  (meets bf16(a_lo) in TMEM columns 4..7)
+__host__ __device__ __forceinline__ uint32_t corr_off(int r, int kk) {
+    return (uint32_t)((r >> 3) * 4096 + (kk >> 3) * 128 + (r & 7) * 16 + (kk & 7) * 2);
+}
+
 // hidden weight images for the tensor path.  transpose = 0: B[n = out][k = in] (forward);
-// transpose = 1: B[n = in][k = out] (reverse sweep).  Zero padded to 128 x 128.
+// transpose = 1: B[n = in][k = out] (reverse sweep).  Zero padded to 128 x 128.  Per (layer, 64-row half): the tf32 hi image
+// (kImgFloats floats) followed by the correction image of the same size (bf16 pairs, or the fp32 lo image).
 __device__ __forceinline__ void pack_wimg_elems(const PtrArray& W, int L, int Wd, int transpose, float* __restrict__ wimg, long long first,
                                                 long long stride) {
     const long long total = (long long)(L - 1) * 128 * 128;
@@ -33,7 +58,14 @@ __device__ __forceinline__ void pack_wimg_elems(const PtrArray& W, int L, int Wd
         float* base = wimg + ((size_t)l * 2 + (nn >> 6)) * 2 * kImgFloats;
         const uint32_t off = img_off128(nn & 63, k) >> 2;
         base[off] = hi;
+#if GPE_TC_BF16_CORR
+        unsigned short* corr = reinterpret_cast<unsigned short*>(base + kImgFloats);
+        const int kk = 16 * (k >> 3) + (k & 7);
+        corr[corr_off(nn & 63, kk) >> 1] = (unsigned short)(pack_bf16x2(v - hi, 0.f) & 0xffffu);
+        corr[corr_off(nn & 63, kk + 8) >> 1] = (unsigned short)(pack_bf16x2(v, 0.f) & 0xffffu);
+#else
         base[kImgFloats + off] = v - hi;
+#endif
     }
 }
 
