@@ -53,6 +53,23 @@ __device__ __forceinline__ void split4(const float4& v, uint4& h, uint4& l) {
     l.x = __float_as_uint(v.x - __uint_as_float(h.x)), l.y = __float_as_uint(v.y - __uint_as_float(h.y));
     l.z = __float_as_uint(v.z - __uint_as_float(h.z)), l.w = __float_as_uint(v.w - __uint_as_float(h.w));
 }
+// One 16-byte row of the B operand (a_{l-1}: the 4 streams of one point for one feature) at byte offset `off` = blk_off(f, p)
+// of the stage's images: tf32 hi values into AH; into AC the correction operand -- the fp32 lo values at the same offset, or
+// (GPE_TC_BF16_CORR) bf16 quadruples in the k order of the A operand's correction columns: per pair of points (2 g, 2 g + 1)
+// one 16-byte core row of bf16(a_lo) (meets bf16(zbar)) followed, 128 B further, by one of bf16(a) (meets bf16(zbar_lo)).
+__device__ __forceinline__ void store_b_row(unsigned char* AH, unsigned char* AC, uint32_t off, const float4& v) {
+    uint4 h, lw;
+    split4(v, h, lw);
+    *reinterpret_cast<uint4*>(AH + off) = h;
+#if GPE_TC_BF16_CORR
+    const uint32_t odd = (off >> 7) & 1u;                       // p & 1: blk_off has p * 128 and nothing else in bits 7..9
+    unsigned char* c = AC + off - odd * 128u + odd * 8u;
+    *reinterpret_cast<uint2*>(c) = make_uint2(pack_bf16x2(__uint_as_float(lw.x), __uint_as_float(lw.y)), pack_bf16x2(__uint_as_float(lw.z), __uint_as_float(lw.w)));
+    *reinterpret_cast<uint2*>(c + 128) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+#else
+    *reinterpret_cast<uint4*>(AC + off) = lw;
+#endif
+}
 __device__ __forceinline__ void red_add_v4(float* g, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(g), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -210,7 +227,14 @@ __device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restri
                     uint4 h, lw;
                     split4(v, h, lw);
                     hi[4 * pp] = h.x, hi[4 * pp + 1] = h.y, hi[4 * pp + 2] = h.z, hi[4 * pp + 3] = h.w;
+#if GPE_TC_BF16_CORR
+                    // correction columns of this warp: 0..3 = bf16 pairs of the 8 values, 4..7 = bf16 pairs of their lo parts
+                    lo[2 * pp] = pack_bf16x2(v.x, v.y), lo[2 * pp + 1] = pack_bf16x2(v.z, v.w);
+                    lo[4 + 2 * pp] = pack_bf16x2(__uint_as_float(lw.x), __uint_as_float(lw.y));
+                    lo[4 + 2 * pp + 1] = pack_bf16x2(__uint_as_float(lw.z), __uint_as_float(lw.w));
+#else
                     lo[4 * pp] = lw.x, lo[4 * pp + 1] = lw.y, lo[4 * pp + 2] = lw.z, lo[4 * pp + 3] = lw.w;
+#endif
                     s2 += v.x;
                 }
                 tmem_st_32x32b_x8(tz, hi);
@@ -230,10 +254,7 @@ __device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restri
 #pragma unroll
                     for (int s = 0; s < D + 2; ++s) st[s] = sv4[s];
                     tc_act_from_stash<D, ACT>(st, a, act);
-                    uint4 h, lw;
-                    split4(make_float4(a[0], a[1], a[2], D == 2 ? a[D + 1] : 0.f), h, lw);
-                    *reinterpret_cast<uint4*>(AH + 16 * r) = h;
-                    *reinterpret_cast<uint4*>(AL + 16 * r) = lw;
+                    store_b_row(AH, AL, 16u * (uint32_t)r, make_float4(a[0], a[1], a[2], D == 2 ? a[D + 1] : 0.f));
                 }
             } else {
                 // ---- l = 1: a_0 = act(W_0 x + b_0) of point pp, features f and f + 64, recomputed from x ----
@@ -256,10 +277,7 @@ __device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restri
                         z[1 + k] = wk;
                     }
                     tc_act_fwd<D, ACT>(z, act);
-                    uint4 h, lw;
-                    split4(make_float4(z[0], z[1], z[2], D == 2 ? z[D + 1] : 0.f), h, lw);
-                    *reinterpret_cast<uint4*>(AH + blk_off(fj, pp)) = h;
-                    *reinterpret_cast<uint4*>(AL + blk_off(fj, pp)) = lw;
+                    store_b_row(AH, AL, blk_off(fj, pp), make_float4(z[0], z[1], z[2], D == 2 ? z[D + 1] : 0.f));
                 }
             }
             fence_async_smem();
@@ -301,12 +319,20 @@ __device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restri
                         tc_fence_after();
                         const uint32_t zh = tb + kDwColZ + (uint32_t)stg * 64, zl = zh + 32;
                         const uint64_t bah = bah0 + (uint64_t)(stg * (kDwStageBytes / 16)), bal = bal0 + (uint64_t)(stg * (kDwStageBytes / 16));
+#if GPE_TC_BF16_CORR
+                        constexpr uint32_t idesc16 = instr_desc(1, 128, 128, 0, 0);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) mma_ts<1, 1>(dcol, zl + 8 * j, bal + (uint64_t)(16 * j), idesc16, (stg == 0 && j == 0) ? 0u : 1u);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) mma_ts<0, 1>(dcol, zh + 8 * j, bah + (uint64_t)(16 * j), idesc, 1u);
+#else
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             mma_ts<0, 1>(dcol, zl + 8 * j, bah + (uint64_t)(16 * j), idesc, (stg == 0 && j == 0) ? 0u : 1u);
                             mma_ts<0, 1>(dcol, zh + 8 * j, bal + (uint64_t)(16 * j), idesc, 1u);
                             mma_ts<0, 1>(dcol, zh + 8 * j, bah + (uint64_t)(16 * j), idesc, 1u);
                         }
+#endif
                         mma_commit(&empty[stg]);
                         if (stg == kDwStages - 1 || it + 1 == items) mma_commit(&acc_full[buf]);
                     }

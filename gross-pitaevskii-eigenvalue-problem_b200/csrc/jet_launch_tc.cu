@@ -53,16 +53,17 @@ static int ensure_smem(K kernel, size_t smem, const char* what) {
     return 0;
 }
 
-// Two tiles in flight per CTA pair (A/B knobs, read per call).  Forward: default on (GPE_TC_TWO_TILES=0 selects the
-// one-tile kernel) -- measured on B200 at 4M points: forward 8.7 -> 8.0 ms, stash forward 10.6 -> 9.7 ms.  Reverse sweep:
-// default off (GPE_TC_TWO_TILES_REV=1 selects it) -- 13.2 -> 13.9 ms: its epilogue, not the MMA chain, is what bounds it.
+// Two tiles in flight per CTA pair (A/B knobs, read per call; GPE_TC_TWO_TILES=0 / GPE_TC_TWO_TILES_REV=0 select the one-tile
+// kernels).  Measured on B200 at 4M points, 1000 W cap (scripts/power_probe.py): forward 7.5 -> 5.9 ms, stash forward
+// 10.6 -> 8.1 ms, reverse sweep 13.6 -> 12.8 ms (with the bf16 correction products; with three tf32 products the reverse
+// sweep was epilogue-bound and gained nothing).
 static bool tc_two_tiles() {
     const char* ev = getenv("GPE_TC_TWO_TILES");
     return !(ev && ev[0] == '0');
 }
 static bool tc_two_tiles_rev() {
     const char* ev = getenv("GPE_TC_TWO_TILES_REV");
-    return ev && ev[0] == '1';
+    return !(ev && ev[0] == '0');
 }
 
 template <int D, bool STASH, int ACT>
