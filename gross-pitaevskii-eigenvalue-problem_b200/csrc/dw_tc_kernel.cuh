@@ -55,13 +55,13 @@ __device__ __forceinline__ void split4(const float4& v, uint4& h, uint4& l) {
 }
 // One 16-byte row of the B operand (a_{l-1}: the 4 streams of one point for one feature) at byte offset `off` = blk_off(f, p)
 // of the stage's images: tf32 hi values into AH; into AC the correction operand -- the fp32 lo values at the same offset, or
-// (GPE_TC_BF16_CORR) bf16 quadruples in the k order of the A operand's correction columns: per pair of points (2 g, 2 g + 1)
+// (GPE_TC_BF16_DW) bf16 quadruples in the k order of the A operand's correction columns: per pair of points (2 g, 2 g + 1)
 // one 16-byte core row of bf16(a_lo) (meets bf16(zbar)) followed, 128 B further, by one of bf16(a) (meets bf16(zbar_lo)).
 __device__ __forceinline__ void store_b_row(unsigned char* AH, unsigned char* AC, uint32_t off, const float4& v) {
     uint4 h, lw;
     split4(v, h, lw);
     *reinterpret_cast<uint4*>(AH + off) = h;
-#if GPE_TC_BF16_CORR
+#if GPE_TC_BF16_DW
     const uint32_t odd = (off >> 7) & 1u;                       // p & 1: blk_off has p * 128 and nothing else in bits 7..9
     unsigned char* c = AC + off - odd * 128u + odd * 8u;
     *reinterpret_cast<uint2*>(c) = make_uint2(pack_bf16x2(__uint_as_float(lw.x), __uint_as_float(lw.y)), pack_bf16x2(__uint_as_float(lw.z), __uint_as_float(lw.w)));
@@ -227,7 +227,7 @@ __device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restri
                     uint4 h, lw;
                     split4(v, h, lw);
                     hi[4 * pp] = h.x, hi[4 * pp + 1] = h.y, hi[4 * pp + 2] = h.z, hi[4 * pp + 3] = h.w;
-#if GPE_TC_BF16_CORR
+#if GPE_TC_BF16_DW
                     // correction columns of this warp: 0..3 = bf16 pairs of the 8 values, 4..7 = bf16 pairs of their lo parts
                     lo[2 * pp] = pack_bf16x2(v.x, v.y), lo[2 * pp + 1] = pack_bf16x2(v.z, v.w);
                     lo[4 + 2 * pp] = pack_bf16x2(__uint_as_float(lw.x), __uint_as_float(lw.y));
@@ -319,7 +319,7 @@ __device__ __forceinline__ void dw_role(int L, int act_rt, const float* __restri
                         tc_fence_after();
                         const uint32_t zh = tb + kDwColZ + (uint32_t)stg * 64, zl = zh + 32;
                         const uint64_t bah = bah0 + (uint64_t)(stg * (kDwStageBytes / 16)), bal = bal0 + (uint64_t)(stg * (kDwStageBytes / 16));
-#if GPE_TC_BF16_CORR
+#if GPE_TC_BF16_DW
                         constexpr uint32_t idesc16 = instr_desc(1, 128, 128, 0, 0);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) mma_ts<1, 1>(dcol, zl + 8 * j, bal + (uint64_t)(16 * j), idesc16, (stg == 0 && j == 0) ? 0u : 1u);

@@ -154,30 +154,32 @@ __global__ void pack_wimg_kernel(PtrArray W, int L, int Wd, int transpose, float
 // slice of a weight image (bhi / bc: descriptors of the tf32 hi image / the correction image, already advanced to the chunk).
 // Correction products (see tc_wimg.cuh): four kind::f16 MMAs on bf16 pairs, one per 8-feature group -- TMEM columns
 // 8 s .. 8 s + 3 hold bf16(a), 8 s + 4 .. 8 s + 7 hold bf16(a_lo), the image holds bf16(w_lo) | bf16(w) in the same k order.
+template <bool BF>
 __device__ __forceinline__ void mma_chunk_corr(uint32_t dcol, uint32_t ahi, uint32_t ac, uint64_t bhi, uint64_t bc, uint32_t idesc,
                                                uint32_t accum_first) {
-#if GPE_TC_BF16_CORR
-    constexpr uint32_t idesc16 = tc::instr_desc(1, 256, 128, 0, 0);
+    if (BF) {
+        constexpr uint32_t idesc16 = tc::instr_desc(1, 256, 128, 0, 0);
 #pragma unroll
-    for (int sgrp = 0; sgrp < 4; ++sgrp)
-        tc::mma_ts<1, 2>(dcol, ac + 8 * sgrp, bc + (uint64_t)(16 * sgrp), idesc16, sgrp == 0 ? accum_first : 1u);
-#else
+        for (int sgrp = 0; sgrp < 4; ++sgrp)
+            tc::mma_ts<1, 2>(dcol, ac + 8 * sgrp, bc + (uint64_t)(16 * sgrp), idesc16, sgrp == 0 ? accum_first : 1u);
+    } else {
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
-        tc::mma_ts<0, 2>(dcol, ac + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, kk == 0 ? accum_first : 1u);
-        tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, bc + (uint64_t)(16 * kk), idesc, 1u);
+        for (int kk = 0; kk < 4; ++kk) {
+            tc::mma_ts<0, 2>(dcol, ac + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, kk == 0 ? accum_first : 1u);
+            tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, bc + (uint64_t)(16 * kk), idesc, 1u);
+        }
     }
-#endif
 }
 __device__ __forceinline__ void mma_chunk_hh(uint32_t dcol, uint32_t ahi, uint64_t bhi, uint32_t idesc, uint32_t accum_first) {
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) tc::mma_ts<0, 2>(dcol, ahi + 8 * kk, bhi + (uint64_t)(16 * kk), idesc, kk == 0 ? accum_first : 1u);
 }
 // the small products first, then hi*hi: the accumulator is rounded toward zero after every MMA
+template <bool BF>
 __device__ __forceinline__ void mma_chunk_3x(uint32_t dcol, uint32_t ahi, uint32_t ac, uint64_t bhi, uint64_t bc, uint32_t idesc,
                                              uint32_t accum_first) {
 #ifndef GPE_TC_PROBE_ONE_PRODUCT   // (energy probe builds issue hi*hi alone: wrong numerics)
-    mma_chunk_corr(dcol, ahi, ac, bhi, bc, idesc, accum_first);
+    mma_chunk_corr<BF>(dcol, ahi, ac, bhi, bc, idesc, accum_first);
     mma_chunk_hh(dcol, ahi, bhi, idesc, 1u);
 #else
     mma_chunk_hh(dcol, ahi, bhi, idesc, accum_first);
@@ -200,9 +202,9 @@ template <> struct FragIO<2> {
 // A-operand fragments of one (point, feature pair): the 4 stream slots are 4 TMEM lanes (lane half lo: slots 0, 1; lane
 // half hi: slots 2, 3), the two features are adjacent columns.  Hi: tf32 values (16x256b store, 8 columns per warp);
 // C: the correction columns of the same warp -- bf16 pairs {a | a_lo} (16x128b.x2 store: columns 0..3 | 4..7), or the
-// fp32 lo values when GPE_TC_BF16_CORR = 0.
+// fp32 lo values when BF = false.
 struct AFrag { uint32_t LoHi[4], HiHi[4], LoC[4], HiC[4]; };
-template <int R>
+template <int R, bool BF>
 __device__ __forceinline__ void make_afrag(const float (&a)[2][R], AFrag& f) {
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
@@ -212,25 +214,26 @@ __device__ __forceinline__ void make_afrag(const float (&a)[2][R], AFrag& f) {
         uint32_t* H = s < 2 ? f.LoHi : f.HiHi;
         uint32_t* C = s < 2 ? f.LoC : f.HiC;
         H[2 * (s & 1)] = h0, H[2 * (s & 1) + 1] = h1;
-#if GPE_TC_BF16_CORR
-        C[s & 1] = pack_bf16x2(v0, v1);
-        C[2 + (s & 1)] = pack_bf16x2(l0, l1);
-#else
-        C[2 * (s & 1)] = __float_as_uint(l0), C[2 * (s & 1) + 1] = __float_as_uint(l1);
-#endif
+        if (BF) {
+            C[s & 1] = pack_bf16x2(v0, v1);
+            C[2 + (s & 1)] = pack_bf16x2(l0, l1);
+        } else {
+            C[2 * (s & 1)] = __float_as_uint(l0), C[2 * (s & 1) + 1] = __float_as_uint(l1);
+        }
     }
 }
 // col_hi / col_c: this warp's 8 columns of the chunk in the tf32 area / the correction area
+template <bool BF>
 __device__ __forceinline__ void store_afrag(uint32_t lane_lo, uint32_t lane_hi, uint32_t col_hi, uint32_t col_c, const AFrag& f) {
     tc::tmem_st_16x256b_x1(lane_lo + col_hi, f.LoHi);
     tc::tmem_st_16x256b_x1(lane_hi + col_hi, f.HiHi);
-#if GPE_TC_BF16_CORR
-    tc::tmem_st_16x128b_x2(lane_lo + col_c, f.LoC);
-    tc::tmem_st_16x128b_x2(lane_hi + col_c, f.HiC);
-#else
-    tc::tmem_st_16x256b_x1(lane_lo + col_c, f.LoC);
-    tc::tmem_st_16x256b_x1(lane_hi + col_c, f.HiC);
-#endif
+    if (BF) {
+        tc::tmem_st_16x128b_x2(lane_lo + col_c, f.LoC);
+        tc::tmem_st_16x128b_x2(lane_hi + col_c, f.HiC);
+    } else {
+        tc::tmem_st_16x256b_x1(lane_lo + col_c, f.LoC);
+        tc::tmem_st_16x256b_x1(lane_hi + col_c, f.HiC);
+    }
 }
 
 // 32-byte vector access to one (point, feature pair) slot of an image block (dw_tc_kernel.cuh: blk_off)
@@ -315,9 +318,9 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
         // split the four stream slots of features (f, f + 1) and hand the chunk to the MMA thread
         auto hand_over = [&](int c, const float (&a)[2][R]) {
             AFrag fr;
-            make_afrag<R>(a, fr);
+            make_afrag<R, kBfFwd>(a, fr);
             const uint32_t col = (uint32_t)(32 * c + kCw * sub);
-            store_afrag(lane_lo, lane_hi, kColAHi + col, kColALo + col, fr);
+            store_afrag<kBfFwd>(lane_lo, lane_hi, kColAHi + col, kColALo + col, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -447,7 +450,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                     for (int c = 0; c < 4; ++c) {
                         mbar_wait(&a_ready[c], acnt & 1u);
                         tc_fence_after();
-                        mma_chunk_3x(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
+                        mma_chunk_3x<kBfFwd>(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
                                      c > 0 ? 1u : 0u);
                     }
                 } else {
@@ -458,7 +461,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                     for (int c = 0; c < 4; ++c) {
                         mbar_wait(&a_ready[c], acnt & 1u);
                         tc_fence_after();
-                        mma_chunk_corr(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
+                        mma_chunk_corr<kBfFwd>(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
                                        c > 0 ? 1u : 0u);
                     }
 #pragma unroll
@@ -501,6 +504,7 @@ __device__ long long g_tc_trace[4096];
 #endif
 
 // MMA issue thread of the two-tile kernels: `steps` = (tile, layer) MMA steps of this pair in program order
+template <bool BF>
 __device__ __forceinline__ void mma2_issue(uint32_t tb, uint32_t wbase, int nmat, bool reverse, int iters, uint64_t* a_ready,
                                            uint64_t* a_free, uint64_t* d_full) {
     using tc::tc_fence_after; using tc::smem_desc; using tc::instr_desc; using tc::mma_commit_pair;
@@ -521,7 +525,7 @@ __device__ __forceinline__ void mma2_issue(uint32_t tb, uint32_t wbase, int nmat
                     tc_fence_after();
                     GPE_TRACE(blockIdx.x == 0, m, 0);
                     const uint32_t ahi = tb + k2ColA + 64u * slot;
-                    mma_chunk_3x(dcol, ahi, ahi + 32u, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc, c > 0 ? 1u : 0u);
+                    mma_chunk_3x<BF>(dcol, ahi, ahi + 32u, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc, c > 0 ? 1u : 0u);
                     mma_commit_pair(&a_free[slot], 3);
                     GPE_TRACE(blockIdx.x == 0, m, 1);
                 }
@@ -595,7 +599,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
         // split the four stream slots of features (f, f + 1), wait for the ring slot, hand the chunk to the MMA thread
         auto hand_over = [&](const float (&a)[2][R]) {
             AFrag fr;
-            make_afrag<R>(a, fr);
+            make_afrag<R, kBfFwd>(a, fr);
             const uint32_t slot = nch & 1u;
             if (nch >= 2) {                                // the MMAs that read this slot two chunks ago have retired
                 mbar_wait(&a_free[slot], ((nch >> 1) - 1) & 1u);
@@ -603,7 +607,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
             }
             GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 2);
             const uint32_t col = k2ColA + 64u * slot + (uint32_t)(kCw * sub);
-            store_afrag(lane_lo, lane_hi, col, col + 32, fr);
+            store_afrag<kBfFwd>(lane_lo, lane_hi, col, col + 32, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -761,7 +765,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
             }
         }
     } else if (cta == 0 && lane == 0) {
-        mma2_issue(tb, smem_u32(wimg_s), nmat, false, iters, a_ready, a_free, d_full);
+        mma2_issue<kBfFwd>(tb, smem_u32(wimg_s), nmat, false, iters, a_ready, a_free, d_full);
     }
     tc_fence_before();
     __syncthreads();
@@ -914,9 +918,9 @@ __device__ __forceinline__ void rev_role(const TcParams& P, const float* __restr
         const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
         auto hand_over = [&](int c, const float (&a)[2][R]) {
             AFrag fr;
-            make_afrag<R>(a, fr);
+            make_afrag<R, kBfRev>(a, fr);
             const uint32_t col = (uint32_t)(32 * c + kCw * sub);
-            store_afrag(lane_lo, lane_hi, kColAHi + col, kColALo + col, fr);
+            store_afrag<kBfRev>(lane_lo, lane_hi, kColAHi + col, kColALo + col, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -1164,7 +1168,7 @@ __device__ __forceinline__ void rev_role(const TcParams& P, const float* __restr
                     for (int c = 0; c < 4; ++c) {
                         mbar_wait(&a_ready[c], acnt & 1u);
                         tc_fence_after();
-                        mma_chunk_3x(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
+                        mma_chunk_3x<kBfRev>(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
                                      c > 0 ? 1u : 0u);
                     }
                 } else {
@@ -1175,7 +1179,7 @@ __device__ __forceinline__ void rev_role(const TcParams& P, const float* __restr
                     for (int c = 0; c < 4; ++c) {
                         mbar_wait(&a_ready[c], acnt & 1u);
                         tc_fence_after();
-                        mma_chunk_corr(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
+                        mma_chunk_corr<kBfRev>(dcol, tb + kColAHi + 32 * c, tb + kColALo + 32 * c, dhi + (uint64_t)(64 * c), dlo + (uint64_t)(64 * c), idesc,
                                        c > 0 ? 1u : 0u);
                     }
 #pragma unroll
@@ -1271,7 +1275,7 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
         const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
         auto hand_over = [&](const float (&a)[2][R]) {
             AFrag fr;
-            make_afrag<R>(a, fr);
+            make_afrag<R, kBfRev>(a, fr);
             const uint32_t slot = nch & 1u;
             if (nch >= 2) {                                // the MMAs that read this slot two chunks ago have retired
                 mbar_wait(&a_free[slot], ((nch >> 1) - 1) & 1u);
@@ -1279,7 +1283,7 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
             }
             GPE_TRACE(blockIdx.x == 0 && tid == 0, nch, 2);
             const uint32_t col = k2ColA + 64u * slot + (uint32_t)(kCw * sub);
-            store_afrag(lane_lo, lane_hi, col, col + 32, fr);
+            store_afrag<kBfRev>(lane_lo, lane_hi, col, col + 32, fr);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -1553,7 +1557,7 @@ __device__ __forceinline__ void rev2_role(const TcParams& P, const float* __rest
         dbout_acc += __shfl_xor_sync(0xffffffffu, dbout_acc, 16);
         if (lane == 0 && sub == 0) atomicAdd(&small_acc[(D + L + 1) * 128], dbout_acc);
     } else if (w == kEpiWarps && cta == 0 && lane == 0) {
-        mma2_issue(tb, smem_u32(wimg_s), nmat, true, iters, a_ready, a_free, d_full);
+        mma2_issue<kBfRev>(tb, smem_u32(wimg_s), nmat, true, iters, a_ready, a_free, d_full);
     }
     tc_fence_before();
     __syncthreads();

@@ -20,12 +20,25 @@ __host__ __device__ __forceinline__ uint32_t img_off128(int r, int c) {
 __device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
 
 // Correction products of the fp32-accurate split.  x = hi + lo with hi = tf32(x):  a w ~= a_hi w_hi + (a_lo w_hi + a_hi w_lo).
-// GPE_TC_BF16_CORR = 1 (default): the bracket, 2^-11 of the result, runs as kind::f16 MMAs on bf16 operands (K = 16 per MMA,
-// i.e. half the MMAs of a tf32 product; 8 mantissa bits are plenty for a term that small): 8 MMAs per 32-feature chunk
-// instead of 12.  = 0: all three products in tf32 (the round-1 scheme).
-#ifndef GPE_TC_BF16_CORR
-#define GPE_TC_BF16_CORR 1
+// bf16 corrections: the bracket, 2^-11 of the result, runs as kind::f16 MMAs on bf16 operands (K = 16 per MMA, i.e. half
+// the MMAs of a tf32 product; 8 mantissa bits are plenty for a term that small): 8 MMAs per 32-feature chunk instead of 12.
+// Otherwise all three products run in tf32 (the round-1 scheme).
+// Per kernel family (A/B builds: csrc/build_variant.sh tag -DGPE_TC_BF16_FWD=1 ...).  Measured on B200 against the fp64 oracle
+// (scripts/grad_err.py, gradient of the GPE2D golden, bar 1e-5) and at 4M points (scripts/power_probe.py):
+//   forward sweeps   bf16: 9.1 -> 8.1 ms (stash forward) but the loss gradient error goes 7.6e-6 -> 1.17e-5: the jets feed the
+//                    cancellation-heavy residual, so the forward keeps three tf32 products                        -> default 0
+//   reverse sweeps   bf16: 13.6 -> 12.4 ms, gradient error 7.6e-6 -> 7.8e-6                                       -> default 1
+//   dW contraction   bf16: 10.4 -> 10.2 ms (it is bound by its operand streams, not by the MMAs), 7.6e-6 -> 7.7e-6 -> default 0
+#ifndef GPE_TC_BF16_FWD
+#define GPE_TC_BF16_FWD 0
 #endif
+#ifndef GPE_TC_BF16_REV
+#define GPE_TC_BF16_REV 1
+#endif
+#ifndef GPE_TC_BF16_DW
+#define GPE_TC_BF16_DW 0
+#endif
+constexpr bool kBfFwd = GPE_TC_BF16_FWD != 0, kBfRev = GPE_TC_BF16_REV != 0;
 
 // bf16x2 {upper = hi16, lower = lo16}, round to nearest
 __device__ __forceinline__ uint32_t pack_bf16x2(float lower, float upper) {
@@ -58,14 +71,14 @@ __device__ __forceinline__ void pack_wimg_elems(const PtrArray& W, int L, int Wd
         float* base = wimg + ((size_t)l * 2 + (nn >> 6)) * 2 * kImgFloats;
         const uint32_t off = img_off128(nn & 63, k) >> 2;
         base[off] = hi;
-#if GPE_TC_BF16_CORR
-        unsigned short* corr = reinterpret_cast<unsigned short*>(base + kImgFloats);
-        const int kk = 16 * (k >> 3) + (k & 7);
-        corr[corr_off(nn & 63, kk) >> 1] = (unsigned short)(pack_bf16x2(v - hi, 0.f) & 0xffffu);
-        corr[corr_off(nn & 63, kk + 8) >> 1] = (unsigned short)(pack_bf16x2(v, 0.f) & 0xffffu);
-#else
-        base[kImgFloats + off] = v - hi;
-#endif
+        if (transpose ? kBfRev : kBfFwd) {
+            unsigned short* corr = reinterpret_cast<unsigned short*>(base + kImgFloats);
+            const int kk = 16 * (k >> 3) + (k & 7);
+            corr[corr_off(nn & 63, kk) >> 1] = (unsigned short)(pack_bf16x2(v - hi, 0.f) & 0xffffu);
+            corr[corr_off(nn & 63, kk + 8) >> 1] = (unsigned short)(pack_bf16x2(v, 0.f) & 0xffffu);
+        } else {
+            base[kImgFloats + off] = v - hi;
+        }
     }
 }
 
