@@ -367,6 +367,53 @@ int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float
     return jet_fwd_impl(desc, W, b, x, n, xform, u, g, h, nullptr, 0, ws, ws_bytes, stream);
 }
 
+// ---- forward without any allocation: the workspace is a static device array --------------------------------------------
+// (no counterpart in the reference; added for callers that cannot call cudaMalloc.)
+// The array lives in every CUDA context that loads this library until the process exits.  In HOST code `g_static_ws` is only
+// a handle for the symbol, never a device address: the address is asked for once per device (with that device current)
+// through cudaGetSymbolAddress and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_static_ws[GPE_STATIC_WS_BYTES];
+
+static int static_ws_ptr(void** out) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static void* ptrs[kMaxDev] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_error("cudaGetDevice: %s", cudaGetErrorString(e)); return -3; }
+    if (dev < 0 || dev >= kMaxDev) { set_error("device index %d outside the static-workspace table (%d)", dev, kMaxDev); return -1; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_ws);
+        if (e != cudaSuccess || !p) { set_error("cudaGetSymbolAddress(g_static_ws): %s", cudaGetErrorString(e)); return -3; }
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+int gpe_mlp_jet_fwd_noalloc(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x, int64_t n,
+                            const gpe_xform* xform, float* u, float* g, float* h, gpe_stream_t stream) {
+    size_t need = 0;
+    int rc = gpe_workspace_bytes(desc, n, &need, nullptr);
+    if (rc) return rc;
+    if (need > (size_t)GPE_STATIC_WS_BYTES) {
+        set_error("gpe_mlp_jet_fwd_noalloc: this network needs %zu bytes of workspace, the static array holds %zu (GPE_STATIC_WS_BYTES); "
+                  "use gpe_mlp_jet_fwd with a caller workspace", need, (size_t)GPE_STATIC_WS_BYTES);
+        return -1;
+    }
+    if (n > (int64_t)GPE_STATIC_MAX_POINTS) {
+        set_error("gpe_mlp_jet_fwd_noalloc: n = %lld exceeds GPE_STATIC_MAX_POINTS = %lld", (long long)n, (long long)GPE_STATIC_MAX_POINTS);
+        return -1;
+    }
+    void* ws = nullptr;
+    if ((rc = static_ws_ptr(&ws))) return rc;
+    // every byte of the workspace the forward reads (packed weights, zero padding, weight images) is rewritten by the pack
+    // kernel of this call, on `stream`, before the sweep reads it: nothing of the previous call's contents survives into it
+    return jet_fwd_impl(desc, W, b, x, n, xform, u, g, h, nullptr, 0, ws, (size_t)GPE_STATIC_WS_BYTES, stream);
+}
+
 int gpe_stash_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* bytes) {
     JetPlan p;
     int wp;

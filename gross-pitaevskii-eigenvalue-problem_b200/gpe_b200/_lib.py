@@ -61,13 +61,15 @@ lib.gpe_last_error.restype = ctypes.c_char_p
 lib.gpe_workspace_bytes.argtypes = [_desc_p, _i64, ctypes.POINTER(_sz), ctypes.POINTER(_sz)]
 lib.gpe_mlp_jet_fwd.argtypes = [_desc_p, _pp, _pp, _vp, _i64, _xf_p, _vp, _vp, _vp, _vp, _sz, _vp]
 lib.gpe_mlp_jet_bwd.argtypes = [_desc_p, _pp, _pp, _vp, _i64, _xf_p, _vp, _vp, _vp, _pp, _pp, _vp, _sz, _vp]
+lib.gpe_mlp_jet_fwd_noalloc.argtypes = [_desc_p, _pp, _pp, _vp, _i64, _xf_p, _vp, _vp, _vp, _vp]
 _loss_p = ctypes.POINTER(LossDesc)
 lib.gpe_gram_moments.argtypes = [_loss_p, _i64] + [_vp] * 8 + [_vp, _vp]
 lib.gpe_gram_adjoints.argtypes = [_loss_p, _i64] + [_vp] * 8 + [_vp] + [_vp] * 4 + [_vp]
 lib.gpe_ffma_probe.argtypes = [ctypes.c_int, ctypes.c_int, _vp, ctypes.POINTER(ctypes.c_double), _vp]
 EXPORTS = ("gpe_version", "gpe_last_error", "gpe_workspace_bytes", "gpe_mlp_jet_fwd", "gpe_mlp_jet_bwd",
            "gpe_gram_moments", "gpe_gram_adjoints", "gpe_ffma_probe", "gpe_set_tensor_path", "gpe_tc_profile",
-           "gpe_tc_timings", "gpe_stash_bytes", "gpe_mlp_jet_fwd_stash", "gpe_mlp_jet_bwd_stashed", "gpe_scalar_program")
+           "gpe_tc_timings", "gpe_stash_bytes", "gpe_mlp_jet_fwd_stash", "gpe_mlp_jet_bwd_stashed", "gpe_scalar_program",
+           "gpe_mlp_jet_fwd_noalloc")
 for _f in EXPORTS[2:]:
     getattr(lib, _f).restype = ctypes.c_int
 

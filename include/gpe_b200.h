@@ -100,6 +100,22 @@ int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float
                     int64_t n, const gpe_xform* xform, float* u, float* g, float* h, void* ws, size_t ws_bytes,
                     gpe_stream_t stream);
 
+/* gpe_mlp_jet_fwd without a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating
+ * library call on this path).  No counterpart in the reference: added for callers
+ * that cannot allocate -- code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.
+ * The forward's scratch (packed weights + tensor-core weight images; independent of n) lives in ONE file-scope
+ * `static __device__` array of GPE_STATIC_WS_BYTES (4 MiB) inside the library; every GPU whose context loads the library
+ * holds that array until the process exits.  Same arguments, outputs and error codes as gpe_mlp_jet_fwd otherwise.
+ * Limits: a descriptor whose gpe_workspace_bytes() forward figure exceeds GPE_STATIC_WS_BYTES, or n >
+ * GPE_STATIC_MAX_POINTS, is rejected with -1 and a message (gpe_last_error).
+ * Sharing: all calls on a device use the same array and it keeps the last call's contents; every byte the forward reads
+ * is rewritten by this call's own pack kernel first, so nothing needs clearing between calls -- but two calls that can
+ * OVERLAP on the GPU (different streams, or concurrent graph branches) race on it: serialise them on one stream. */
+#define GPE_STATIC_WS_BYTES (4u << 20)
+#define GPE_STATIC_MAX_POINTS (1ll << 24)
+int gpe_mlp_jet_fwd_noalloc(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
+                            int64_t n, const gpe_xform* xform, float* u, float* g, float* h, gpe_stream_t stream);
+
 /* Parameter gradient of  sum_n( u_bar[n] u + <g_bar[n], g> + <h_bar[n], h> ).  Any of
  * u_bar/g_bar/h_bar may be NULL (= zeros).  dW[l], db[l] have the shapes of W[l], b[l]. */
 int gpe_mlp_jet_bwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
