@@ -571,7 +571,8 @@ def run_b200(args):
             kname = max(tc_ms, key=tc_ms.get)
             kms = tc_ms[kname]
             alg = {"stash_forward": f_contr, "reverse_sweep": f_contr, "dw_contraction": f_contr, "fused_backward": 2 * f_contr}[kname]
-            sym = {"stash_forward": f"tcp::jet_fwd2_tc_kernel<{d},true,ACT_TANH>", "reverse_sweep": f"tcp::jet_rev_tc_kernel<{d},ACT_TANH>",
+            sym = {"stash_forward": f"tcp::jet_fwd2_tc_kernel<{d},true,ACT_TANH>", "reverse_sweep": (f"tcp::jet_rev_tc_kernel<{d},ACT_TANH>" if os.environ.get("GPE_TC_TWO_TILES_REV", "1")[:1] == "0"
+                                     else f"tcp::jet_rev2_tc_kernel<{d},ACT_TANH>"),
                    "dw_contraction": f"tcp::dw_tc_kernel<{d},ACT_TANH>", "fused_backward": f"tcp::bwd_fused_tc_kernel<{d},ACT_TANH>"}[kname]
             achieved = alg * n / (kms * 1e-3) / 1e12
             # image blocks of 2 KB per point and hidden matrix l = 1..L-1: st_l written by the stash forward, read by the
@@ -589,6 +590,10 @@ def run_b200(args):
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",
                 "tf32_peak": bf16 / 2, "effective_3xtf32_peak": bf16 / 6, "frac_of_3xtf32_peak": achieved / (bf16 / 6),
                 "algorithmic_flops_per_point": alg, "executed_tensor_flops_per_point": 3 * 2 * W * W * (2 + d) * (L - 1) * (alg // f_contr),
+                # same multiply-adds in every variant; the reverse sweep issues its two correction products as bf16 kind::f16 MMAs
+                # (K = 16: 8 MMA issue slots per 32-feature chunk instead of 12), forward and dW keep three tf32 products
+                "correction_products": {"stash_forward": "tf32", "reverse_sweep": "bf16 (kind::f16)", "dw_contraction": "tf32",
+                                        "fused_backward": "bf16 (sweep) + tf32 (dW)"}[kname],
                 "kernel_ms_per_step": kms, "kernel_launches_per_step": launches, "tensor_step_ms": tc_ms,
                 "traffic": (trow or {}).get("dram_bytes_per_launch"),
                 "traffic_source": ({"file": "profiles/r2_ncu_traffic.json", "git_sha": tinfo.get("git_sha"),
