@@ -21,6 +21,8 @@ Reference classes mirrored (paths under /root/reference):
 There is no CPU path: tensors must live on a CUDA device.
 """
 import math
+import os
+import weakref
 
 import numpy as np
 import torch
@@ -84,6 +86,53 @@ _ACT_OF = {nn.Tanh: ops.ACT_TANH, ShiftedTanh: ops.ACT_SHIFTED_TANH, nn.LeakyReL
 _generation = [0]
 
 
+class _SplitJets(torch.autograd.Function):
+    """Cut the jets of one batched kernel call over several point sets back into per-set tensors.  Backward: ONE
+    concatenation per stream (a set that did not ask for derivatives, or whose output went unused, contributes zeros),
+    so the reverse kernels run once for all sets."""
+
+    @staticmethod
+    def forward(ctx, u, g, h, sizes, with_derivs):
+        ctx.sizes, ctx.with_derivs = sizes, with_derivs
+        ctx.gshape, ctx.hshape = tuple(g.shape), tuple(h.shape)
+        ctx.set_materialize_grads(False)
+        outs, off = [], 0
+        for n, dv in zip(sizes, with_derivs):
+            outs.append(u.narrow(0, off, n))
+            if dv:
+                outs.append(g.narrow(0, off, n))
+                outs.append(h.narrow(0, off, n))
+            off += n
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        it = iter(grads)
+        gu, gg, gh = [], [], []
+        for dv in ctx.with_derivs:
+            gu.append(next(it))
+            gg.append(next(it) if dv else None)
+            gh.append(next(it) if dv else None)
+        ref = next((t for t in grads if t is not None), None)
+        if ref is None:
+            return None, None, None, None, None
+
+        def join(parts, shape):
+            if all(t is None for t in parts) or 0 in shape:
+                return None
+            if all(t is not None for t in parts):
+                return torch.cat(parts, 0)
+            out, off = ref.new_zeros(shape), 0
+            for n, t in zip(ctx.sizes, parts):
+                if t is not None:
+                    out.narrow(0, off, n).copy_(t)
+                off += n
+            return out
+
+        n_all = sum(ctx.sizes)
+        return join(gu, (n_all,)), join(gg, ctx.gshape), join(gh, ctx.hshape), None, None
+
+
 def invalidate_caches():
     """Drop every model's cached jets / moments (parameters were changed in a way autograd cannot see)."""
     _generation[0] += 1
@@ -101,6 +150,13 @@ class JetMLP(nn.Module):
     #: (every rank passes its own block); boundary / data points are REPLICATED (every rank passes the same few points):
     #: those terms go through `gdist.replicated_term`, so the SUM all-reduce of the gradients counts them once.
     group = None
+    #: One kernel call for all point sets of a step.  A training step evaluates the network on several point sets -- the
+    #: collocation jets, the mirrored values of symmetry_loss, the handful of boundary points -- each its own forward /
+    #: backward launch train; below ~20k points a launch is latency, not work (one wave of tiles), so the sets a step asked
+    #: for are remembered and the NEXT step that starts with one of them evaluates all of them in a single batched call
+    #: (jets for every set; the value-only sets ignore theirs).  Applies while the sets together hold at most
+    #: `batch_points` points and the same tensors are passed again; 0 disables.  (GPE_BATCH_POINTS overrides.)
+    batch_points = 32768
     #: optional min-max feature scaling x -> (x - lb) / (ub - lb) in front of the first layer
     #: (S/helmholtz_2D_circle.py:89-94); sequences of length d, folded into (W_0, b_0) per call
     input_lb = None
@@ -148,6 +204,8 @@ class JetMLP(nn.Module):
         pver = (_generation[0],) + tuple(p._version for lin in lins for p in (lin.weight, lin.bias))
         cache = self.__dict__.setdefault("_jet_cache", {})
         if cache.get("pver") != pver:          # parameters stepped: drop the previous step's graphs
+            # the point sets that step evaluated and used: [weakref(x), jet kind, xform, used]
+            self.__dict__["_jet_plan"] = [e for e in cache.get("requests", ()) if e[3]]
             cache.clear()
             cache["pver"] = pver
         # Only results that belong to a live autograd graph are shared between the loss methods of one step (their
@@ -157,7 +215,16 @@ class JetMLP(nn.Module):
         key = (id(x), x._version, kind, xform, True)
         hit = cache.get(key) if use_cache else None
         if hit is not None and hit[0] is x:
+            for e in cache.get("requests", ()):
+                if e[1] == kind and e[2] == xform and e[0]() is x:
+                    e[3] = True
             return hit[1]
+        if use_cache:
+            reqs = cache.setdefault("requests", [])
+            if not reqs and self._run_plan(cache, lins, x, kind, xform):
+                return self.jets(x, derivs, xform)          # a cache hit now (marks the set as used)
+            if len(reqs) <= 8:
+                reqs.append([weakref.ref(x), kind, xform, True, id(x), tuple(x.shape)])
         xin = x if x.is_contiguous() and x.dtype == torch.float32 else x.contiguous().float()
         Ws, bs = [lin.weight for lin in lins], [lin.bias for lin in lins]
         if self.input_lb is not None:
@@ -165,6 +232,11 @@ class JetMLP(nn.Module):
         out = ops.mlp_jets(xin, Ws, bs, self._act_kind(), kind, xform, self.precision)
         if not use_cache:
             return out
+        self._cache_put(cache, key, x, out)
+        return out
+
+    @staticmethod
+    def _cache_put(cache, key, x, out):
         cache[key] = (x, out)
 
         def _invalidate(_grad, cache=cache, key=key):
@@ -178,7 +250,51 @@ class JetMLP(nn.Module):
         for t in out:
             if t.requires_grad:
                 t.register_hook(_invalidate)
-        return out
+
+    def _run_plan(self, cache, lins, x, kind, xform):
+        """First evaluation of a step: if the previous step evaluated this point set together with others (same tensors,
+        small enough), evaluate all of them now in one batched call and file the pieces in the cache.  True = done."""
+        plan = self.__dict__.get("_jet_plan")
+        limit = int(os.environ.get("GPE_BATCH_POINTS", self.batch_points))
+        if not plan or len(plan) < 2 or len(plan) > 8 or limit <= 0 or self.jet_mode == "full":
+            return False
+        # the step must open the way the previous one did: same kind of request on the same tensor -- or on a new tensor of
+        # the same shape (a freshly sampled / uploaded collocation block), which then takes the old one's place in every set
+        first = plan[0]
+        if first[1] != kind or first[2] != xform or first[5] != tuple(x.shape):
+            return False
+        sets = [(x if e[4] == first[4] else e[0](), e[1], e[2]) for e in plan]
+        kinds = {k for _, k, _ in sets if k != ops.JET_VALUE}
+        if len(kinds) > 1:
+            return False
+        if len({(id(t), k, xf) for t, k, xf in sets}) != len(sets):
+            return False
+        for t, k, xf in sets:
+            if (t is None or not t.is_cuda or t.device != x.device or t.dtype != torch.float32 or t.dim() != 2 or t.shape[1] != x.shape[1]
+                    or not t.is_contiguous() or (xf is not None and k != ops.JET_VALUE)):
+                return False
+        if sum(t.shape[0] for t, _, _ in sets) > limit or min(t.shape[0] for t, _, _ in sets) == 0:
+            return False
+        main = next(iter(kinds)) if kinds else ops.JET_VALUE
+        parts = []
+        for t, k, xf in sets:
+            if xf is None:
+                parts.append(t)
+            else:   # mirrored coordinates a x + b (symmetry_loss): python scalars only, so the step stays graph-capturable
+                cols = [t.detach()[:, i:i + 1] * float(xf[0][i]) + float(xf[1][i]) for i in range(t.shape[1])]
+                parts.append(cols[0] if len(cols) == 1 else torch.cat(cols, 1))
+        Ws, bs = [lin.weight for lin in lins], [lin.bias for lin in lins]
+        if self.input_lb is not None:
+            Ws[0], bs[0] = self._first_layer_folded(Ws[0], bs[0])
+        u, g, h = ops.mlp_jets(torch.cat(parts, 0), Ws, bs, self._act_kind(), main, None, self.precision)
+        flags = tuple(k != ops.JET_VALUE for _, k, _ in sets)
+        pieces = iter(_SplitJets.apply(u, g, h, tuple(t.shape[0] for t, _, _ in sets), flags))
+        for (t, k, xf), dv in zip(sets, flags):
+            ui = next(pieces)
+            out = (ui, next(pieces), next(pieces)) if dv else (ui, ui.new_empty((t.shape[0], 0)), ui.new_empty((t.shape[0], 0)))
+            self._cache_put(cache, (id(t), t._version, k, xf, True), t, out)
+        cache["requests"] = [[weakref.ref(t), k, xf, False, id(t), tuple(t.shape)] for t, k, xf in sets]
+        return True
 
     def _net(self, x):
         """Network output [N,1]."""

@@ -1,8 +1,9 @@
 """Digest of one `ncu --set full` report: headline metrics + SASS opcode / stall histogram + hottest lines.
-usage: ncu_digest.py report.ncu-rep"""
+usage: ncu_digest.py report.ncu-rep [kernel-name-regex]   (a report that holds several kernels: one digest per regex)"""
 import csv, collections, subprocess, sys, io
 rep = sys.argv[1]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+flt = ["--kernel-name", "regex:" + sys.argv[2]] if len(sys.argv) > 2 else []
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"] + flt, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[2]
 want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
@@ -12,9 +13,14 @@ want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread"]
 for h, u, v in zip(hdr, units, vals):
     if h in want: print(f"{h:70s} {v} {u}")
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+print("kernel:", vals[hdr.index("Kernel Name")][:100])
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + flt, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hdr = rows[1]; data = rows[2:]
+hdr = rows[1]
+data = []
+for r in rows[2:]:          # ncu prints the kernel's listing twice: keep the first block
+    if len(r) != len(hdr): break
+    data.append(r)
 iS = hdr.index("# Samples"); iI = hdr.index("Instructions Executed"); iSrc = hdr.index("Source")
 tot_s = sum(int(r[iS]) for r in data); tot_i = sum(int(r[iI]) for r in data)
 print("total samples", tot_s, "warp instructions", tot_i)

@@ -362,3 +362,54 @@ def test_scalar_program_against_autograd():
     ga = torch.autograd.grad((torch.stack(list(got)) * w).sum(), m)[0]
     gb = torch.autograd.grad(sum(wi * t for wi, t in zip(w, want)), m)[0]
     assert float((ga - gb).abs().max()) <= 1e-13 * float(gb.abs().max())
+
+
+# ------------------------------------------------------------------------------------------- one call per small step
+def test_small_step_evaluates_all_point_sets_in_one_call():
+    """BASELINE config 1 in small: collocation jets, mirrored values (symmetry_loss) and the two boundary points.  The first
+    step runs three network evaluations; from the second step on (same tensors, <= batch_points) they are one batched call
+    with the same loss and gradient; a freshly uploaded collocation block of the same shape keeps the batching."""
+    import gpe_b200
+    from gpe_b200 import ops
+    torch.manual_seed(3)
+    model = gpe_b200.RootGPE1D([1, 100, 100, 100, 1], mode=0, gamma=1.0)
+    model.apply(po.xavier_bias001_)
+    model = model.cuda()
+    lo, hi, n = -10.0, 10.0, 3000
+    X = (torch.rand(n, 1, device="cuda") * (hi - lo) + lo).requires_grad_(True)
+    bp, bv = torch.tensor([[lo], [hi]], device="cuda"), torch.zeros(2, 1, device="cuda")
+
+    def loss_fn(Xc):
+        pde, _, _, full_u = model.pde_loss(3, Xc, model.forward(Xc), 1.0, "harmonic")
+        return pde + 10.0 * model.boundary_loss(bp, bv) + 20.0 * model.normalization_loss(full_u, (hi - lo) / n) + 5.0 * model.symmetry_loss(Xc, lo, hi)
+
+    calls, real = [], ops.mlp_jets
+
+    def counting(x, *a, **k):
+        calls.append(int(x.shape[0]))
+        return real(x, *a, **k)
+
+    def grads(Xc):
+        for p in model.parameters():
+            p.grad = None
+        del calls[:]
+        loss = loss_fn(Xc)
+        loss.backward()
+        return float(loss), torch.cat([p.grad.reshape(-1) for p in model.parameters()]).double(), list(calls)
+
+    ops.mlp_jets = counting
+    try:
+        l1, g1, c1 = grads(X)
+        gpe_b200.models.invalidate_caches()                     # stands in for the optimizer step between two evaluations
+        l2, g2, c2 = grads(X)
+        gpe_b200.models.invalidate_caches()
+        l3, g3, c3 = grads(X)                            # the batched step hands its plan on
+        X2 = X.detach().clone().requires_grad_(True)     # a new tensor with the same points, e.g. the next uploaded block
+        gpe_b200.models.invalidate_caches()
+        l4, g4, c4 = grads(X2)
+    finally:
+        ops.mlp_jets = real
+    assert sorted(c1) == [2, n, n] and c2 == [2 * n + 2] and c3 == [2 * n + 2] and c4 == [2 * n + 2], (c1, c2, c3, c4)
+    for l, g in ((l2, g2), (l3, g3), (l4, g4)):
+        assert abs(l - l1) <= 1e-5 * abs(l1)
+        assert float((g - g1).norm() / g1.norm()) < 1e-5
