@@ -590,9 +590,9 @@ def run_b200(args):
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",
                 "tf32_peak": bf16 / 2, "effective_3xtf32_peak": bf16 / 6, "frac_of_3xtf32_peak": achieved / (bf16 / 6),
                 "algorithmic_flops_per_point": alg, "executed_tensor_flops_per_point": 3 * 2 * W * W * (2 + d) * (L - 1) * (alg // f_contr),
-                # same multiply-adds in every variant; the reverse sweep issues its two correction products as bf16 kind::f16 MMAs
-                # (K = 16: 8 MMA issue slots per 32-feature chunk instead of 12), forward and dW keep three tf32 products
-                "correction_products": {"stash_forward": "tf32", "reverse_sweep": "bf16 (kind::f16)", "dw_contraction": "tf32",
+                # same multiply-adds in every variant; the sweeps issue their two correction products as bf16 kind::f16 MMAs
+                # (K = 16: 8 MMA issue slots per 32-feature chunk instead of 12), the dW contraction keeps three tf32 products
+                "correction_products": {"stash_forward": "bf16 (kind::f16)", "reverse_sweep": "bf16 (kind::f16)", "dw_contraction": "tf32",
                                         "fused_backward": "bf16 (sweep) + tf32 (dW)"}[kname],
                 "kernel_ms_per_step": kms, "kernel_launches_per_step": launches, "tensor_step_ms": tc_ms,
                 "traffic": (trow or {}).get("dram_bytes_per_launch"),

@@ -130,6 +130,18 @@ struct TcScope {
     }
 };
 
+// tcgen05 accumulation truncates: every MMA rounds the fp32 accumulator toward zero, so a hidden-layer contraction (32-48 MMAs)
+// comes out low by a few 2^-24 -- always in the same direction, which the residual of the loss (differences of nearly equal
+// terms) amplifies.  The forward epilogue multiplies what it reads from tensor memory by 1 + beta 2^-24.  Measured against the
+// fp64 oracle (scripts/debias_sweep.py), gradient of the GPE2D golden / jets of random networks:
+//   three tf32 products   beta 0: 7.8e-6   beta 4: 1.0e-6 (optimum; jets 1.3-1.6x better; per-case optima between 4 and 10)
+//   bf16 corrections      beta 0: 1.19e-5  beta 8: 1.4e-6 (jets of [1,128x4,1] 2.7x better, the 2-D nets unchanged)
+// beta = GPE_TC_DEBIAS_FWD (read per call), default kTcDebiasFwd.  The reverse sweep's adjoints gain nothing measurable.
+static float tc_debias() {
+    const char* ev = getenv("GPE_TC_DEBIAS_FWD");
+    const float beta = ev ? (float)atof(ev) : tcp::kTcDebiasFwd;
+    return 1.f + beta * 5.9604644775390625e-8f;
+}
 static int tc_env_mode(const char* name, int dflt);
 static int tc_interleave() {
     static int v = -1;
@@ -274,7 +286,7 @@ size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, const float* resident, float* zb,
                   double* dWacc, float* small_acc, cudaStream_t s, const unsigned int** abort_flag) {
-    tcp::TcParams Pf{L, act, wimg_fwd, small, tc_interleave_fwd()}, Pr{L, act, wimg_rev, small, tc_interleave()};
+    tcp::TcParams Pf{L, act, wimg_fwd, small, tc_debias(), tc_interleave_fwd()}, Pr{L, act, wimg_rev, small, 1.f, tc_interleave()};
     const long long chunk = tc_bwd_chunk(n);
     return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag)
                   : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag);
@@ -285,7 +297,7 @@ size_t tc_resident_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (s
 
 int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
                   float* g, float* h, float* resident, cudaStream_t s) {
-    tcp::TcParams P{L, act, wimg, small, tc_interleave_fwd()};
+    tcp::TcParams P{L, act, wimg, small, tc_debias(), tc_interleave_fwd()};
     if (resident) return d == 1 ? fwd_tc<1, true>(P, x, n, u, g, h, resident, s) : fwd_tc<2, true>(P, x, n, u, g, h, resident, s);
     return d == 1 ? fwd_tc<1, false>(P, x, n, u, g, h, nullptr, s) : fwd_tc<2, false>(P, x, n, u, g, h, nullptr, s);
 }

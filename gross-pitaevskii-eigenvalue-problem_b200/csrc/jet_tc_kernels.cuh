@@ -44,6 +44,7 @@ struct TcParams {
     int act;
     const float* wimg;     // [L-1][cta 2][hi,lo][kImgFloats]
     const float* small;    // W0t[D][128], b[L][128], wout[128], bout[4]   (same pack as the FFMA path)
+    float debias;          // forward sweeps: multiplier on every accumulator read, 1 + beta 2^-24 (tc_debias, jet_launch_tc.cu)
     int interleave;        // order of the 16 hi*hi MMAs of a layer relative to its 32 correction MMAs (the accumulator is rounded
                            // toward zero after every MMA, so what lands late lands on a large accumulator):
                            //   0: all corrections first, hi*hi last -- 24 MMAs trail the last chunk, fewest roundings at size;
@@ -392,7 +393,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
 #pragma unroll
-                        for (int s = 0; s < R; ++s) a[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
+                        for (int s = 0; s < R; ++s) a[e][s] = P.debias * __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
                         a[e][0] += e ? b2.y : b2.x;
 #pragma unroll
                         for (int s = 1; s < 4; ++s) sv8[4 * e + s] = s < R ? a[e][s] : 0.f;
@@ -696,7 +697,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
 #pragma unroll
-                    for (int s = 0; s < R; ++s) a[e][s] = __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
+                    for (int s = 0; s < R; ++s) a[e][s] = P.debias * __uint_as_float(s < 2 ? LoHi[2 * (s & 1) + e] : HiHi[2 * (s & 1) + e]);
                     a[e][0] += e ? b2.y : b2.x;
 #pragma unroll
                     for (int s = 1; s < 4; ++s) sv8[4 * e + s] = s < R ? a[e][s] : 0.f;

@@ -23,14 +23,15 @@ __device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v
 // bf16 corrections: the bracket, 2^-11 of the result, runs as kind::f16 MMAs on bf16 operands (K = 16 per MMA, i.e. half
 // the MMAs of a tf32 product; 8 mantissa bits are plenty for a term that small): 8 MMAs per 32-feature chunk instead of 12.
 // Otherwise all three products run in tf32 (the round-1 scheme).
-// Per kernel family (A/B builds: csrc/build_variant.sh tag -DGPE_TC_BF16_FWD=1 ...).  Measured on B200 against the fp64 oracle
-// (scripts/grad_err.py, gradient of the GPE2D golden, bar 1e-5) and at 4M points (scripts/power_probe.py):
-//   forward sweeps   bf16: 9.1 -> 8.1 ms (stash forward) but the loss gradient error goes 7.6e-6 -> 1.17e-5: the jets feed the
-//                    cancellation-heavy residual, so the forward keeps three tf32 products                        -> default 0
-//   reverse sweeps   bf16: 13.6 -> 12.4 ms, gradient error 7.6e-6 -> 7.8e-6                                       -> default 1
-//   dW contraction   bf16: 10.4 -> 10.2 ms (it is bound by its operand streams, not by the MMAs), 7.6e-6 -> 7.7e-6 -> default 0
+// Per kernel family (A/B builds: csrc/build_variant.sh tag -DGPE_TC_BF16_FWD=0 ...).  Measured on B200 against the fp64 oracle
+// (scripts/grad_err.py / scripts/debias_sweep.py: gradient of the GPE2D golden, bar 1e-5) and at 4M points (scripts/power_probe.py):
+//   forward sweeps   bf16: stash forward 9.1 -> 7.9 ms.  Gradient error 7.8e-6 (tf32) / 1.19e-5 (bf16) with the raw accumulators,
+//                    1.0e-6 / 1.4e-6 with the de-biased epilogue (kTcDebiasFwd below): what the residual of the loss amplifies
+//                    is the tensor core's truncation bias, not the width of the correction products                -> default 1
+//   reverse sweeps   bf16: 13.6 -> 12.4 ms, gradient error unchanged to 2 %                                        -> default 1
+//   dW contraction   bf16: 10.4 -> 10.2 ms (it is bound by its operand streams, not by the MMAs)                   -> default 0
 #ifndef GPE_TC_BF16_FWD
-#define GPE_TC_BF16_FWD 0
+#define GPE_TC_BF16_FWD 1
 #endif
 #ifndef GPE_TC_BF16_REV
 #define GPE_TC_BF16_REV 1
@@ -39,6 +40,8 @@ __device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v
 #define GPE_TC_BF16_DW 0
 #endif
 constexpr bool kBfFwd = GPE_TC_BF16_FWD != 0, kBfRev = GPE_TC_BF16_REV != 0;
+// de-bias factor of the forward epilogue in units of 2^-24 (see tc_debias, jet_launch_tc.cu): measured optimum per scheme
+constexpr float kTcDebiasFwd = kBfFwd ? 8.f : 4.f;
 
 // bf16x2 {upper = hi16, lower = lo16}, round to nearest
 __device__ __forceinline__ uint32_t pack_bf16x2(float lower, float upper) {

@@ -5,6 +5,8 @@ The loop bodies are the oracle's own (`root_train_terms`, `final_train_terms`, .
 reference method names, so the same function drives the oracle class on the CPU and the B200 class on
 the GPU.  Tolerances (north-star): loss terms and parameter gradients 1e-5 relative in fp32 -- measured
 here against the float64 goldens, so the bound includes the kernels' own fp32 rounding."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -14,8 +16,10 @@ from helpers import scalar, load_weights, golden_grads, flat, rel_err, model_gra
     OPT_VARIANT_GOLDENS, opt_variant_model_and_kwargs
 
 pytestmark = pytest.mark.gpu
-TOL = 1e-5    # north-star: loss terms AND parameter gradients within 1e-5 relative (measured: 1-4e-6)
-GTOL = 1e-5
+# north-star: loss terms AND parameter gradients within 1e-5 relative (measured: 1-4e-6).  GPE_TEST_TOL only ever TIGHTENS
+# the bar (margin probes of kernel variants: which goldens sit close to it)
+TOL = min(1e-5, float(os.environ.get("GPE_TEST_TOL", "1e-5")))
+GTOL = TOL
 
 
 def close(a, b, tol=TOL):
