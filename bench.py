@@ -580,7 +580,7 @@ def run_b200(args):
             hbm_bytes = {"stash_forward": 4 * d + 2048 * (L - 1), "reverse_sweep": 4 * d + 4 * (2 + d) + 2 * 2048 * (L - 1),
                          "dw_contraction": 4 * d + 2048 * (L - 1) + 2048 * (L - 2),
                          "fused_backward": 4 * d + 4 * (2 + d) + 2048 * (L - 1) + 2048 * (L - 2)}[kname]
-            chunk = 262144
+            chunk = int(os.environ.get("GPE_TC_CHUNK", 1048576))
             launches = 1 if kname in ("stash_forward", "fused_backward") else (n + chunk - 1) // chunk
             tfile = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
             tinfo = json.load(open(tfile)) if os.path.exists(tfile) else {}

@@ -275,7 +275,12 @@ static int bwd_tc(const tcp::TcParams& Pf, const tcp::TcParams& Pr, const float*
 
 // chunk of points processed per (stash forward, reverse sweep, dW contraction) round
 long long tc_bwd_chunk(long long n) {
-    const long long cap = 262144;
+    static long long cap = 0;   // GPE_TC_CHUNK (points, multiple of 64; read once): zbar + recompute-stash workspace = 12 KB per point of it
+    if (cap == 0) {
+        const char* ev = getenv("GPE_TC_CHUNK");
+        long long v = ev ? atoll(ev) : 0;
+        cap = v >= 64 ? (v + 63) / 64 * 64 : 1048576;   // measured at 4M points: 22.6 ms (262144) / 22.1 (1M) / 22.05 (4M)
+    }
     long long c = (n + 63) / 64 * 64;
     return c < cap ? (c > 0 ? c : 64) : cap;
 }
