@@ -333,7 +333,7 @@ def trace_scale(pred, allow_factor=False):
         if fn is None:
             return None
         name = fn.name()
-        if "JetFunction" in name:
+        if "JetFunction" in name or "_SplitJets" in name:      # the jet node, or its piece of a batched call (_run_plan)
             return s
         if name in ("UnsqueezeBackward0", "ViewBackward0", "AliasBackward0", "CloneBackward0", "ReshapeAliasBackward0",
                     "UnsafeViewBackward0", "SqueezeBackward1", "ToCopyBackward0"):
