@@ -296,6 +296,12 @@ class JetMLP(nn.Module):
         cache["requests"] = [[weakref.ref(t), k, xf, False, id(t), tuple(t.shape)] for t, k, xf in sets]
         return True
 
+    def _check_predictions(self, predictions):
+        """Loss methods that rebuild u from the jets of `inputs` ignore the `predictions` argument: make sure it IS the
+        network output of this step (checked through its autograd history; a tensor without one cannot be told apart)."""
+        if predictions is not None and predictions.grad_fn is not None and trace_scale(predictions) != 1.0:
+            raise RuntimeError("gpe_b200: `predictions` must be model.forward(inputs) (use models.patch for anything else)")
+
     def _net(self, x):
         """Network output [N,1]."""
         return self.jets(x)[0].unsqueeze(1)
@@ -1116,10 +1122,12 @@ class GPE2D(JetMLP):
 
     def riesz_loss(self, predictions, inputs):
         """:112-151 (sum form)."""
+        self._check_predictions(predictions)
         return self._terms(self._M(inputs)[0])[2].float()
 
     def pde_loss(self, inputs, predictions):
         """:154-213 -> (pde_loss + L_f + L_lambda, pde_residual, lambda_pde)."""
+        self._check_predictions(predictions)
         M, V = self._M(inputs)
         pde_all, mu, _ = self._terms(M)
         u, g, h = self.jets(inputs)
@@ -1372,10 +1380,6 @@ class LearnableKHelmholtz2D(JetMLP):
         """:84-103."""
         return self.adaptive_bc_scale * gdist.replicated_term(torch.mean((self.forward(x_bc) - y_bc) ** 2), self.group)
 
-    def _check_predictions(self, predictions):
-        if predictions is not None and trace_scale(predictions) != 1.0:
-            raise RuntimeError("gpe_b200: `predictions` must be model.forward(inputs) (use models.patch for anything else)")
-
     def riesz_loss(self, predictions, inputs):
         """:105-127: sum |grad u|^2."""
         self._check_predictions(predictions)
@@ -1413,7 +1417,33 @@ def patch(model, jet_mode="full", precision=ops.PREC_AUTO, input_lb=None, input_
     def forward(self, x):
         return self._net(x)
 
+    # what the module's own forward computes on a probe batch: the rerouted forward must reproduce it (a forward that does
+    # more than the bare network -- e.g. the `* sin(pi x)` factor of R/box_pinn_simulation.py:119-130 -- cannot be patched)
+    probe = want = None
+    p0 = next(model.parameters(), None)
+    if p0 is not None and p0.is_cuda:
+        lins = [m for m in model.modules() if isinstance(m, nn.Linear)]
+        d = lins[0].in_features
+        lo = torch.tensor([float(v) for v in input_lb], device=p0.device) if input_lb is not None else -torch.ones(d, device=p0.device)
+        hi = torch.tensor([float(v) for v in input_ub], device=p0.device) if input_ub is not None else torch.ones(d, device=p0.device)
+        gen = torch.Generator(device=p0.device).manual_seed(1)
+        probe = lo + (hi - lo) * torch.rand(16, d, device=p0.device, generator=gen)
+        try:
+            with torch.no_grad():
+                want = model(probe)
+        except Exception:      # a forward that needs more than x (module globals not set yet ...): nothing to compare with
+            probe = want = None
     model.__class__ = type(cls.__name__ + "B200", (JetMLP, cls), {"forward": forward, "jet_mode": jet_mode, "precision": precision})
     if input_lb is not None:
         model.input_lb, model.input_ub = [float(v) for v in input_lb], [float(v) for v in input_ub]
+    if want is not None:
+        with torch.no_grad():
+            got = model(probe)
+        if tuple(got.shape) != tuple(want.shape) or not torch.allclose(got, want.float(), rtol=1e-4, atol=1e-5):
+            model.__class__ = cls
+            for k in ("input_lb", "input_ub"):
+                model.__dict__.pop(k, None)
+            raise ValueError("gpe_b200.patch: this module's forward(x) is not its bare network (a boundary factor, an input "
+                             "scaling without input_lb / input_ub, an output transform ...): use the matching drop-in class "
+                             "instead, or pass the scaling bounds")
     return model

@@ -122,6 +122,9 @@ def gram_moments(u, g=None, h=None, nm=None, *, x=None, base=None, V=None, q=Non
     u, g, h and nm."""
     if lap_cols is None:
         lap_cols = 0 if h is None or h.dim() != 2 else (2 if h.shape[1] == 3 else h.shape[1])
+    if int(nl_kind) == NL_POW and float(nl_power) != float(int(nl_power)):
+        raise ValueError(f"gpe_b200: NL_POW evaluates u**p by repeated multiplication and needs an integer p (got {nl_power}); "
+                         "use NL_ABSPOW (|u|^(p-1) u) for a fractional power")
     return _GramMoments.apply(u, g, h, nm, x, base, V, q, int(d), int(nl_kind), float(nl_power), float(scale), int(bfactor),
                               int(sym_sign), int(lap_cols))
 

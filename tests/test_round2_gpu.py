@@ -421,3 +421,45 @@ def test_small_step_evaluates_all_point_sets_in_one_call():
     for l, g in ((l2, g2), (l3, g3), (l4, g4)):
         assert abs(l - l1) <= 1e-5 * abs(l1)
         assert float((g - g1).norm() / g1.norm()) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------- loud failures on edge inputs
+def test_edge_inputs_fail_loudly():
+    """a patched forward that is not the bare network, a `predictions` argument that is not the network
+    output, and a fractional NL_POW power used to give silently different numbers."""
+    import gpe_b200
+    from gpe_b200 import ops
+
+    class WithFactor(torch.nn.Module):           # R/box_pinn_simulation.py:119-130: forward = network(x) * sin(pi x)
+        def __init__(self):
+            super().__init__()
+            self.network = torch.nn.Sequential(torch.nn.Linear(1, 64), torch.nn.Tanh(), torch.nn.Linear(64, 64), torch.nn.Tanh(), torch.nn.Linear(64, 1))
+
+        def forward(self, x):
+            return self.network(x) * torch.sin(np.pi * x)
+
+    m = WithFactor().cuda()
+    with pytest.raises(ValueError, match="not its bare network"):
+        gpe_b200.patch(m)
+    assert type(m) is WithFactor                    # left as it was
+    x = torch.rand(8, 1, device="cuda")
+    assert torch.allclose(m(x), m.network(x) * torch.sin(np.pi * x))
+
+    class Plain(WithFactor):
+        def forward(self, x):
+            return self.network(x)
+
+    p = gpe_b200.patch(Plain().cuda())
+    assert torch.allclose(p(x), p.network(x), rtol=1e-4, atol=1e-5)
+
+    g2 = _gpe2d()
+    X = (torch.rand(300, 2, device="cuda") * 4 - 2).requires_grad_(True)
+    with pytest.raises(RuntimeError, match="must be model.forward"):
+        g2.pde_loss(X, 2.0 * g2.forward(X))
+    with pytest.raises(RuntimeError, match="must be model.forward"):
+        g2.riesz_loss(2.0 * g2.forward(X), X)
+    g2.pde_loss(X, g2.forward(X))
+
+    u = torch.rand(64, device="cuda")
+    with pytest.raises(ValueError, match="integer p"):
+        ops.gram_moments(u, None, None, None, d=1, nl_kind=ops.NL_POW, nl_power=2.5)
