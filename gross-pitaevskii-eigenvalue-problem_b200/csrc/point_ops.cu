@@ -310,3 +310,65 @@ extern "C" int gpe_scalar_program(const int32_t* ops, const double* consts, int 
     if (e != cudaSuccess) { gpe::set_error("scalar_program_kernel: %s", cudaGetErrorString(e)); return -4; }
     return 0;
 }
+
+
+// ---- curriculum stage bookkeeping: one launch per epoch ------------------------------------------------------------------
+// What R/harmonic_pinn_simulation.py:385-423 does on the HOST after every epoch -- scheduler.step(loss) of
+// CosineAnnealingWarmRestarts (the reference passes the loss where the scheduler expects an epoch), the loss / mu /
+// constraint logs, best-loss patience counter, the early-stop test and the snapshot of the parameters of the stop epoch --
+// on device scalars, so an epoch stays one CUDA-graph replay.  One CTA: thread 0 does the scalar part, all threads copy the
+// snapshot in the (single) epoch that trips the stop.
+namespace gpe {
+namespace {
+__global__ void stage_bookkeeping_kernel(gpe_stage_state st, gpe_stage_consts c, gpe_stage_snapshot snap) {
+    __shared__ int first_s;
+    if (threadIdx.x == 0) {
+        const float val = *st.total, best = *st.best;
+        const long long ep = *st.epoch;
+        // CosineAnnealingWarmRestarts(T_0, T_mult, eta_min).step(val): fp32, the order of gpe_b200.training._loss_as_epoch_lr
+        const float T0 = c.t_0, tm1 = c.t_mult - 1.f;
+        float n = floorf(log2f(fmaxf(val / T0 * tm1 + 1.f, 1.f)));
+        const bool restart = val >= T0;
+        const float p2 = exp2f(n);
+        const float t_cur = restart ? val - T0 * (p2 - 1.f) / tm1 : val;
+        const float t_i = restart ? T0 * p2 : T0;
+        *st.lr = c.eta_min + (c.base_lr - c.eta_min) * (1.f + cosf(3.14159265358979323846f * t_cur / t_i)) / 2.f;
+        if (ep >= 0 && ep < c.ring_width) {
+            st.rings[ep] = val;
+            st.rings[c.ring_width + ep] = *st.mu;
+            st.rings[2 * c.ring_width + ep] = *st.constraint;
+        }
+        const bool improved = val < best;
+        const long long stale = improved ? 0 : *st.stale + 1;
+        *st.stale = stale;
+        *st.best = (val != val || best != best) ? (val != val ? val : best) : fminf(best, val);   // torch.minimum: NaN propagates
+        const bool hit = (val <= c.tol) || (stale >= c.patience);
+        const bool first = hit && !*st.done;
+        if (first) *st.final_epoch = ep;
+        if (hit) *st.done = 1;
+        *st.epoch = ep + 1;
+        first_s = first ? 1 : 0;
+    }
+    __syncthreads();
+    if (first_s) {
+        for (int t = 0; t < snap.n; ++t)
+            for (long long i = threadIdx.x; i < snap.numel[t]; i += blockDim.x) snap.dst[t][i] = snap.src[t][i];
+    }
+}
+}  // namespace
+}  // namespace gpe
+
+extern "C" int gpe_stage_bookkeeping(const gpe_stage_state* st, const gpe_stage_consts* c, const gpe_stage_snapshot* snap, gpe_stream_t stream) {
+    if (!st || !c || !snap) { gpe::set_error("gpe_stage_bookkeeping: null argument"); return -1; }
+    if (!st->total || !st->mu || !st->constraint || !st->lr || !st->epoch || !st->final_epoch || !st->done || !st->best || !st->stale || !st->rings) {
+        gpe::set_error("gpe_stage_bookkeeping: null state pointer"); return -1;
+    }
+    if (snap->n < 0 || snap->n > GPE_STAGE_MAX_TENSORS) { gpe::set_error("gpe_stage_bookkeeping: %d snapshot tensors (0..%d)", snap->n, GPE_STAGE_MAX_TENSORS); return -1; }
+    for (int t = 0; t < snap->n; ++t)
+        if (!snap->src[t] || !snap->dst[t] || snap->numel[t] < 0) { gpe::set_error("gpe_stage_bookkeeping: bad snapshot tensor %d", t); return -1; }
+    if (c->ring_width < 0 || !(c->t_0 > 0.f) || !(c->t_mult > 1.f)) { gpe::set_error("gpe_stage_bookkeeping: bad constants"); return -1; }
+    gpe::stage_bookkeeping_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*st, *c, *snap);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { gpe::set_error("stage_bookkeeping_kernel: %s", cudaGetErrorString(e)); return -4; }
+    return 0;
+}

@@ -324,6 +324,44 @@ std::tuple<Tensor, Tensor> scalar_program(const Tensor& ops, const Tensor& const
     return {vals, jac};
 }
 
+// gpe::stage_bookkeeping: the host side of one curriculum epoch (scheduler.step(loss), logs, patience, early stop, snapshot)
+// on device scalars, one launch.  All state tensors are updated in place.
+void stage_bookkeeping(const Tensor& total, const Tensor& mu, const Tensor& constraint, Tensor lr, Tensor epoch, Tensor final_epoch,
+                       Tensor done, Tensor best, Tensor stale, Tensor rings, at::TensorList params, at::TensorList snaps, double base_lr,
+                       double tol, int64_t patience, double t_0, double t_mult, double eta_min) {
+    auto f32 = [](const Tensor& t, const char* nm) {
+        TORCH_CHECK(t.is_cuda() && t.scalar_type() == at::kFloat && t.numel() == 1, "gpe_b200: `", nm, "` must be a CUDA float32 scalar");
+    };
+    auto i64 = [](const Tensor& t, const char* nm) {
+        TORCH_CHECK(t.is_cuda() && t.scalar_type() == at::kLong && t.numel() == 1, "gpe_b200: `", nm, "` must be a CUDA int64 scalar");
+    };
+    f32(total, "total"); f32(mu, "mu"); f32(constraint, "constraint"); f32(lr, "lr"); f32(best, "best");
+    i64(epoch, "epoch"); i64(final_epoch, "final_epoch"); i64(stale, "stale");
+    TORCH_CHECK(done.is_cuda() && done.scalar_type() == at::kBool && done.numel() == 1, "gpe_b200: `done` must be a CUDA bool scalar");
+    TORCH_CHECK(rings.is_cuda() && rings.scalar_type() == at::kFloat && rings.is_contiguous() && rings.dim() == 2 && rings.size(0) == 3,
+                "gpe_b200: `rings` must be a contiguous CUDA float32 tensor [3, epochs]");
+    TORCH_CHECK(params.size() == snaps.size() && (int64_t)params.size() <= GPE_STAGE_MAX_TENSORS, "gpe_b200: params / snaps: equal length, at most ",
+                GPE_STAGE_MAX_TENSORS);
+    gpe_stage_snapshot snap{};
+    snap.n = (int)params.size();
+    for (size_t t = 0; t < params.size(); ++t) {
+        const Tensor &p = params[t], &q = snaps[t];
+        TORCH_CHECK(p.is_cuda() && q.is_cuda() && p.scalar_type() == at::kFloat && q.scalar_type() == at::kFloat && p.is_contiguous() &&
+                        q.is_contiguous() && p.numel() == q.numel(),
+                    "gpe_b200: parameter and snapshot tensors must be contiguous CUDA float32 tensors of equal size");
+        snap.src[t] = p.data_ptr<float>();
+        snap.dst[t] = q.data_ptr<float>();
+        snap.numel[t] = p.numel();
+    }
+    gpe_stage_state st{total.data_ptr<float>(), mu.data_ptr<float>(), constraint.data_ptr<float>(), lr.data_ptr<float>(), epoch.data_ptr<int64_t>(),
+                       final_epoch.data_ptr<int64_t>(), stale.data_ptr<int64_t>(), reinterpret_cast<unsigned char*>(done.data_ptr<bool>()),
+                       best.data_ptr<float>(), rings.data_ptr<float>()};
+    gpe_stage_consts c{(float)base_lr, (float)tol, (float)t_0, (float)t_mult, (float)eta_min, patience, rings.size(1)};
+    c10::cuda::CUDAGuard guard(total.device());
+    auto stream = reinterpret_cast<gpe_stream_t>(at::cuda::getCurrentCUDAStream().stream());
+    check_rc(gpe_stage_bookkeeping(&st, &c, &snap, stream), "gpe_stage_bookkeeping");
+}
+
 double ffma_probe(int64_t mode, int64_t iters, const Tensor& sink) {
     TORCH_CHECK(sink.is_cuda() && sink.scalar_type() == at::kFloat && sink.numel() >= 1, "sink must be a CUDA float tensor");
     c10::cuda::CUDAGuard guard(sink.device());
@@ -491,6 +529,9 @@ TORCH_LIBRARY(gpe, m) {
           "int nl_kind, float nl_power, float scale, int bfactor, int sym_sign, int lap_cols, Tensor c) -> "
           "(Tensor, Tensor, Tensor, Tensor)");
     m.def("scalar_program(Tensor ops, Tensor consts, Tensor inputs, Tensor outs) -> (Tensor, Tensor)");
+    m.def("stage_bookkeeping(Tensor total, Tensor mu, Tensor constraint, Tensor(a!) lr, Tensor(b!) epoch, Tensor(c!) final_epoch, Tensor(d!) done, "
+          "Tensor(e!) best, Tensor(f!) stale, Tensor(g!) rings, Tensor[] params, Tensor(h!)[] snaps, float base_lr, float tol, int patience, "
+          "float t_0, float t_mult, float eta_min) -> ()");
     m.def("ffma_probe(int mode, int iters, Tensor sink) -> float");
 }
 
@@ -502,6 +543,7 @@ TORCH_LIBRARY_IMPL(gpe, CUDA, m) {
     m.impl("gram_moments", &gram_moments);
     m.impl("gram_adjoints", &gram_adjoints);
     m.impl("scalar_program", &scalar_program);
+    m.impl("stage_bookkeeping", &stage_bookkeeping);
     m.impl("ffma_probe", &ffma_probe);
 }
 

@@ -69,7 +69,7 @@ lib.gpe_ffma_probe.argtypes = [ctypes.c_int, ctypes.c_int, _vp, ctypes.POINTER(c
 EXPORTS = ("gpe_version", "gpe_last_error", "gpe_workspace_bytes", "gpe_mlp_jet_fwd", "gpe_mlp_jet_bwd",
            "gpe_gram_moments", "gpe_gram_adjoints", "gpe_ffma_probe", "gpe_set_tensor_path", "gpe_tc_profile",
            "gpe_tc_timings", "gpe_stash_bytes", "gpe_mlp_jet_fwd_stash", "gpe_mlp_jet_bwd_stashed", "gpe_scalar_program",
-           "gpe_mlp_jet_fwd_noalloc")
+           "gpe_mlp_jet_fwd_noalloc", "gpe_stage_bookkeeping")
 for _f in EXPORTS[2:]:
     getattr(lib, _f).restype = ctypes.c_int
 

@@ -123,20 +123,11 @@ class _Stage:
         torch.nn.utils.clip_grad_norm_(self.params, 1.0)
         self.opt.step()
         with torch.no_grad():
-            val = total.detach().float()
-            self.lr.copy_(_loss_as_epoch_lr(val, self.base_lr))        # :391
-            idx = self.epoch.view(1)
-            self.rings.index_copy_(1, idx, torch.stack([val, mu.detach().float(), cons.detach().float()]).view(3, 1))
-            improved = val < self.best                                  # :394-399
-            self.stale.copy_(torch.where(improved, torch.zeros_like(self.stale), self.stale + 1))
-            self.best.copy_(torch.minimum(self.best, val))
-            hit = (val <= self.tol) | (self.stale >= PATIENCE)          # :401-412
-            first = hit & ~self.done
-            self.final_epoch.copy_(torch.where(first, self.epoch, self.final_epoch))
-            for s, q in zip(self.snap, self.params):
-                s.copy_(torch.where(first, q, s))
-            self.done.logical_or_(hit)
-            self.epoch.add_(1)
+            # scheduler.step(loss) (:391), logs, patience (:394-399), early stop and snapshot (:401-412): one launch on device scalars
+            val = total.detach().float().reshape(())
+            torch.ops.gpe.stage_bookkeeping(val, mu.detach().float().reshape(()), cons.detach().float().reshape(()), self.lr, self.epoch,
+                                            self.final_epoch, self.done, self.best, self.stale, self.rings, self.params, self.snap,
+                                            float(self.base_lr), float(self.tol), PATIENCE, float(T_0), float(T_MULT), float(ETA_MIN))
         return val
 
     def finish(self, ran):

@@ -188,6 +188,36 @@ enum { GPE_PROG_CONST = 0, GPE_PROG_INPUT = 1, GPE_PROG_ADD = 2, GPE_PROG_SUB = 
 int gpe_scalar_program(const int32_t* ops, const double* consts, int n_nodes, const double* inputs, int n_in,
                        const int32_t* outs, int n_out, double* vals, double* jac, gpe_stream_t stream);
 
+/* ---- curriculum stage bookkeeping ------------------------------------------------------------
+ * What the reference's curriculum loop does on the host after every epoch
+ * (Gross-Pitaevskii/src/final/refine/harmonic_pinn_simulation.py:385-423): scheduler.step(loss) of
+ * CosineAnnealingWarmRestarts(T_0, T_mult, eta_min) -- the loss goes where the scheduler expects an epoch --,
+ * the loss / mu / constraint logs (every epoch into rings[3][ring_width]; the reference keeps every 10th / 100th), the
+ * best-loss patience counter (:394-399), the early-stop test (:401-412) and the copy of the parameters of the stop epoch.
+ * All state lives in device scalars, so the epoch stays one CUDA-graph replay; one launch, one CTA.  `done` is one byte
+ * (torch.bool).  The snapshot copy src[t] -> dst[t] happens only in the epoch that first trips the stop. */
+#define GPE_STAGE_MAX_TENSORS 24
+typedef struct {
+    const float *total, *mu, *constraint; /* this epoch's scalars                       */
+    float* lr;                            /* out: the next epoch's learning rate        */
+    int64_t *epoch, *final_epoch, *stale; /* in/out                                     */
+    unsigned char* done;                  /* in/out                                     */
+    float* best;                          /* in/out                                     */
+    float* rings;                         /* [3][ring_width]: total, mu, constraint     */
+} gpe_stage_state;
+typedef struct {
+    float base_lr, tol, t_0, t_mult, eta_min;
+    int64_t patience, ring_width;
+} gpe_stage_consts;
+typedef struct {
+    int n;
+    const float* src[GPE_STAGE_MAX_TENSORS];
+    float* dst[GPE_STAGE_MAX_TENSORS];
+    int64_t numel[GPE_STAGE_MAX_TENSORS];
+} gpe_stage_snapshot;
+int gpe_stage_bookkeeping(const gpe_stage_state* st, const gpe_stage_consts* c, const gpe_stage_snapshot* snap,
+                          gpe_stream_t stream);
+
 /* ---- tensor-core (tcgen05) path control ----
  * The 3xTF32 tensor path is the GPE_PREC_AUTO default wherever it applies (64 < width <= 128, Laplacian jets, <= 3 hidden
  * matrices); GPE_TENSOR=0 in the environment or gpe_set_tensor_path(0) makes GPE_PREC_AUTO select the FFMA kernels instead
