@@ -385,7 +385,7 @@ def run_b200(args):
         gopt = torch.optim.Adam(params, lr=wl.lr, capturable=True)
 
         def body():
-            gopt.zero_grad(set_to_none=False)
+            gopt.zero_grad(set_to_none=True)
             lossg = loss_fn(X)
             lossg.backward()
             torch.nn.utils.clip_grad_norm_(params, max_norm=1.0)

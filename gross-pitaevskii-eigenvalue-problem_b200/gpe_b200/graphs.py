@@ -5,7 +5,7 @@ The small configurations of the reference (config 1: 10k points, [1,100,100,100,
 ~200 small kernels (jet forward, moments, the fp64 scalar algebra of the loss, adjoints, reverse, clip, Adam).  The
 ops of this package allocate through torch's caching allocator and launch on the current stream only, so the whole
 step -- zero_grad, the reference's loss methods, backward(), clip_grad_norm_, optimizer.step() -- captures into one
-CUDA graph.  Measured on B200, config 1 with the root-notebook loop body: 3.6 ms eager -> 0.90 ms per step.
+CUDA graph.  Measured on B200, config 1 with the root-notebook loop body: 2.2 ms eager -> 0.34-0.41 ms per step (round 1: 0.90).
 
     step = GraphedStep(lambda: train_body(model, X, ...), optimizer)     # train_body returns tensors (loss, mu, ...)
     for epoch in range(n):
@@ -14,7 +14,8 @@ CUDA graph.  Measured on B200, config 1 with the root-notebook loop body: 3.6 ms
 Rules (CUDA graphs): drop every reference to losses / outputs of earlier EAGER steps on the same parameters before
 constructing a GraphedStep (a live loss keeps its graph, whose AccumulateGrad nodes stay bound to the eager stream, and
 the capture fails with "legacy stream depend on a capturing blocking stream"); tensor shapes and the python control flow of the step must not change between replays; use
-`torch.optim.Adam(..., capturable=True)`; read results with `.item()`/`float()` only outside the step function
+`torch.optim.Adam(..., capturable=True)`; call `zero_grad(set_to_none=True)` inside the step (the backward then hands its
+gradient tensors over -- with zeroed `.grad` buffers every parameter costs a fill and an accumulate add per step); read results with `.item()`/`float()` only outside the step function
 (e.g. every k-th epoch for the early-stop test); scalars that change per stage (gamma of the curriculum) must be
 device tensors updated in place with `.fill_()` / `.copy_()`.  Evaluating the model between replays (monitoring every
 k-th epoch) is safe: every replay invalidates the models' per-step caches, and evaluations without grad are never cached.

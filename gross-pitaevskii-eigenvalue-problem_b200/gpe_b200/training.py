@@ -106,7 +106,7 @@ class _Stage:
 
     def body(self, first_of_mode=False):
         m = self.model
-        self.opt.zero_grad(set_to_none=False)
+        self.opt.zero_grad(set_to_none=True)     # the backward hands its gradient tensors over: no fill, no accumulate add
         u_pred = m.forward(self.X)
         if first_of_mode:                                              # :366-371
             self.normal_const = float(torch.max(u_pred).detach())

@@ -18,7 +18,7 @@ gopt = torch.optim.Adam(params, lr=wl.lr, capturable=True)
 
 
 def body():
-    gopt.zero_grad(set_to_none=False)
+    gopt.zero_grad(set_to_none=True)
     loss = loss_fn(X)
     loss.backward()
     torch.nn.utils.clip_grad_norm_(params, max_norm=1.0)
