@@ -134,6 +134,8 @@ std::mutex g_plan_mu;
 PlanEntry g_plans[64];
 int g_n_plans = 0;
 
+bool use_tensor_path(const gpe_mlp_desc* desc);
+bool tc_shape_ok(const gpe_mlp_desc* desc);
 int padded_width(int w) { return w <= 64 ? 64 : w <= 128 ? 128 : w <= 256 ? 256 : 0; }
 
 int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
@@ -148,12 +150,13 @@ int get_plan(const gpe_mlp_desc* desc, JetPlan* out, int* wp_out) {
     }
     if (desc->jet < 0 || desc->jet > 3) { set_error("unknown jet kind %d", desc->jet); return -1; }
     if (desc->precision < GPE_PREC_FP32 || desc->precision > GPE_PREC_AUTO) { set_error("unknown precision %d", desc->precision); return -1; }
-    if (desc->precision == GPE_PREC_TF32X3 && !(desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden))) {
-        set_error("GPE_PREC_TF32X3: no tcgen05 kernel for d=%d width=%d n_hidden=%d jet=%d act=%d (64 < width <= 128, 2..4 hidden layers, "
-                  "Laplacian-type jets); use GPE_PREC_AUTO or GPE_PREC_FP32", desc->d, desc->width, desc->n_hidden, desc->jet, desc->act);
+    if (desc->precision == GPE_PREC_TF32X3 && !tc_shape_ok(desc)) {
+        set_error("GPE_PREC_TF32X3: no tcgen05 kernel for d=%d width=%d n_hidden=%d jet=%d act=%d (33 <= width <= 128 -- LeakyReLU: 65 <= width "
+                  "--, 2..4 hidden layers, Laplacian-type jets); use GPE_PREC_AUTO or GPE_PREC_FP32", desc->d, desc->width, desc->n_hidden, desc->jet, desc->act);
         return -1;
     }
-    const int wp = padded_width(desc->width);
+    // the tensor path packs every width up to 128 into its 128-wide layout
+    const int wp = (desc->width >= 1 && desc->width <= 64 && use_tensor_path(desc)) ? 128 : padded_width(desc->width);
     if (desc->width < 1 || !wp) { set_error("hidden width %d unsupported (1..256)", desc->width); return -1; }
     int dev = -1;
     if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device (this library has no CPU fallback)"); return -2; }
@@ -190,7 +193,10 @@ bool tc_enabled() {
 // GPE_PREC_TF32X3: the tcgen05 kernels (get_plan rejects shapes they do not cover); GPE_PREC_AUTO: tcgen05 where a kernel
 // exists, unless the process default (GPE_TENSOR=0 / gpe_set_tensor_path(0)) says FFMA.
 bool tc_shape_ok(const gpe_mlp_desc* desc) {
-    return desc->act != ACT_RESBLOCK_TANH && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
+    // W <= 64 (zero-padded into the 128-wide kernels) only with the smooth activations: a piecewise-linear activation turns the
+    // tensor path's ~1e-6 perturbation of a pre-activation next to the kink into an O(1/N) change of the gradient
+    const bool smooth = desc->act == ACT_TANH || desc->act == ACT_SHIFTED_TANH;
+    return desc->act != ACT_RESBLOCK_TANH && (desc->width > 64 || smooth) && tc_eligible(desc->d, desc->jet, desc->width, desc->n_hidden);
 }
 bool use_tensor_path(const gpe_mlp_desc* desc) {
     if (desc->precision == GPE_PREC_FP32) return false;

@@ -10,7 +10,11 @@ namespace gpe {
 
 bool tc_eligible(int d, int jet, int width, int L) {
     const bool lap = jet == JET_LAPLACIAN || (d == 1 && (jet == JET_DIAG || jet == JET_FULL));
-    return lap && width > 64 && width <= 128 && L >= 2 && L - 1 <= tcp::kTcMaxMat;
+    // every width up to 128 is zero-padded to the 128-wide images: measured on B200 the padded tensor kernels beat the FFMA
+    // kernels of W <= 64 at every size (scripts/w64_probe.py, [2,64x3,1]: 4000 points 0.11 vs 0.12 ms, 1M points 5.3 vs 12.0 ms)
+    // (not below 33: a handful of features with a small, cancelling output sees the 2e-7 absolute error of the ex2/rcp tanh;
+    // capi.cu additionally keeps kinked activations of W <= 64 on the FFMA kernels)
+    return lap && width >= 33 && width <= 128 && L >= 2 && L - 1 <= tcp::kTcMaxMat;
 }
 
 size_t tc_wimg_bytes(int L) { return (size_t)(L - 1) * 2 * 2 * tcp::kImgFloats * sizeof(float); }

@@ -219,7 +219,7 @@ int gpe_stage_bookkeeping(const gpe_stage_state* st, const gpe_stage_consts* c, 
                           gpe_stream_t stream);
 
 /* ---- tensor-core (tcgen05) path control ----
- * The 3xTF32 tensor path is the GPE_PREC_AUTO default wherever it applies (64 < width <= 128, Laplacian jets, <= 3 hidden
+ * The 3xTF32 tensor path is the GPE_PREC_AUTO default wherever it applies (33 <= width <= 128 -- LeakyReLU: 65 <= width --, Laplacian jets, <= 3 hidden
  * matrices); GPE_TENSOR=0 in the environment or gpe_set_tensor_path(0) makes GPE_PREC_AUTO select the FFMA kernels instead
  * (north_star: tensor cores "only if TF32/BF16-split accuracy holds", otherwise register-blocked FFMA).
  * gpe_set_tensor_path returns the previous setting.  gpe_tc_profile(1) brackets every tensor-path backward

@@ -491,8 +491,9 @@ def test_reverse_kernel_runs_once_per_step(golden):
         pde, _, _, _ = model.pde_loss(2, X, model.forward(X), 1.0)
         pde.backward()
         torch.cuda.synchronize()
-    n_bwd = sum(1 for e in prof.events() if "jet_bwd_kernel" in e.name)
-    n_fwd = sum(1 for e in prof.events() if "jet_fwd_kernel" in e.name)
+    # FFMA kernels (jet_fwd_kernel / jet_bwd_kernel) or the tensor path's (jet_fwd*_tc_kernel with the stash / jet_rev*_tc_kernel)
+    n_bwd = sum(1 for e in prof.events() if "jet_bwd_kernel" in e.name or ("jet_rev" in e.name and "tc_kernel" in e.name))
+    n_fwd = sum(1 for e in prof.events() if "jet_fwd_kernel" in e.name or ("jet_fwd" in e.name and "tc_kernel" in e.name))
     assert n_fwd == 1 and n_bwd == 1, (n_fwd, n_bwd)
 
 

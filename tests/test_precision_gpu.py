@@ -29,13 +29,22 @@ def test_precision_selects_the_kernels_per_call():
     b = ops.mlp_jet_fwd(x, Ws, bs, 0, ops.JET_LAPLACIAN, precision=ops.PREC_TF32X3)
     for u, v in zip(a, b):
         assert float((u - v).norm() / v.norm()) < 1e-5
-    # no tensor-core kernel for width 64 / the full 2-D Hessian: TF32X3 must refuse, AUTO and FP32 must run
+    # widths up to 64 (the paper's nets) are zero-padded into the 128-wide tensor kernels: AUTO picks them, and they agree with FFMA
     Ws64, bs64 = make_net(2, 64, 3, seed=1, act=0)
     Ws64, bs64 = [w.cuda() for w in Ws64], [b.cuda() for b in bs64]
+    k64 = _kernels_of(lambda: ops.mlp_jet_fwd(x, Ws64, bs64, 0, ops.JET_LAPLACIAN, precision=ops.PREC_AUTO))
+    assert any("tc_kernel" in k for k in k64)
+    a64 = ops.mlp_jet_fwd(x, Ws64, bs64, 0, ops.JET_LAPLACIAN, precision=ops.PREC_FP32)
+    b64 = ops.mlp_jet_fwd(x, Ws64, bs64, 0, ops.JET_LAPLACIAN, precision=ops.PREC_TF32X3)
+    for u, v in zip(a64, b64):
+        assert float((u - v).norm() / v.norm()) < 1e-5
+    # no tensor-core kernel for width 200 / the full 2-D Hessian: TF32X3 must refuse, AUTO and FP32 must run
+    Ws200, bs200 = make_net(2, 200, 3, seed=1, act=0)
+    Ws200, bs200 = [w.cuda() for w in Ws200], [b.cuda() for b in bs200]
     with pytest.raises(RuntimeError, match="GPE_PREC_TF32X3"):
-        ops.mlp_jet_fwd(x, Ws64, bs64, 0, ops.JET_LAPLACIAN, precision=ops.PREC_TF32X3)
+        ops.mlp_jet_fwd(x, Ws200, bs200, 0, ops.JET_LAPLACIAN, precision=ops.PREC_TF32X3)
     with pytest.raises(RuntimeError, match="GPE_PREC_TF32X3"):
         ops.mlp_jet_fwd(x, Ws, bs, 0, ops.JET_FULL, precision=ops.PREC_TF32X3)
-    ops.mlp_jet_fwd(x, Ws64, bs64, 0, ops.JET_LAPLACIAN, precision=ops.PREC_AUTO)
+    ops.mlp_jet_fwd(x, Ws200, bs200, 0, ops.JET_LAPLACIAN, precision=ops.PREC_AUTO)
     with pytest.raises(RuntimeError, match="unknown precision"):
         ops.mlp_jet_fwd(x, Ws, bs, 0, ops.JET_LAPLACIAN, precision=7)
