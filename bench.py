@@ -316,12 +316,15 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    from gpe_b200.models import invalidate_caches
+
     def make_step(Xc):
         def step(events=None):
             for p in params:
                 p.grad = None
             if events:
                 events[0].record()
+            invalidate_caches()      # a training step follows an optimizer step: nothing of the previous step's jets may be reused
             loss = loss_fn(Xc)
             if events:
                 events[1].record()

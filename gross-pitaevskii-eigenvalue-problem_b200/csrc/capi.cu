@@ -204,6 +204,19 @@ bool use_tensor_path(const gpe_mlp_desc* desc) {
     return tc_enabled() && tc_shape_ok(desc);
 }
 
+// Value-only forwards (the mirrored points of symmetry_loss, monitoring calls) of a net the tensor kernels cover: from
+// kValueTcMinPoints points on, the tensor forward -- jets computed and dropped -- beats the FFMA value kernel (1M points,
+// [1,128x4,1]: 1.5 vs 2.4 ms).  GPE_PREC_AUTO only; the backward of a value-only call stays on the FFMA kernels.
+constexpr long long kValueTcMinPoints = 16384;
+bool value_on_tensor(const gpe_mlp_desc* desc, long long n, gpe_mlp_desc* as_jets) {
+    if (desc->jet != GPE_JET_VALUE || desc->precision != GPE_PREC_AUTO || n < kValueTcMinPoints) return false;
+    gpe_mlp_desc dv = *desc;
+    dv.jet = desc->d == 1 ? GPE_JET_DIAG : GPE_JET_LAPLACIAN;
+    if (!use_tensor_path(&dv)) return false;
+    if (as_jets) *as_jets = dv;
+    return true;
+}
+
 struct WsLayout {
     size_t wt_fwd, w_bwd, small, wimg, small_acc, dWacc, stash, wimg_rev, zb, total_fwd, total_bwd;
     bool tc;
@@ -335,7 +348,16 @@ int gpe_workspace_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* fwd_bytes, 
     if (rc) return rc;
     if (n < 0) { set_error("negative n"); return -1; }
     const WsLayout w = layout(desc, p, wp, n);
-    if (fwd_bytes) *fwd_bytes = w.total_fwd;
+    size_t fwd = w.total_fwd;
+    gpe_mlp_desc dv;
+    if (value_on_tensor(desc, n, &dv)) {       // the forward may run on the tensor kernels: their layout (128-wide, weight images)
+        JetPlan pv;
+        int wpv;
+        if (int rcv = get_plan(&dv, &pv, &wpv)) return rcv;
+        const size_t fv = layout(&dv, pv, wpv, n).total_fwd;
+        fwd = fv > fwd ? fv : fwd;
+    }
+    if (fwd_bytes) *fwd_bytes = fwd;
     if (bwd_bytes) *bwd_bytes = w.total_bwd;
     return 0;
 }
@@ -352,6 +374,21 @@ static int jet_fwd_impl(const gpe_mlp_desc* desc, const float* const* W, const f
     if (!W || !b || !x || !u || !ws) { set_error("null pointer argument"); return -1; }
     if (desc->jet != GPE_JET_VALUE && (!g || !h)) { set_error("g and h outputs required for derivative jets"); return -1; }
     if (xform && desc->jet != GPE_JET_VALUE) { set_error("xform is only valid with GPE_JET_VALUE"); return -1; }
+    gpe_mlp_desc dv;
+    if (!resident && value_on_tensor(desc, n, &dv)) {
+        JetPlan pv;
+        int wpv;
+        if ((rc = get_plan(&dv, &pv, &wpv))) return rc;
+        const WsLayout wv = layout(&dv, pv, wpv, n);
+        if (ws_bytes < wv.total_fwd) { set_error("workspace too small: %zu < %zu", ws_bytes, wv.total_fwd); return -1; }
+        char* vbase = static_cast<char*>(ws);
+        cudaStream_t vs = reinterpret_cast<cudaStream_t>(stream);
+        NvtxRange vrange("gpe:jet_fwd(tensor, value only)");
+        if ((rc = pack(&dv, wpv, wv, W, b, vbase, false, vs, true, false, false))) return rc;
+        const XForm vxf = make_xform(xform);
+        return launch_fwd_tc(dv.d, dv.n_hidden, dv.act, reinterpret_cast<float*>(vbase + wv.wimg), reinterpret_cast<float*>(vbase + wv.small), x, n, u,
+                             nullptr, nullptr, nullptr, vs, vxf.a, vxf.b);
+    }
     const WsLayout w = layout(desc, p, wp, n);
     if (ws_bytes < w.total_fwd) { set_error("workspace too small: %zu < %zu", ws_bytes, w.total_fwd); return -1; }
     char* base = static_cast<char*>(ws);

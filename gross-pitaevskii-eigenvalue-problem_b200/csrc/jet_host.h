@@ -65,7 +65,7 @@ int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wim
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, const float* resident, float* zb,
                   double* dWacc, float* small_acc, cudaStream_t s, const unsigned int** abort_flag);
 int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
-                  float* g, float* h, float* resident, cudaStream_t s);
+                  float* g, float* h, float* resident, cudaStream_t s, const float* xa = nullptr, const float* xb = nullptr);
 size_t tc_resident_stash_bytes(int L, long long n);
 
 }  // namespace gpe

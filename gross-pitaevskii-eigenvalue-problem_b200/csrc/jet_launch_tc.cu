@@ -295,7 +295,8 @@ size_t tc_zb_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)tc_bwd
 int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wimg_rev, const float* small, const float* x,
                   long long n, const float* ub, const float* gb, const float* hb, float* stash, const float* resident, float* zb,
                   double* dWacc, float* small_acc, cudaStream_t s, const unsigned int** abort_flag) {
-    tcp::TcParams Pf{L, act, wimg_fwd, small, tc_debias(), tc_interleave_fwd()}, Pr{L, act, wimg_rev, small, 1.f, tc_interleave()};
+    tcp::TcParams Pf{L, act, wimg_fwd, small, {1.f, 1.f}, {0.f, 0.f}, tc_debias(), tc_interleave_fwd()},
+        Pr{L, act, wimg_rev, small, {1.f, 1.f}, {0.f, 0.f}, 1.f, tc_interleave()};
     const long long chunk = tc_bwd_chunk(n);
     return d == 1 ? bwd_tc<1>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag)
                   : bwd_tc<2>(Pf, Pr, x, n, ub, gb, hb, stash, resident, zb, dWacc, small_acc, chunk, s, abort_flag);
@@ -305,8 +306,9 @@ int launch_bwd_tc(int d, int L, int act, const float* wimg_fwd, const float* wim
 size_t tc_resident_stash_bytes(int L, long long n) { return (size_t)(L - 1) * (size_t)((n + 7) / 8) * tcp::kBlkFloats * sizeof(float); }
 
 int launch_fwd_tc(int d, int L, int act, const float* wimg, const float* small, const float* x, long long n, float* u,
-                  float* g, float* h, float* resident, cudaStream_t s) {
-    tcp::TcParams P{L, act, wimg, small, tc_debias(), tc_interleave_fwd()};
+                  float* g, float* h, float* resident, cudaStream_t s, const float* xa, const float* xb) {
+    // xa / xb (value-only calls: g = h = nullptr, no stash): the affine input map of the mirrored points
+    tcp::TcParams P{L, act, wimg, small, {xa ? xa[0] : 1.f, xa ? xa[1] : 1.f}, {xb ? xb[0] : 0.f, xb ? xb[1] : 0.f}, tc_debias(), tc_interleave_fwd()};
     if (resident) return d == 1 ? fwd_tc<1, true>(P, x, n, u, g, h, resident, s) : fwd_tc<2, true>(P, x, n, u, g, h, resident, s);
     return d == 1 ? fwd_tc<1, false>(P, x, n, u, g, h, nullptr, s) : fwd_tc<2, false>(P, x, n, u, g, h, nullptr, s);
 }

@@ -44,6 +44,7 @@ struct TcParams {
     int act;
     const float* wimg;     // [L-1][cta 2][hi,lo][kImgFloats]
     const float* small;    // W0t[D][128], b[L][128], wout[128], bout[4]   (same pack as the FFMA path)
+    float xa[2], xb[2];    // forward sweeps only: x_eff = xa * x + xb per coordinate (mirror points of symmetry_loss; value-only calls)
     float debias;          // forward sweeps: multiplier on every accumulator read, 1 + beta 2^-24 (tc_debias, jet_launch_tc.cu)
     int interleave;        // order of the 16 hi*hi MMAs of a layer relative to its 32 correction MMAs (the accumulator is rounded
                            // toward zero after every MMA, so what lands late lands on a large accumulator):
@@ -334,7 +335,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
             const bool valid = p < n;
             float xin[D];
 #pragma unroll
-            for (int i = 0; i < D; ++i) xin[i] = valid ? __ldg(x + p * D + i) : 0.f;
+            for (int i = 0; i < D; ++i) xin[i] = valid ? fmaf(P.xa[i], __ldg(x + p * D + i), P.xb[i]) : 0.f;
             // whole image blocks are written: the tail rows (x = 0) stay finite
             float* sp = stash + slot_off(p, sub, tq);
             const bool do_stash = STASH && (p >> 3) < nblk8;
@@ -354,7 +355,7 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                     for (int k = 0; k < D; ++k) {
                         const float wk = e ? w2[k].y : w2[k].x;
                         z0 = fmaf(wk, xin[k], z0);
-                        a[e][1 + k] = wk;
+                        a[e][1 + k] = wk * P.xa[k];      // chain rule of x_eff = xa x + xb (xa = 1 outside mirrored value calls)
                     }
                     a[e][0] = z0;
                     a[e][1 + D] = 0.f;
@@ -429,8 +430,9 @@ jet_fwd_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* _
                 }
                 out_u[p] = o[0] + bout;
 #pragma unroll
-                for (int i = 0; i < D; ++i) out_g[p * D + i] = o[1 + i];
-                out_h[p] = o[1 + D];
+                for (int i = 0; i < D; ++i)
+                    if (out_g) out_g[p * D + i] = o[1 + i];
+                if (out_h) out_h[p] = o[1 + D];
             }
         }
     } else if (cta == 0 && lane == 0) {
@@ -641,7 +643,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
         auto input_layer = [&](const Tile& ts) {
             float xin[D];
 #pragma unroll
-            for (int i = 0; i < D; ++i) xin[i] = ts.valid ? __ldg(x + ts.p * D + i) : 0.f;
+            for (int i = 0; i < D; ++i) xin[i] = ts.valid ? fmaf(P.xa[i], __ldg(x + ts.p * D + i), P.xb[i]) : 0.f;
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
                 const int f = 32 * c + fb;
@@ -657,7 +659,7 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
                     for (int k = 0; k < D; ++k) {
                         const float wk = e ? w2[k].y : w2[k].x;
                         z0 = fmaf(wk, xin[k], z0);
-                        a[e][1 + k] = wk;
+                        a[e][1 + k] = wk * P.xa[k];      // chain rule of x_eff = xa x + xb (xa = 1 outside mirrored value calls)
                     }
                     a[e][0] = z0;
                     a[e][1 + D] = 0.f;
@@ -734,8 +736,9 @@ jet_fwd2_tc_kernel(TcParams P, const float* __restrict__ x, long long n, float* 
                     }
                     out_u[ts.p] = o[0] + bout;
 #pragma unroll
-                    for (int i = 0; i < D; ++i) out_g[ts.p * D + i] = o[1 + i];
-                    out_h[ts.p] = o[1 + D];
+                    for (int i = 0; i < D; ++i)
+                        if (out_g) out_g[ts.p * D + i] = o[1 + i];
+                    if (out_h) out_h[ts.p] = o[1 + D];
                 }
             }
         };

@@ -463,3 +463,43 @@ def test_edge_inputs_fail_loudly():
     u = torch.rand(64, device="cuda")
     with pytest.raises(ValueError, match="integer p"):
         ops.gram_moments(u, None, None, None, d=1, nl_kind=ops.NL_POW, nl_power=2.5)
+
+
+# ------------------------------------------------------------------------------------------- value-only forwards at scale
+@pytest.mark.parametrize("d,W,L", [(1, 128, 4), (2, 100, 3), (1, 64, 3)])
+def test_large_value_only_forward_runs_on_the_tensor_kernels(d, W, L):
+    """From 16384 points on, a value-only forward (the mirrored points of symmetry_loss: x -> a x + b) of a net the tensor
+    kernels cover runs on them (jets computed, dropped); below that, and with GPE_PREC_FP32, the FFMA value kernel.  Same
+    values to the parity bar, and the gradient through the value-only node is unchanged (its backward stays FFMA)."""
+    from gpe_b200 import ops
+    Ws, bs = make_net(d, W, L, seed=4, act=0)
+    Ws, bs = [w.cuda().requires_grad_(True) for w in Ws], [b.cuda().requires_grad_(True) for b in bs]
+    n = 40001
+    g0 = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.rand(n, d, device="cuda", generator=g0) * 4 - 2
+    xf = ((-1.0,) * d + (1.0,) * (2 - d), (0.5,) * d + (0.0,) * (2 - d))
+
+    def kernels(fn):
+        with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        return {e.name for e in prof.events()}
+
+    with torch.no_grad():
+        names = kernels(lambda: ops.mlp_jets(x, Ws, bs, 0, ops.JET_VALUE, xf))
+        assert any("jet_fwd" in k and "tc_kernel" in k for k in names), names
+        small = kernels(lambda: ops.mlp_jets(x[:2000].contiguous(), Ws, bs, 0, ops.JET_VALUE, xf))
+        assert not any("tc_kernel" in k for k in small)
+        u_t = ops.mlp_jets(x, Ws, bs, 0, ops.JET_VALUE, xf)[0]
+        u_f = ops.mlp_jets(x, Ws, bs, 0, ops.JET_VALUE, xf, ops.PREC_FP32)[0]
+        xm = x * torch.tensor(xf[0][:d], device="cuda") + torch.tensor(xf[1][:d], device="cuda")
+        u_j = ops.mlp_jets(xm, Ws, bs, 0, ops.JET_DIAG if d == 1 else ops.JET_LAPLACIAN)[0]
+    assert _rel(u_t, u_f) < 1e-5 and _rel(u_t, u_j) < 1e-5
+    w = torch.randn(n, device="cuda", generator=g0) * 0.3 + 1
+    grads = []
+    for prec in (ops.PREC_AUTO, ops.PREC_FP32):
+        for t in Ws + bs:
+            t.grad = None
+        (ops.mlp_jets(x, Ws, bs, 0, ops.JET_VALUE, xf, prec)[0] * w).sum().backward()
+        grads.append(torch.cat([t.grad.reshape(-1) for t in Ws + bs]).double())
+    assert float((grads[0] - grads[1]).norm() / grads[1].norm()) < 1e-5
