@@ -95,7 +95,9 @@ const char* gpe_last_error(void); /* thread-local */
 int gpe_workspace_bytes(const gpe_mlp_desc* desc, int64_t n, size_t* fwd_bytes, size_t* bwd_bytes);
 
 /* W[0] [W,d], W[1..L-1] [W,W], W[L] [1,W]  (PyTorch [out,in] row-major); b[l] [W], b[L] [1].
- * x [n,d].  Outputs: u [n]; g [n,d]; h [n,H] (H by jet kind); g,h may be NULL for JET_VALUE. */
+ * x [n,d].  Outputs: u [n]; g [n,d]; h [n,H] (H by jet kind); g,h may be NULL for JET_VALUE.
+ * (GPE_PREC_AUTO, GPE_JET_VALUE, n >= 16384, a shape the tensor kernels cover: the tensor forward computes the values --
+ * gpe_workspace_bytes accounts for its layout.) */
 int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
                     int64_t n, const gpe_xform* xform, float* u, float* g, float* h, void* ws, size_t ws_bytes,
                     gpe_stream_t stream);
