@@ -65,8 +65,10 @@ enum {
 
 /* Arithmetic of the hidden-layer contractions, chosen PER CALL by gpe_mlp_desc.precision:
  * GPE_PREC_FP32: register-blocked FFMA (fp32 throughout), any supported shape.
- * GPE_PREC_TF32X3: tcgen05 tensor cores, every fp32 operand split into hi+lo TF32 halves and
- * three MMAs per product (hi*hi + hi*lo + lo*hi), fp32 accumulation in TMEM; a shape without a
+ * GPE_PREC_TF32X3: tcgen05 tensor cores, every fp32 operand split into hi + lo (hi = tf32) and the product formed as
+ * hi*hi + (hi*lo + lo*hi), fp32 accumulation in TMEM: the hi*hi term as tf32 MMAs, the 2^-11-sized bracket as tf32 MMAs
+ * (dW contraction) or as bf16 kind::f16 MMAs (forward and reverse sweeps), the forward epilogue compensating the
+ * accumulator's round-toward-zero bias; fp32-accurate to ~2e-6 on the jets.  A shape without a
  * tensor-core kernel is an error (-1), never a silent change of path.
  * GPE_PREC_AUTO: TF32X3 where a tensor-core kernel exists for the shape (and the process default
  * gpe_set_tensor_path / GPE_TENSOR allows it), else FP32. */
