@@ -114,7 +114,9 @@ int gpe_mlp_jet_fwd(const gpe_mlp_desc* desc, const float* const* W, const float
  * GPE_STATIC_MAX_POINTS, is rejected with -1 and a message (gpe_last_error).
  * Sharing: all calls on a device use the same array and it keeps the last call's contents; every byte the forward reads
  * is rewritten by this call's own pack kernel first, so nothing needs clearing between calls -- but two calls that can
- * OVERLAP on the GPU (different streams, or concurrent graph branches) race on it: serialise them on one stream. */
+ * OVERLAP on the GPU (different streams, or concurrent graph branches) race on it: serialise them on one stream.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress) and sets the kernels' shared-memory
+ * attributes: make that call once outside a stream capture (the usual warm-up call), later calls only launch. */
 #define GPE_STATIC_WS_BYTES (4u << 20)
 #define GPE_STATIC_MAX_POINTS (1ll << 24)
 int gpe_mlp_jet_fwd_noalloc(const gpe_mlp_desc* desc, const float* const* W, const float* const* b, const float* x,
