@@ -131,3 +131,54 @@ def test_known_answer_convergence(potential, lb, ub, exact):
         assert abs(mu - exact(mode)) < 1e-4 * exact(mode), (potential, mode, mu, exact(mode))
         losses = np.asarray(history[mode][0.0]["loss"], dtype=np.float64)
         assert np.isfinite(losses).all() and losses[-1] < 1e-3 * losses[0]
+
+
+def test_stage_bookkeeping_kernel_matches_the_tensor_arithmetic_it_replaced():
+    """gpe_stage_bookkeeping (csrc/point_ops.cu) against the device-tensor version of R/harmonic_pinn_simulation.py:385-423
+    it replaced: scheduler.step(loss) on both branches (loss below / above T_0), ring logs, patience counter, the stop by
+    tolerance and by patience, the snapshot of the stop epoch only, NaN losses."""
+    import math
+    from gpe_b200 import training
+    dev = "cuda"
+    torch.manual_seed(0)
+    params = [torch.randn(7, 5, device=dev), torch.randn(11, device=dev)]
+    snaps = [torch.zeros_like(q) for q in params]
+    snaps_ref = [torch.zeros_like(q) for q in params]
+    epochs, base_lr, tol, patience = 40, 3e-4, 1e-3, 6
+    st = dict(lr=torch.tensor(base_lr, device=dev), epoch=torch.zeros((), dtype=torch.long, device=dev),
+              final=torch.full((), epochs, dtype=torch.long, device=dev), done=torch.zeros((), dtype=torch.bool, device=dev),
+              best=torch.full((), float("inf"), device=dev), stale=torch.zeros((), dtype=torch.long, device=dev),
+              rings=torch.zeros(3, epochs, device=dev))
+    ref = {k: v.clone() for k, v in st.items()}
+    # losses: falling, one above T_0 = 200 (restart branch), a plateau that trips the patience, then one below tol
+    losses = [900.0, 450.0, 250.0, 120.0, 3.0, 1.0, 0.5] + [0.6] * 8 + [5e-4, float("nan"), 0.4]
+    for i, lv in enumerate(losses):
+        for q in params:
+            q.add_(0.01)                                    # the parameters move every epoch
+        val, mu, cons = torch.tensor(lv, device=dev), torch.tensor(1.0 + 0.1 * i, device=dev), torch.tensor(0.5 * lv, device=dev)
+        torch.ops.gpe.stage_bookkeeping(val, mu, cons, st["lr"], st["epoch"], st["final"], st["done"], st["best"], st["stale"], st["rings"],
+                                        params, snaps, base_lr, tol, patience, float(training.T_0), float(training.T_MULT), float(training.ETA_MIN))
+        # the tensor arithmetic of the previous version of training._Stage.body
+        ref["lr"].copy_(training._loss_as_epoch_lr(val, base_lr))
+        ref["rings"].index_copy_(1, ref["epoch"].view(1), torch.stack([val, mu, cons]).view(3, 1))
+        improved = val < ref["best"]
+        ref["stale"].copy_(torch.where(improved, torch.zeros_like(ref["stale"]), ref["stale"] + 1))
+        ref["best"].copy_(torch.minimum(ref["best"], val))
+        hit = (val <= tol) | (ref["stale"] >= patience)
+        first = hit & ~ref["done"]
+        ref["final"].copy_(torch.where(first, ref["epoch"], ref["final"]))
+        for s_, q in zip(snaps_ref, params):
+            s_.copy_(torch.where(first, q, s_))
+        ref["done"].logical_or_(hit)
+        ref["epoch"].add_(1)
+        torch.cuda.synchronize()
+        la, lb_ = float(st["lr"]), float(ref["lr"])
+        assert (math.isnan(la) and math.isnan(lb_)) or abs(la - lb_) <= 2e-6 * lb_, (i, la, lb_)
+        for k in ("epoch", "final", "done", "stale"):
+            assert st[k].item() == ref[k].item(), (i, k, st[k].item(), ref[k].item())
+        a, b = float(st["best"]), float(ref["best"])
+        assert (math.isnan(a) and math.isnan(b)) or a == b, (i, a, b)
+        assert torch.equal(torch.nan_to_num(st["rings"], nan=-7.0), torch.nan_to_num(ref["rings"], nan=-7.0))
+        for s_, r_ in zip(snaps, snaps_ref):
+            assert torch.equal(s_, r_)
+    assert bool(ref["done"]) and int(ref["final"]) == 12          # the patience stop: seven epochs after the last improvement (epoch 6)
