@@ -592,6 +592,11 @@ def run_b200(args):
                 "bound": "tensor", "kernel": sym, "achieved": achieved, "peak": bf16, "unit": "TFLOP/s", "frac": achieved / bf16,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if measured.get("bf16_tflops_sustained") else "fallback 1.4 PFLOP/s",
                 "tf32_peak": bf16 / 2, "effective_3xtf32_peak": bf16 / 6, "frac_of_3xtf32_peak": achieved / (bf16 / 6),
+                # what THIS kernel's MMA schedule could reach: per 32-feature chunk the sweeps issue 4 tf32 + 4 bf16 MMAs of equal
+                # duration (8 slots: tf32 peak x 4/8), the dW contraction 12 tf32 MMAs (tf32 peak x 4/12)
+                "mma_slots_per_chunk": 12 if kname == "dw_contraction" else 8,
+                "effective_peak_of_this_schedule": (bf16 / 6) if kname == "dw_contraction" else (bf16 / 4),
+                "frac_of_this_schedule": achieved / ((bf16 / 6) if kname == "dw_contraction" else (bf16 / 4)),
                 "algorithmic_flops_per_point": alg, "executed_tensor_flops_per_point": 3 * 2 * W * W * (2 + d) * (L - 1) * (alg // f_contr),
                 # same multiply-adds in every variant; the sweeps issue their two correction products as bf16 kind::f16 MMAs
                 # (K = 16: 8 MMA issue slots per 32-feature chunk instead of 12), the dW contraction keeps three tf32 products
